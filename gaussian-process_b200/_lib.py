@@ -1,0 +1,62 @@
+"""ctypes binding of libgpk.so (C ABI declared in include/gpk.h).  Fails loudly when the library
+has not been built: there is no fallback path."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libgpk.so")
+
+_vp, _i, _ll, _sz = C.c_void_p, C.c_int, C.c_longlong, C.c_size_t
+
+# name -> (restype, argtypes); mirrors include/gpk.h one to one
+SIGNATURES = {
+    "gpk_version": (_i, []),
+    "gpk_last_error_string": (C.c_char_p, []),
+    "gpk_launch_count": (C.c_ulonglong, []),
+    "gpk_padded_n": (_i, [_i]),
+    "gpk_cov_batched": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _ll, _ll, _vp]),
+    "gpk_potrf_workspace_bytes": (_sz, [_i, _i]),
+    "gpk_potrf_batched": (_i, [_vp, _i, _i, _vp, _vp, _sz, _vp]),
+    "gpk_loss_workspace_bytes": (_sz, [_i, _i, _i]),
+    "gpk_loss_batched": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "gpk_fit_workspace_bytes": (_sz, [_i, _i]),
+    "gpk_fit": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "gpk_predict_workspace_bytes": (_sz, [_i, _i]),
+    "gpk_predict": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _ll, _vp, _vp, _i, _vp, _sz, _vp]),
+    "gpk_prob_surface": (_i, [_vp, _ll, _i, _i, _vp, _vp, _vp, _vp]),
+    "gpk_sum_gaussians": (_i, [_vp, _i, _vp, _i, C.c_double, _vp, _vp]),
+}
+
+_lib = None
+
+
+class GpkError(RuntimeError):
+    pass
+
+
+def load():
+    """Loads libgpk.so (once) and declares every prototype."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.isfile(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(or gaussian-process_b200/csrc/build.sh).  This package has no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)          # AttributeError here = library / header mismatch
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(status, what):
+    if status != 0:
+        msg = load().gpk_last_error_string()
+        raise GpkError(f"{what} failed (status {status}): {msg.decode() if msg else ''}")
+
+
+def launch_count():
+    return int(load().gpk_launch_count())

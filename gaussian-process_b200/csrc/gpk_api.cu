@@ -1,0 +1,238 @@
+// extern "C" entry points of libgpk (see include/gpk.h) and the host-side drivers that sequence the
+// kernels of the blocked factorisation.  No torch types, no allocation, no CPU fallback.
+#include <atomic>
+#include <cstdarg>
+#include <cstring>
+#include <mutex>
+
+#include "../../include/gpk.h"
+#include "gpk_common.cuh"
+
+namespace gpk {
+
+static std::mutex g_err_mu;
+static char g_err[512] = "";
+static std::atomic<unsigned long long> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+    std::lock_guard<std::mutex> lk(g_err_mu);
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+void count_launch(int n) { g_launches.fetch_add((unsigned long long)n); }
+
+int check_launch(const char* what) {
+    count_launch(1);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        set_error("%s: %s", what, cudaGetErrorString(e));
+        return 1;
+    }
+    return 0;
+}
+
+static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+BlockedLayout blocked_layout(int P, int N, int d) {
+    BlockedLayout L{};
+    L.P = P; L.N = N; L.d = d;
+    L.Np = round_up(N, NB);
+    L.T = L.Np / NB;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += align256(bytes); return o; };
+    const size_t Np = L.Np, T = L.T;
+    L.mat = take((size_t)P * Np * Np * 8);
+    L.dinv = take((size_t)P * T * NB * NB * 8);
+    L.dinvT = take((size_t)P * T * NB * NB * 8);
+    L.mt = take((size_t)P * NB * Np * 8);
+    L.xs = take((size_t)P * d * Np * 8);
+    L.sq = take((size_t)P * Np * 8);
+    L.cn = take((size_t)P * Np * 8);
+    L.z = take((size_t)P * Np * 8);
+    L.alpha = take((size_t)P * Np * 8);
+    L.total = off;
+    return L;
+}
+
+// Blocked left-looking Cholesky (phase 1).  mode: what the diagonal kernel leaves in the diagonal blocks.
+static int factor_phase(double* mat, int Np, int T, int P, double* dinv, double* dinvT, int* info,
+                        const unsigned char* active, int mode, cudaStream_t st) {
+    for (int J = 0; J < T; ++J) {
+        if (launch_syrk_update(mat, Np, T, J, P, active, st)) return 1;
+        if (launch_diag_block(mat, Np, J, P, dinv, dinvT, T, info, active, mode, st)) return 1;
+        if (launch_trsm_panel(mat, Np, T, J, P, dinv, active, st)) return 1;
+    }
+    return 0;
+}
+
+// Blocked triangular inverse (phase 2), in place: L (with D_I already in the diagonal blocks) -> W = L^-1.
+static int inverse_phase(double* mat, int Np, int T, int P, const double* dinvT, double* mt,
+                         const unsigned char* active, cudaStream_t st) {
+    for (int J = T - 2; J >= 0; --J) {
+        if (launch_inv_panel(mat, Np, T, J, P, dinvT, mt, active, st)) return 1;
+        if (launch_inv_update(mat, Np, T, J, P, mt, active, st)) return 1;
+    }
+    return 0;
+}
+
+static bool bad_dims(const char* who, int N, int d, int S) {
+    if (N < 1 || d < 1 || d > MAX_D || S < 0 || S > MAX_S) {
+        set_error("%s: unsupported sizes N=%d d=%d S=%d (d<=%d, S<=%d)", who, N, d, S, MAX_D, MAX_S);
+        return true;
+    }
+    return false;
+}
+
+}  // namespace gpk
+
+using namespace gpk;
+
+extern "C" {
+
+int gpk_version(void) { return GPK_VERSION; }
+const char* gpk_last_error_string(void) { return g_err; }
+unsigned long long gpk_launch_count(void) { return g_launches.load(); }
+int gpk_padded_n(int N) { return round_up(N, NB); }
+
+int gpk_cov_batched(const double* X1, const double* X2, const double* e, const double* ls, int P, int N1, int N2,
+                    int d, double* K_out, long long ldk, long long strideK, void* stream) {
+    if (bad_dims("gpk_cov_batched", N1, d, 0) || N2 < 1 || P < 1) return 2;
+    return launch_cov_full(X1, X2, e, ls, P, N1, N2, d, K_out, ldk, strideK, (cudaStream_t)stream);
+}
+
+size_t gpk_potrf_workspace_bytes(int P, int Np) {
+    const size_t T = Np / NB;
+    return 2 * align256((size_t)P * T * NB * NB * 8);
+}
+
+int gpk_potrf_batched(double* K_inout, int P, int Np, int* info, void* workspace, size_t workspace_bytes,
+                      void* stream) {
+    if (Np < NB || Np % NB != 0 || P < 1) { set_error("gpk_potrf_batched: Np=%d must be a positive multiple of %d", Np, NB); return 2; }
+    if (workspace_bytes < gpk_potrf_workspace_bytes(P, Np)) { set_error("gpk_potrf_batched: workspace too small"); return 3; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const int T = Np / NB;
+    double* dinv = (double*)workspace;
+    double* dinvT = (double*)((char*)workspace + align256((size_t)P * T * NB * NB * 8));
+    if (cudaMemsetAsync(info, 0, (size_t)P * sizeof(int), st) != cudaSuccess) { set_error("memset info failed"); return 1; }
+    return factor_phase(K_inout, Np, T, P, dinv, dinvT, info, nullptr, DIAG_WRITE_FACTOR, st);
+}
+
+size_t gpk_loss_workspace_bytes(int P, int N, int d) {
+    if (N <= SMALL_N_MAX) return 256;
+    return blocked_layout(P, N, d).total;
+}
+
+int gpk_loss_batched(const double* X, const double* y, const double* e, const double* ls,
+                     const unsigned char* active, const double* sigma_vals, int P, int N, int d, int S,
+                     int* counts_out, int* info, double* resid_out, double* sig_out, void* workspace,
+                     size_t workspace_bytes, void* stream) {
+    if (bad_dims("gpk_loss_batched", N, d, S) || P < 1) return 2;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cudaMemsetAsync(info, 0, (size_t)P * sizeof(int), st) != cudaSuccess) { set_error("memset info failed"); return 1; }
+    if (N <= SMALL_N_MAX)
+        return launch_small_loss(X, y, e, ls, active, sigma_vals, P, N, d, S, counts_out, info, resid_out, sig_out, st);
+
+    // blocked path, in waves of as many particles as the workspace holds
+    const size_t per1 = blocked_layout(1, N, d).total;
+    if (workspace == nullptr || workspace_bytes < per1) { set_error("gpk_loss_batched: workspace too small (%zu < %zu)", workspace_bytes, per1); return 3; }
+    int Pw = P;
+    while (Pw > 1 && blocked_layout(Pw, N, d).total > workspace_bytes) Pw = (Pw * 7) / 8 < Pw ? (Pw * 7) / 8 : Pw - 1;
+    for (int p0 = 0; p0 < P; p0 += Pw) {
+        const int Pc = (P - p0 < Pw) ? (P - p0) : Pw;
+        const BlockedLayout L = blocked_layout(Pc, N, d);
+        char* ws = (char*)workspace;
+        double* mat = (double*)(ws + L.mat);
+        double* dinv = (double*)(ws + L.dinv);
+        double* dinvT = (double*)(ws + L.dinvT);
+        double* mt = (double*)(ws + L.mt);
+        double* xs = (double*)(ws + L.xs);
+        double* sq = (double*)(ws + L.sq);
+        double* cn = (double*)(ws + L.cn);
+        double* z = (double*)(ws + L.z);
+        double* alpha = (double*)(ws + L.alpha);
+        const unsigned char* act = active ? active + p0 : nullptr;
+        const double* lsp = ls + (size_t)p0 * d;
+        if (launch_scale_points(X, lsp, Pc, N, L.Np, d, xs, sq, act, st)) return 1;
+        if (launch_cov_lower(xs, sq, e, Pc, N, L.Np, d, mat, act, st)) return 1;
+        if (factor_phase(mat, L.Np, L.T, Pc, dinv, dinvT, info + p0, act, DIAG_WRITE_INVERSE, st)) return 1;
+        if (inverse_phase(mat, L.Np, L.T, Pc, dinvT, mt, act, st)) return 1;
+        if (launch_wy(mat, L.Np, N, Pc, y, z, act, st)) return 1;
+        if (launch_colnorm_alpha(mat, L.Np, Pc, z, cn, alpha, act, st)) return 1;
+        if (launch_counts(alpha, cn, e, sigma_vals, Pc, N, L.Np, S, counts_out + (size_t)p0 * S,
+                          resid_out ? resid_out + (size_t)p0 * N : nullptr,
+                          sig_out ? sig_out + (size_t)p0 * N : nullptr, act, st)) return 1;
+    }
+    return 0;
+}
+
+size_t gpk_fit_workspace_bytes(int N, int d) {
+    (void)d;
+    const size_t Np = round_up(N, NB), T = Np / NB;
+    return 2 * align256(T * NB * NB * 8) + align256(NB * Np * 8) + 2 * align256(Np * 8);
+}
+
+int gpk_fit(const double* X, const double* y, const double* e, const double* ls, int N, int d, double* W_out,
+            double* alpha_out, double* xs_out, double* sq_out, int* info, void* workspace, size_t workspace_bytes,
+            void* stream) {
+    if (bad_dims("gpk_fit", N, d, 0)) return 2;
+    if (workspace_bytes < gpk_fit_workspace_bytes(N, d)) { set_error("gpk_fit: workspace too small"); return 3; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const int Np = round_up(N, NB), T = Np / NB;
+    char* ws = (char*)workspace;
+    size_t off = 0;
+    double* dinv = (double*)(ws + off); off += align256((size_t)T * NB * NB * 8);
+    double* dinvT = (double*)(ws + off); off += align256((size_t)T * NB * NB * 8);
+    double* mt = (double*)(ws + off); off += align256((size_t)NB * Np * 8);
+    double* z = (double*)(ws + off); off += align256((size_t)Np * 8);
+    double* cn = (double*)(ws + off);
+    if (cudaMemsetAsync(info, 0, sizeof(int), st) != cudaSuccess) { set_error("memset info failed"); return 1; }
+    if (launch_scale_points(X, ls, 1, N, Np, d, xs_out, sq_out, nullptr, st)) return 1;
+    if (launch_cov_lower(xs_out, sq_out, e, 1, N, Np, d, W_out, nullptr, st)) return 1;
+    if (factor_phase(W_out, Np, T, 1, dinv, dinvT, info, nullptr, DIAG_WRITE_INVERSE, st)) return 1;
+    if (inverse_phase(W_out, Np, T, 1, dinvT, mt, nullptr, st)) return 1;
+    if (launch_wy(W_out, Np, N, 1, y, z, nullptr, st)) return 1;
+    if (launch_colnorm_alpha(W_out, Np, 1, z, cn, alpha_out, nullptr, st)) return 1;
+    return 0;
+}
+
+size_t gpk_predict_workspace_bytes(int N, int chunk) {
+    const size_t Np = round_up(N, NB), T = Np / NB, Bp = round_up(chunk, NB);
+    return align256(Bp * Np * 8) + align256(T * Bp * 8);
+}
+
+int gpk_predict(const double* W, const double* alpha, const double* xs, const double* sq, const double* ls, int N,
+                int d, const double* Xfit, long long M, double* mu_out, double* sd_out, int chunk, void* workspace,
+                size_t workspace_bytes, void* stream) {
+    if (bad_dims("gpk_predict", N, d, 0) || chunk < 1) return 2;
+    if (M <= 0) return 0;
+    if (workspace_bytes < gpk_predict_workspace_bytes(N, chunk)) { set_error("gpk_predict: workspace too small"); return 3; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const int Np = round_up(N, NB), T = Np / NB;
+    const int BpMax = round_up(chunk, NB);
+    double* KsT = (double*)workspace;
+    double* partial = (double*)((char*)workspace + align256((size_t)BpMax * Np * 8));
+    for (long long m0 = 0; m0 < M; m0 += chunk) {
+        const int B = (int)((M - m0 < chunk) ? (M - m0) : chunk);
+        const int Bp = round_up(B, NB);
+        if (launch_cross_cov(xs, sq, ls, alpha, N, Np, d, Xfit, M, m0, B, Bp, KsT, mu_out, st)) return 1;
+        if (launch_predict_gemm(W, Np, T, KsT, Bp, partial, st)) return 1;
+        if (launch_predict_finalize(partial, T, Bp, B, sd_out + m0, st)) return 1;
+    }
+    return 0;
+}
+
+int gpk_prob_surface(const double* table, long long R, int ncols, int npoints, double* y_out, double* p_out,
+                     int* valid_out, void* stream) {
+    if (npoints < 1) { set_error("gpk_prob_surface: npoints=%d", npoints); return 2; }
+    return launch_prob_surface(table, R, ncols, npoints, y_out, p_out, valid_out, (cudaStream_t)stream);
+}
+
+int gpk_sum_gaussians(const double* y, int n, const double* gaus, int ng, double half_dy, double* p_out,
+                      void* stream) {
+    return launch_sum_gaussians(y, n, gaus, ng, half_dy, p_out, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,86 @@
+// Shared declarations for libgpk (B200 / sm_100a GP-fitting hot path).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+
+namespace gpk {
+
+constexpr int NB = 128;           // tile edge of the blocked factorisation (doubles)
+constexpr int MAX_D = 8;          // kinematic dimensions supported by the kernels
+constexpr int MAX_S = 4096;       // sigma-scale grid points supported by the count kernels
+constexpr int SMALL_N_MAX = 128;  // one-CTA (shared-memory resident) loss path up to this N
+
+// ---- library state (gpk_api.cu) -------------------------------------------------------
+void set_error(const char* fmt, ...);
+void count_launch(int n = 1);
+int check_launch(const char* what);   // cudaGetLastError -> status; also counts the launch
+
+inline int round_up(int x, int m) { return (x + m - 1) / m * m; }
+
+// ---- workspace layout of the blocked loss / fit path ------------------------------------
+// All offsets in bytes, each section 256-byte aligned.
+struct BlockedLayout {
+    int P, N, Np, T, d;
+    size_t mat;      // [P][Np][Np]   K -> L -> W = L^-1 (lower block triangle)
+    size_t dinv;     // [P][T][NB][NB] inverse of each diagonal Cholesky block (zero upper)
+    size_t dinvT;    // [P][T][NB][NB] its transpose
+    size_t mt;       // [P][NB][Np]    phase-2 panel (L_KJ * D_J)^T
+    size_t xs;       // [P][d][Np]     x / l
+    size_t sq;       // [P][Np]        sum_d xs^2
+    size_t cn;       // [P][Np]        column sums of squares of W  (= diag K^-1)
+    size_t z;        // [P][Np]        W y
+    size_t alpha;    // [P][Np]        W^T z = K^-1 y
+    size_t total;
+};
+BlockedLayout blocked_layout(int P, int N, int d);
+
+// ---- kernels launchers (implemented across the .cu files) ---------------------------------
+// gpk_cov.cu
+int launch_scale_points(const double* X, const double* ls, int P, int N, int Np, int d,
+                        double* xs, double* sq, const unsigned char* active, cudaStream_t st);
+int launch_cov_lower(const double* xs, const double* sq, const double* e, int P, int N, int Np, int d,
+                     double* mat, const unsigned char* active, cudaStream_t st);
+int launch_cov_full(const double* X1, const double* X2, const double* e, const double* ls, int P,
+                    int N1, int N2, int d, double* K, long long ldk, long long strideK, cudaStream_t st);
+int launch_cross_cov(const double* xs, const double* sq, const double* ls, const double* alpha, int N, int Np,
+                     int d, const double* Xfit, long long M, long long m0, int B, int Bp, double* KsT,
+                     double* mu_out, cudaStream_t st);
+
+// gpk_diag.cu
+enum DiagMode { DIAG_WRITE_INVERSE = 0, DIAG_WRITE_FACTOR = 1 };
+int launch_diag_block(double* mat, int Np, int J, int P, double* dinv, double* dinvT, int T,
+                      int* info, const unsigned char* active, int mode, cudaStream_t st);
+
+// gpk_gemm.cu
+int launch_syrk_update(double* mat, int Np, int T, int J, int P, const unsigned char* active, cudaStream_t st);
+int launch_trsm_panel(double* mat, int Np, int T, int J, int P, const double* dinv,
+                      const unsigned char* active, cudaStream_t st);
+int launch_inv_panel(const double* mat, int Np, int T, int J, int P, const double* dinvT, double* mt,
+                     const unsigned char* active, cudaStream_t st);
+int launch_inv_update(double* mat, int Np, int T, int J, int P, const double* mt,
+                      const unsigned char* active, cudaStream_t st);
+int launch_predict_gemm(const double* W, int Np, int T, const double* KsT, int Bp, double* partial,
+                        cudaStream_t st);
+
+// gpk_loss.cu
+int launch_small_loss(const double* X, const double* y, const double* e, const double* ls,
+                      const unsigned char* active, const double* sigma_vals, int P, int N, int d, int S,
+                      int* counts, int* info, double* resid_out, double* sig_out, cudaStream_t st);
+int launch_wy(const double* mat, int Np, int N, int P, const double* y, double* z,
+              const unsigned char* active, cudaStream_t st);
+int launch_colnorm_alpha(const double* mat, int Np, int P, const double* z, double* cn, double* alpha,
+                         const unsigned char* active, cudaStream_t st);
+int launch_counts(const double* alpha, const double* cn, const double* e, const double* sigma_vals,
+                  int P, int N, int Np, int S, int* counts, double* resid_out, double* sig_out,
+                  const unsigned char* active, cudaStream_t st);
+int launch_predict_finalize(const double* partial, int T, int Bp, int B, double* sigma_out, cudaStream_t st);
+
+// gpk_surface.cu
+int launch_prob_surface(const double* table, long long R, int ncols, int npoints,
+                        double* y_out, double* p_out, int* valid_out, cudaStream_t st);
+
+int launch_sum_gaussians(const double* y, int n, const double* gaus, int ng, double half_dy, double* p_out,
+                         cudaStream_t st);
+
+}  // namespace gpk

@@ -1,0 +1,291 @@
+// Kernel (b), loss part: self-prediction at the training points and the count reduction of the
+// calibration loss (find_len_scales.py:159-163), plus the one-CTA small-N path that fuses everything.
+//
+// With D = diag(e^2), K = k(X,X) + D and K_s = K - D (GP_func.py:21,32 with x_fit = x_known):
+//     mu - y        = K_s alpha - y            = -D alpha                (alpha = K^-1 y)
+//     var_i         = 1 - k_i^T K^-1 k_i       = d_i - d_i^2 (K^-1)_ii
+//     (K^-1)_ii     = sum_k W_ki^2,  W = L^-1  (column sums of squares of the triangular inverse)
+// so the N x N right-hand-side solve of GP_func.py:38 reduces to the triangular inverse (N^3/3 flop).
+//
+// Counts: |pull| <= 1 with pull = r / max(sd * s, 1e-12) (find_len_scales.py:161-163) is, for IEEE
+// division, exactly |r| <= max(fl(sd * s), 1e-12); the predicate is monotone in s, so each point
+// contributes to all scales from its first passing index on: histogram of first indices + prefix sum.
+#include "gpk_cholinv.cuh"
+
+namespace gpk {
+
+// first index k in [0, S) with  a <= max(fl(sd * s_k), 1e-12);  S if none
+__device__ __forceinline__ int first_inside(double a, double sd, const double* __restrict__ sv, int S) {
+    int lo = 0, hi = S;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        const double thr = fmax(__dmul_rn(sd, sv[mid]), 1e-12);
+        if (a <= thr) hi = mid; else lo = mid + 1;
+    }
+    return lo;
+}
+
+// hist[0..S] (int, shared) -> counts_out[0..S) inclusive prefix; called by all threads after a barrier
+__device__ __forceinline__ void prefix_and_store(int* hist, int S, int* __restrict__ counts_out) {
+    const int tid = threadIdx.x;
+    if (tid < 32) {
+        const int chunk = (S + 31) / 32;
+        const int b = tid * chunk, e = min(S, b + chunk);
+        int s = 0;
+        for (int k = b; k < e; ++k) s += hist[k];
+        int incl = s;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (tid >= o) incl += v;
+        }
+        int run = incl - s;
+        for (int k = b; k < e; ++k) { run += hist[k]; hist[k] = run; }
+    }
+    __syncthreads();
+    for (int k = tid; k < S; k += blockDim.x) counts_out[k] = hist[k];
+}
+
+__device__ __forceinline__ void resid_sigma(double d, double alpha, double cn, double& resid, double& sd) {
+    resid = -(d * alpha);
+    const double var = fma(-(d * cn), d, d);
+    sd = sqrt(fmax(var, 1e-12));                  // np.clip(var, 1e-12, None); sqrt   GP_func.py:39-40
+}
+
+// ---------------------------------------------------------------------------------------------
+// Small-N fused loss: covariance, Cholesky, inverse, alpha, counts -- one CTA per particle, all in
+// shared memory (the reference's real PSO size: N <= 100 after the KMeans cap, find_len_scales.py:24-47).
+struct SmallSmem {
+    static constexpr size_t lm = 0;
+    static constexpr size_t col = lm + (size_t)NB * CI_LD * 8;
+    static constexpr size_t xr = col + NB * 8;
+    static constexpr size_t xs = xr + NB * 8;
+    static constexpr size_t sq = xs + (size_t)MAX_D * NB * 8;
+    static constexpr size_t y = sq + NB * 8;
+    static constexpr size_t d = y + NB * 8;
+    static constexpr size_t z = d + NB * 8;
+    static constexpr size_t a = z + NB * 8;
+    static constexpr size_t sg = a + NB * 8;
+    static constexpr size_t hist = sg + NB * 8;
+    static constexpr size_t total = hist + (size_t)(MAX_S + 1) * 4;
+};
+
+__global__ void __launch_bounds__(256, 1)
+k_small_loss(const double* __restrict__ X, const double* __restrict__ y, const double* __restrict__ e,
+             const double* __restrict__ ls, const unsigned char* __restrict__ active,
+             const double* __restrict__ sigma_vals, int N, int d, int S, int* __restrict__ counts,
+             int* __restrict__ info, double* __restrict__ resid_out, double* __restrict__ sig_out) {
+    extern __shared__ __align__(16) unsigned char raw[];
+    double* Lm = reinterpret_cast<double*>(raw + SmallSmem::lm);
+    double* col = reinterpret_cast<double*>(raw + SmallSmem::col);
+    double* xr = reinterpret_cast<double*>(raw + SmallSmem::xr);
+    double (*xs)[NB] = reinterpret_cast<double (*)[NB]>(raw + SmallSmem::xs);
+    double* sq = reinterpret_cast<double*>(raw + SmallSmem::sq);
+    double* yv = reinterpret_cast<double*>(raw + SmallSmem::y);
+    double* dv = reinterpret_cast<double*>(raw + SmallSmem::d);
+    double* zv = reinterpret_cast<double*>(raw + SmallSmem::z);
+    double* av = reinterpret_cast<double*>(raw + SmallSmem::a);
+    double* sg = reinterpret_cast<double*>(raw + SmallSmem::sg);
+    int* hist = reinterpret_cast<int*>(raw + SmallSmem::hist);
+
+    const int p = blockIdx.x;
+    const int tid = threadIdx.x;
+    if (active && !active[p]) {
+        for (int k = tid; k < S; k += 256) counts[(size_t)p * S + k] = 0;
+        return;
+    }
+    if (tid < N) {
+        double acc = 0.0;
+        for (int dd = 0; dd < d; ++dd) {
+            const double v = __ddiv_rn(X[(size_t)dd * N + tid], ls[(size_t)p * d + dd]);
+            xs[dd][tid] = v;
+            const double v2 = __dmul_rn(v, v);
+            acc = (dd == 0) ? v2 : __dadd_rn(acc, v2);
+        }
+        sq[tid] = acc;
+        yv[tid] = y[tid];
+        const double ee = e[tid];
+        dv[tid] = __dmul_rn(ee, ee);
+    }
+    for (int k = tid; k <= S; k += 256) hist[k] = 0;
+    __syncthreads();
+
+    // K + diag(e^2) into the lower triangle; identity into the X part
+    for (int idx = tid; idx < N * N; idx += 256) {
+        const int r = idx / N, c = idx - r * N;
+        if (c <= r) {
+            double dot = __dmul_rn(xs[0][r], xs[0][c]);
+            for (int dd = 1; dd < d; ++dd) dot = fma(xs[dd][r], xs[dd][c], dot);
+            double s = __dsub_rn(__dadd_rn(sq[r], sq[c]), __dmul_rn(2.0, dot));
+            s = fmax(s, 0.0);
+            double v = exp(__dmul_rn(-0.5, s));
+            if (r == c) v = __dadd_rn(v, dv[r]);
+            Lm[r * CI_LD + c] = v;
+        } else {
+            Lm[r * CI_LD + c + 1] = 0.0;
+        }
+    }
+    if (tid < N) Lm[tid * CI_LD + tid + 1] = 1.0;
+    __syncthreads();
+
+    const int bad = chol_inv_inplace(Lm, N, col, xr);
+    if (bad && tid == 0) info[p] = bad;
+
+    // z = W y  (W[k][c] = Lm[c][k+1])
+    if (tid < N) {
+        const int k = tid;
+        double acc = 0.0;
+        for (int c = 0; c <= k; ++c) acc = fma(Lm[c * CI_LD + k + 1], yv[c], acc);
+        zv[k] = acc;
+    }
+    __syncthreads();
+    if (tid < N) {
+        const int i = tid;
+        double cn = 0.0, al = 0.0;
+        const double* row = Lm + i * CI_LD + 1;
+        for (int k = i; k < N; ++k) {
+            const double w = row[k];
+            cn = fma(w, w, cn);
+            al = fma(w, zv[k], al);
+        }
+        double resid, sd;
+        resid_sigma(dv[i], al, cn, resid, sd);
+        av[i] = fabs(resid);
+        sg[i] = sd;
+        if (resid_out) resid_out[(size_t)p * N + i] = resid;
+        if (sig_out) sig_out[(size_t)p * N + i] = sd;
+        const int k0 = first_inside(av[i], sd, sigma_vals, S);
+        atomicAdd(&hist[k0], 1);
+    }
+    __syncthreads();
+    prefix_and_store(hist, S, counts + (size_t)p * S);
+}
+
+int launch_small_loss(const double* X, const double* y, const double* e, const double* ls,
+                      const unsigned char* active, const double* sigma_vals, int P, int N, int d, int S,
+                      int* counts, int* info, double* resid_out, double* sig_out, cudaStream_t st) {
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t er = cudaFuncSetAttribute(k_small_loss, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)SmallSmem::total);
+        if (er != cudaSuccess) { set_error("k_small_loss smem attr: %s", cudaGetErrorString(er)); return 1; }
+        configured = true;
+    }
+    k_small_loss<<<P, 256, SmallSmem::total, st>>>(X, y, e, ls, active, sigma_vals, N, d, S, counts, info,
+                                                   resid_out, sig_out);
+    return check_launch("k_small_loss");
+}
+
+// ---------------------------------------------------------------------------------------------
+// z = W y : one warp per row, W lower block-triangular with zero upper parts in the diagonal blocks.
+__global__ void __launch_bounds__(256) k_wy(const double* __restrict__ mat, int Np, int N,
+                                            const double* __restrict__ y, double* __restrict__ z,
+                                            const unsigned char* __restrict__ active) {
+    const int p = blockIdx.y;
+    if (active && !active[p]) return;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int k = blockIdx.x * 8 + warp;
+    if (k >= Np) return;
+    const double* row = mat + (size_t)p * Np * Np + (size_t)k * Np;
+    const int cend = min(k, N - 1);
+    double acc = 0.0;
+    for (int c = lane; c <= cend; c += 32) acc = fma(row[c], y[c], acc);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) z[(size_t)p * Np + k] = acc;
+}
+
+int launch_wy(const double* mat, int Np, int N, int P, const double* y, double* z, const unsigned char* active,
+              cudaStream_t st) {
+    k_wy<<<dim3(Np / 8, P), 256, 0, st>>>(mat, Np, N, y, z, active);
+    return check_launch("k_wy");
+}
+
+// cn_i = sum_{k>=i} W[k][i]^2,  alpha_i = sum_{k>=i} W[k][i] z_k : 32 columns per CTA, 8 warps sweep rows.
+__global__ void __launch_bounds__(256) k_colnorm_alpha(const double* __restrict__ mat, int Np,
+                                                       const double* __restrict__ z, double* __restrict__ cn,
+                                                       double* __restrict__ alpha,
+                                                       const unsigned char* __restrict__ active) {
+    const int p = blockIdx.y;
+    if (active && !active[p]) return;
+    __shared__ double s_cn[8][32], s_al[8][32];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int i = blockIdx.x * 32 + lane;
+    const int kstart = (blockIdx.x * 32 / NB) * NB;       // first row of the diagonal block
+    const double* M = mat + (size_t)p * Np * Np;
+    const double* zp = z + (size_t)p * Np;
+    double a = 0.0, b = 0.0;
+    for (int k = kstart + warp; k < Np; k += 8) {
+        const double w = M[(size_t)k * Np + i];
+        a = fma(w, w, a);
+        b = fma(w, zp[k], b);
+    }
+    s_cn[warp][lane] = a;
+    s_al[warp][lane] = b;
+    __syncthreads();
+    if (warp == 0) {
+        double ta = 0.0, tb = 0.0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) { ta += s_cn[w][lane]; tb += s_al[w][lane]; }
+        cn[(size_t)p * Np + i] = ta;
+        alpha[(size_t)p * Np + i] = tb;
+    }
+}
+
+int launch_colnorm_alpha(const double* mat, int Np, int P, const double* z, double* cn, double* alpha,
+                         const unsigned char* active, cudaStream_t st) {
+    k_colnorm_alpha<<<dim3(Np / 32, P), 256, 0, st>>>(mat, Np, z, cn, alpha, active);
+    return check_launch("k_colnorm_alpha");
+}
+
+// counts[p][s] from alpha / cn: one CTA per particle.
+__global__ void __launch_bounds__(256) k_counts(const double* __restrict__ alpha, const double* __restrict__ cn,
+                                                const double* __restrict__ e, const double* __restrict__ sigma_vals,
+                                                int N, int Np, int S, int* __restrict__ counts,
+                                                double* __restrict__ resid_out, double* __restrict__ sig_out,
+                                                const unsigned char* __restrict__ active) {
+    __shared__ int hist[MAX_S + 1];
+    const int p = blockIdx.x;
+    const int tid = threadIdx.x;
+    if (active && !active[p]) {
+        for (int k = tid; k < S; k += 256) counts[(size_t)p * S + k] = 0;
+        return;
+    }
+    for (int k = tid; k <= S; k += 256) hist[k] = 0;
+    __syncthreads();
+    for (int i = tid; i < N; i += 256) {
+        const double ee = e[i];
+        const double d = __dmul_rn(ee, ee);
+        double resid, sd;
+        resid_sigma(d, alpha[(size_t)p * Np + i], cn[(size_t)p * Np + i], resid, sd);
+        if (resid_out) resid_out[(size_t)p * N + i] = resid;
+        if (sig_out) sig_out[(size_t)p * N + i] = sd;
+        atomicAdd(&hist[first_inside(fabs(resid), sd, sigma_vals, S)], 1);
+    }
+    __syncthreads();
+    prefix_and_store(hist, S, counts + (size_t)p * S);
+}
+
+int launch_counts(const double* alpha, const double* cn, const double* e, const double* sigma_vals, int P, int N,
+                  int Np, int S, int* counts, double* resid_out, double* sig_out, const unsigned char* active,
+                  cudaStream_t st) {
+    k_counts<<<P, 256, 0, st>>>(alpha, cn, e, sigma_vals, N, Np, S, counts, resid_out, sig_out, active);
+    return check_launch("k_counts");
+}
+
+// sigma_b = sqrt(clip(1 - sum_I partial[I][b], 1e-12))     GP_func.py:34,39-40
+__global__ void k_predict_finalize(const double* __restrict__ partial, int T, int Bp, int B,
+                                   double* __restrict__ sigma_out) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    double s = 0.0;
+    for (int I = 0; I < T; ++I) s += partial[(size_t)I * Bp + b];
+    sigma_out[b] = sqrt(fmax(1.0 - s, 1e-12));
+}
+
+int launch_predict_finalize(const double* partial, int T, int Bp, int B, double* sigma_out, cudaStream_t st) {
+    k_predict_finalize<<<(B + 255) / 256, 256, 0, st>>>(partial, T, Bp, B, sigma_out);
+    return check_launch("k_predict_finalize");
+}
+
+}  // namespace gpk

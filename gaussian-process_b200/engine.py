@@ -1,0 +1,258 @@
+"""Host-side engine: NumPy in / NumPy out wrappers around libgpk.  PyTorch supplies device
+memory, the current CUDA stream and pinned staging only -- every computation is a libgpk kernel.
+
+Reference functions served (file:line in rferguson22/Gaussian-Process):
+  cov_batched      kernel_func            GP_func.py:49-65 (+ :21 diagonal)
+  LossContext      wass_loss -> counts    find_len_scales.py:154-163
+  GPFit / gp       GP                     GP_func.py:12-45
+  prob_surface     generate_prob_surf     calc_prob_surf.py:67-81
+"""
+import os
+
+import numpy as np
+import torch
+
+from . import _lib
+
+NB = 128
+DEFAULT_CHUNK = 4096          # grid points per predict pass (K_* tile of Np x chunk doubles stays in L2)
+
+
+def device():
+    if not torch.cuda.is_available():
+        raise RuntimeError("gaussian-process_b200 needs a CUDA device (B200); there is no CPU fallback")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def to_dev(a, dtype=None):
+    t = torch.from_numpy(np.ascontiguousarray(a))
+    if dtype is not None:
+        t = t.to(dtype)
+    return t.to(device(), non_blocking=False)
+
+
+_ws_cache = {}
+
+
+def workspace(nbytes, tag="main"):
+    """Grow-only scratch buffer per (device, tag)."""
+    key = (torch.cuda.current_device(), tag)
+    buf = _ws_cache.get(key)
+    if buf is None or buf.numel() < nbytes:
+        _ws_cache.pop(key, None)
+        buf = None
+        torch.cuda.empty_cache()
+        buf = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device())
+        _ws_cache[key] = buf
+    return buf
+
+
+def release_workspaces():
+    _ws_cache.clear()
+    torch.cuda.empty_cache()
+
+
+def free_bytes():
+    free, _total = torch.cuda.mem_get_info()
+    return int(free)
+
+
+# ------------------------------------------------------------------------------------ (a)
+def cov_batched(x1, x2, ls, e=None):
+    """K[p] = kernel_func(x1, x2, ls[p]) (+ diag(e^2) if e is given).  x1 (d,N1), x2 (d,N2), ls (P,d)."""
+    lib = _lib.load()
+    x1, x2 = _f64(x1), _f64(x2)
+    ls = np.atleast_2d(_f64(ls))
+    d, n1 = x1.shape
+    n2 = x2.shape[1]
+    p = ls.shape[0]
+    dx1, dx2, dls = to_dev(x1), to_dev(x2), to_dev(ls)
+    de = to_dev(_f64(e)) if e is not None else None
+    out = torch.empty((p, n1, n2), dtype=torch.float64, device=device())
+    st = lib.gpk_cov_batched(dx1.data_ptr(), dx2.data_ptr(), de.data_ptr() if de is not None else None,
+                             dls.data_ptr(), p, n1, n2, d, out.data_ptr(), n2, n1 * n2, _stream())
+    _lib.check(st, "gpk_cov_batched")
+    return out.cpu().numpy()
+
+
+def potrf_batched(k):
+    """Lower Cholesky factors of a batch (P,Np,Np), Np a multiple of 128.  Returns (L, info)."""
+    lib = _lib.load()
+    k = _f64(k)
+    p, n, _ = k.shape
+    dk = to_dev(k)
+    info = torch.zeros(p, dtype=torch.int32, device=device())
+    ws = workspace(lib.gpk_potrf_workspace_bytes(p, n), "potrf")
+    st = lib.gpk_potrf_batched(dk.data_ptr(), p, n, info.data_ptr(), ws.data_ptr(), ws.numel(), _stream())
+    _lib.check(st, "gpk_potrf_batched")
+    return np.tril(dk.cpu().numpy()), info.cpu().numpy()
+
+
+# ------------------------------------------------------------------------------------ (b)
+class LossContext:
+    """Device-resident training set + sigma grid for repeated swarm evaluations (one per PSO
+    iteration).  Only the (P,d) positions go up and the (P,S) int32 counts come down per call."""
+
+    def __init__(self, x, y, e, sigma_vals, max_particles=None, mem_fraction=0.85):
+        self.lib = _lib.load()
+        x, y, e, sigma_vals = _f64(x), _f64(y), _f64(e), _f64(sigma_vals)
+        self.d, self.n = x.shape
+        self.s = sigma_vals.shape[0]
+        self.x, self.y, self.e, self.sig = to_dev(x), to_dev(y), to_dev(e), to_dev(sigma_vals)
+        self.mem_fraction = mem_fraction
+        self._pin_pos = None
+        self._pin_counts = None
+
+    def _ws(self, p):
+        need = self.lib.gpk_loss_workspace_bytes(p, self.n, self.d)
+        have = _ws_cache.get((torch.cuda.current_device(), "loss"))
+        if have is not None and have.numel() >= need:
+            return have
+        one = self.lib.gpk_loss_workspace_bytes(1, self.n, self.d)
+        budget = int((free_bytes() + (have.numel() if have is not None else 0)) * self.mem_fraction)
+        if need > budget:                      # libgpk runs the swarm in waves inside this much memory
+            need = max(one, budget // one * one)
+        return workspace(need, "loss")
+
+    def counts_device(self, positions_dev, active_dev, p, want_detail=False):
+        """All inputs already on the device; returns device tensors (counts, info[, resid, sd])."""
+        dev = device()
+        counts = torch.empty((p, self.s), dtype=torch.int32, device=dev)
+        info = torch.empty(p, dtype=torch.int32, device=dev)
+        resid = torch.empty((p, self.n), dtype=torch.float64, device=dev) if want_detail else None
+        sd = torch.empty((p, self.n), dtype=torch.float64, device=dev) if want_detail else None
+        ws = self._ws(p)
+        st = self.lib.gpk_loss_batched(
+            self.x.data_ptr(), self.y.data_ptr(), self.e.data_ptr(), positions_dev.data_ptr(),
+            active_dev.data_ptr() if active_dev is not None else None, self.sig.data_ptr(), p, self.n, self.d,
+            self.s, counts.data_ptr(), info.data_ptr(), resid.data_ptr() if want_detail else None,
+            sd.data_ptr() if want_detail else None, ws.data_ptr(), ws.numel(), _stream())
+        _lib.check(st, "gpk_loss_batched")
+        return (counts, info, resid, sd) if want_detail else (counts, info)
+
+    def counts(self, positions, active=None, want_detail=False):
+        """positions (P,d) host -> counts (P,S) int32 host (+ info, optional resid/sd)."""
+        positions = np.atleast_2d(_f64(positions))
+        p = positions.shape[0]
+        if self._pin_pos is None or self._pin_pos.shape[0] != p:
+            self._pin_pos = torch.empty((p, self.d), dtype=torch.float64).pin_memory()
+            self._pin_act = torch.empty(p, dtype=torch.uint8).pin_memory()
+            self._pin_counts = torch.empty((p, self.s), dtype=torch.int32).pin_memory()
+            self._pin_info = torch.empty(p, dtype=torch.int32).pin_memory()
+        self._pin_pos.numpy()[...] = positions
+        self._pin_act.numpy()[...] = 1 if active is None else np.asarray(active, dtype=np.uint8)
+        dpos = self._pin_pos.to(device(), non_blocking=True)
+        dact = self._pin_act.to(device(), non_blocking=True)
+        out = self.counts_device(dpos, dact, p, want_detail)
+        self._pin_counts.copy_(out[0], non_blocking=True)
+        self._pin_info.copy_(out[1], non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        res = [self._pin_counts.numpy().copy(), self._pin_info.numpy().copy()]
+        if want_detail:
+            res += [out[2].cpu().numpy(), out[3].cpu().numpy()]
+        return tuple(res)
+
+
+# ------------------------------------------------------------------------------------ (b)+(c)
+class GPFit:
+    """Cached fit state (W = L^-1, alpha, scaled points) on the device.  GP_func.py:21-24."""
+
+    def __init__(self, x, y, e, ls):
+        self.lib = lib = _lib.load()
+        x, y, e, ls = _f64(x), _f64(y), _f64(e), _f64(ls).reshape(-1)
+        self.d, self.n = x.shape
+        if ls.shape[0] != self.d:
+            raise ValueError(f"lengths has {ls.shape[0]} entries, x_known has {self.d} dimensions")
+        self.np_ = lib.gpk_padded_n(self.n)
+        dev = device()
+        dx, dy, de = to_dev(x), to_dev(y), to_dev(e)
+        self.ls = to_dev(ls)
+        self.W = torch.empty((self.np_, self.np_), dtype=torch.float64, device=dev)
+        self.alpha = torch.empty(self.np_, dtype=torch.float64, device=dev)
+        self.xs = torch.empty((self.d, self.np_), dtype=torch.float64, device=dev)
+        self.sq = torch.empty(self.np_, dtype=torch.float64, device=dev)
+        info = torch.zeros(1, dtype=torch.int32, device=dev)
+        ws = workspace(lib.gpk_fit_workspace_bytes(self.n, self.d), "fit")
+        st = lib.gpk_fit(dx.data_ptr(), dy.data_ptr(), de.data_ptr(), self.ls.data_ptr(), self.n, self.d,
+                         self.W.data_ptr(), self.alpha.data_ptr(), self.xs.data_ptr(), self.sq.data_ptr(),
+                         info.data_ptr(), ws.data_ptr(), ws.numel(), _stream())
+        _lib.check(st, "gpk_fit")
+        if int(info.item()) != 0:
+            # numpy.linalg.cholesky's behaviour at GP_func.py:22
+            raise np.linalg.LinAlgError("Matrix is not positive definite")
+
+    def predict_device(self, xfit_dev, m, chunk=DEFAULT_CHUNK):
+        dev = device()
+        mu = torch.empty(m, dtype=torch.float64, device=dev)
+        sd = torch.empty(m, dtype=torch.float64, device=dev)
+        chunk = int(max(NB, min(chunk, -(-m // NB) * NB)))
+        ws = workspace(self.lib.gpk_predict_workspace_bytes(self.n, chunk), "predict")
+        st = self.lib.gpk_predict(self.W.data_ptr(), self.alpha.data_ptr(), self.xs.data_ptr(), self.sq.data_ptr(),
+                                  self.ls.data_ptr(), self.n, self.d, xfit_dev.data_ptr(), m, mu.data_ptr(),
+                                  sd.data_ptr(), chunk, ws.data_ptr(), ws.numel(), _stream())
+        _lib.check(st, "gpk_predict")
+        return mu, sd
+
+    def predict(self, x_fit, chunk=DEFAULT_CHUNK):
+        """x_fit (d,M) host -> (mu (M,), sd (M,)) host float64.  GP_func.py:26-45."""
+        x_fit = _f64(x_fit)
+        if x_fit.shape[0] != self.d:
+            raise ValueError(f"x_fit has {x_fit.shape[0]} dimensions, expected {self.d}")
+        m = x_fit.shape[1]
+        if m == 0:
+            return np.zeros(0), np.zeros(0)
+        mu, sd = self.predict_device(to_dev(x_fit), m, chunk)
+        return mu.cpu().numpy(), sd.cpu().numpy()
+
+
+def gp(x_known, y_known, e_known, x_fit, lengths, batch_size=10000):
+    """GP(x_known, y_known, e_known, x_fit, lengths, batch_size).  `batch_size` only bounded host memory
+    in the reference (GP_func.py:28-31); results do not depend on it and it is ignored here."""
+    return GPFit(x_known, y_known, e_known, lengths).predict(x_fit)
+
+
+# ------------------------------------------------------------------------------------ (d)
+def prob_surface(table, points=100, rows_per_pass=None):
+    """table (R, 2E) host payload -> (row_index[Rv], y[Rv,points], p[Rv,points]) of the emitting rows."""
+    lib = _lib.load()
+    table = _f64(table)
+    r, ncols = table.shape
+    if r == 0 or ncols == 0:
+        return np.zeros(0, dtype=np.int64), np.zeros((0, points)), np.zeros((0, points))
+    if rows_per_pass is None:
+        rows_per_pass = max(1, min(r, (1 << 28) // (points * 16)))
+    idx_parts, y_parts, p_parts = [], [], []
+    dev = device()
+    for r0 in range(0, r, rows_per_pass):
+        rc = min(rows_per_pass, r - r0)
+        dt = to_dev(table[r0:r0 + rc])
+        y = torch.empty((rc, points), dtype=torch.float64, device=dev)
+        p = torch.empty((rc, points), dtype=torch.float64, device=dev)
+        valid = torch.empty(rc, dtype=torch.int32, device=dev)
+        st = lib.gpk_prob_surface(dt.data_ptr(), rc, ncols, points, y.data_ptr(), p.data_ptr(), valid.data_ptr(),
+                                  _stream())
+        _lib.check(st, "gpk_prob_surface")
+        keep = torch.nonzero(valid, as_tuple=False).reshape(-1)
+        idx_parts.append(keep.cpu().numpy() + r0)
+        y_parts.append(y.index_select(0, keep).cpu().numpy())
+        p_parts.append(p.index_select(0, keep).cpu().numpy())
+    return np.concatenate(idx_parts), np.concatenate(y_parts), np.concatenate(p_parts)
+
+
+def sum_gaussians(y, gaus, half_dy):
+    lib = _lib.load()
+    y, gaus = _f64(y), _f64(gaus)
+    dy_, dg = to_dev(y), to_dev(gaus)
+    out = torch.empty(y.shape[0], dtype=torch.float64, device=device())
+    st = lib.gpk_sum_gaussians(dy_.data_ptr(), y.shape[0], dg.data_ptr(), gaus.shape[0], float(half_dy),
+                               out.data_ptr(), _stream())
+    _lib.check(st, "gpk_sum_gaussians")
+    return out.cpu().numpy()

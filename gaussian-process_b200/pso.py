@@ -1,0 +1,201 @@
+"""Length-scale optimiser: host side of find_len_scales.py on top of the batched GPU loss.
+
+The particle-swarm state update stays in NumPy with the reference's expression order and RNG call
+order (find_len_scales.py:88-100,123-141) so that a seeded run reproduces the reference trajectory;
+what the reference fans out over a fork pool (`executor.map(evaluate_loss_helper, ...)`, :77,:103,:134)
+is one `gpk_loss_batched` launch per swarm evaluation.  The GPU returns the integer count matrix and
+the host finishes :163-177 with the same NumPy expressions, so the score is bit-identical whenever
+the counts are."""
+import numpy as np
+from scipy.stats import norm
+
+from . import engine, lhs as _lhs, sharding
+
+N_SIGMA = 1000
+OOB_SCORE = 1e13
+
+
+def sigma_to_percent(x):
+    """Fraction of a normal distribution within x standard deviations.  find_len_scales.py:192-201."""
+    return norm.cdf(x) - norm.cdf(-x)
+
+
+def sigma_grid():
+    sigma_vals = np.linspace(0.001, 3, N_SIGMA)           # find_len_scales.py:66
+    return sigma_vals, sigma_to_percent(sigma_vals)        # :67
+
+
+def out_of_bounds_mask(positions, lower, upper):
+    """True where a particle touches or leaves the box (find_len_scales.py:156: <= / >=)."""
+    positions = np.atleast_2d(positions)
+    return np.any(positions <= lower, axis=1) | np.any(positions >= upper, axis=1)
+
+
+def finish_losses(counts, n_points, positions, sigma_vals, expected, lower, upper, oob):
+    """counts (P,S) -> PSO scores (P,), the arithmetic of find_len_scales.py:163-177 and the sign
+    flip of :182, vectorised over particles (row-wise identical to the scalar expressions)."""
+    positions = np.atleast_2d(positions)
+    measured = counts.astype(np.float64) / n_points                       # np.mean(bool, axis=0)
+    diff = np.abs(measured - expected[None, :])
+    wasserstein = np.trapz(diff, sigma_vals, axis=1)
+    span = upper - lower
+    with np.errstate(invalid="ignore", divide="ignore"):     # degenerate (zero-range) dims are always out of bounds
+        d_lo = (positions - lower) / span
+        d_hi = (upper - positions) / span
+        d_min = np.min(np.minimum(d_lo, d_hi), axis=1)
+        proximity = np.clip(1 - 2 * d_min, 0.0, 1.0)
+    scores = -(-wasserstein - (0.01 * proximity))
+    return np.where(oob, OOB_SCORE, scores)
+
+
+class SwarmLoss:
+    """evaluate_loss for a whole swarm.  Holds the device-resident training set."""
+
+    def __init__(self, x_known, y_known, e_known, sigma_vals, expected_percents, lower_bounds, upper_bounds):
+        self.ctx = engine.LossContext(x_known, y_known, e_known, sigma_vals)
+        self.n = np.asarray(x_known).shape[1]
+        self.sigma_vals = np.asarray(sigma_vals, dtype=np.float64)
+        self.expected = np.asarray(expected_percents, dtype=np.float64)
+        self.lower = np.asarray(lower_bounds, dtype=np.float64)
+        self.upper = np.asarray(upper_bounds, dtype=np.float64)
+        self.evaluations = 0
+
+    def __call__(self, positions):
+        positions = np.atleast_2d(np.asarray(positions, dtype=np.float64))
+        oob = out_of_bounds_mask(positions, self.lower, self.upper)
+        if np.all(oob):
+            return np.full(positions.shape[0], OOB_SCORE)
+        counts, info = self.ctx.counts(positions, active=~oob)
+        if np.any(info != 0):
+            raise np.linalg.LinAlgError("Matrix is not positive definite")   # GP_func.py:22 behaviour
+        self.evaluations += positions.shape[0]
+        return finish_losses(counts, self.n, positions, self.sigma_vals, self.expected, self.lower, self.upper, oob)
+
+
+def evaluate_loss_batch(positions, x_known, y_known, e_known, sigma_vals, expected_percents, lower_bounds,
+                        upper_bounds):
+    """Batched evaluate_loss: positions (P,d) -> (P,) float64 scores."""
+    return SwarmLoss(x_known, y_known, e_known, sigma_vals, expected_percents, lower_bounds, upper_bounds)(positions)
+
+
+def kmeans_subsample(x_known, y_known, e_known, max_points):
+    """Host-side KMeans cap of find_len_scales.py:25-47 (sklearn, random_state=0)."""
+    from sklearn.cluster import KMeans
+    pts = x_known.T
+    km = KMeans(n_clusters=max_points, n_init='auto', random_state=0)
+    labels = km.fit_predict(pts)
+    chosen = []
+    for k in range(max_points):
+        members = np.where(labels == k)[0]
+        if len(members) == 0:
+            continue
+        dist2 = np.sum((pts[members] - km.cluster_centers_[k]) ** 2, axis=1)
+        chosen.append(members[np.argmin(dist2)])
+    chosen = np.array(chosen)
+    return x_known[:, chosen], y_known[chosen], e_known[chosen]
+
+
+def swarm_bounds(x_known):
+    """find_len_scales.py:56-64: lower = smallest positive coordinate gap, upper = coordinate range."""
+    upper = np.max(x_known, axis=1) - np.min(x_known, axis=1)
+    gaps = [np.diff(np.unique(row)) for row in x_known]
+    lower = np.array([np.min(g[g > 0]) if np.any(g > 0) else 0 for g in gaps])
+    return lower, upper
+
+
+def len_scale_opt(x_known, y_known, e_known, PSO_progress, *, num_particles=40, max_iter=500, patience=100,
+                  max_points=100, inertia_decay=0.002, lhs_random_state=None, swarm_fn=None, trace=None,
+                  distributed=None):
+    """Drop-in for find_len_scales.len_scale_opt (:22-150); keyword defaults are the reference's
+    hard-coded constants (:24,:49-54).  `trace` (a list) receives (positions, scores) of every swarm
+    evaluation; `swarm_fn` overrides the evaluator (tests); `distributed` shards the swarm over the
+    initialised torch.distributed group (default: automatically when world_size > 1)."""
+    x_known = np.asarray(x_known, dtype=np.float64)
+    y_known = np.asarray(y_known, dtype=np.float64)
+    e_known = np.asarray(e_known, dtype=np.float64)
+    if x_known.shape[1] > max_points:
+        print(f"Dataset too large ({x_known.shape[1]} points). Subsampling to {max_points} for hyperparameter optimisation.")
+        x_known, y_known, e_known = kmeans_subsample(x_known, y_known, e_known, max_points)
+
+    ndim = len(x_known)
+    restart_count = 0
+    lower_bounds, upper_bounds = swarm_bounds(x_known)
+    v_max = 1.0 * (upper_bounds - lower_bounds)
+    sigma_vals, expected_percents = sigma_grid()
+
+    lhs_cls = _lhs.get_lhs_class()
+    if lhs_random_state is None:
+        sampler = lhs_cls(xlimits=np.column_stack((lower_bounds, upper_bounds)), criterion="center")
+    else:
+        sampler = lhs_cls(xlimits=np.column_stack((lower_bounds, upper_bounds)), criterion="center",
+                          random_state=lhs_random_state)
+    positions = np.array(sampler(num_particles), dtype=np.float64)
+    velocities = np.zeros_like(positions)
+
+    evaluate = swarm_fn if swarm_fn is not None else SwarmLoss(
+        x_known, y_known, e_known, sigma_vals, expected_percents, lower_bounds, upper_bounds)
+    if distributed is None:
+        distributed = sharding.world()[1] > 1
+    if distributed:
+        evaluate = sharding.ShardedSwarm(evaluate)
+
+    def scored(p):
+        s = np.asarray(evaluate(p), dtype=np.float64)
+        if trace is not None:
+            trace.append((p.copy(), s.copy()))
+        return s
+
+    pbest_scores = scored(positions)
+    pbest_pos = positions.copy()
+    g = np.argmin(pbest_scores)
+    gbest_pos = pbest_pos[g].copy()
+    gbest_score = pbest_scores[g]
+    stall = 0
+
+    for i in range(max_iter):
+        w = max(0.4, 0.9 - i * inertia_decay)
+        c1 = c2 = 1.4
+        r1 = np.random.rand(num_particles, ndim)
+        r2 = np.random.rand(num_particles, ndim)
+        velocities = (w * velocities + c1 * r1 * (pbest_pos - positions) + c2 * r2 * (gbest_pos - positions))
+        velocities = np.clip(velocities, -v_max, v_max)
+        positions += velocities
+        positions = np.clip(positions, lower_bounds, upper_bounds)
+
+        scores = scored(positions)
+        improved = scores < pbest_scores
+        pbest_pos[improved] = positions[improved]
+        pbest_scores[improved] = scores[improved]
+        cur = np.argmin(pbest_scores)
+        if pbest_scores[cur] < gbest_score:
+            gbest_score = pbest_scores[cur]
+            gbest_pos = pbest_pos[cur].copy()
+            stall = 0
+        else:
+            stall += 1
+
+        if PSO_progress and i % 20 == 0:
+            print(f"Iter {i}: Best Score = {gbest_score:.6f}, No Improve = {stall}")
+
+        if stall >= patience:
+            if PSO_progress:
+                print(f"Stagnation at iter {i}, soft-restarting swarm...")
+            noise = 0.1 * (upper_bounds - lower_bounds)
+            pbest_pos += np.random.uniform(-noise, noise, pbest_pos.shape)
+            pbest_pos = np.clip(pbest_pos, lower_bounds, upper_bounds)
+            positions = pbest_pos.copy()
+            velocities = np.zeros_like(positions)
+            pbest_scores = scored(pbest_pos)
+            g = np.argmin(pbest_scores)
+            gbest_pos = pbest_pos[g].copy()
+            gbest_score = pbest_scores[g]
+            stall = 0
+            restart_count += 1
+
+    print("PSO completed.")
+    print("Optimal length scale found:")
+    print(gbest_pos)
+    print("Value of loss function:")
+    print(gbest_score)
+    print(f"Total soft restarts: {restart_count}")
+    return gbest_pos

@@ -1,0 +1,57 @@
+"""Probability-surface step: host side of calc_prob_surf.py on top of the fused GPU reduction.
+
+The row loop of generate_prob_surf (calc_prob_surf.py:67-81: finite mask, linspace y-axis,
+sum_gaussians) is one `gpk_prob_surface` launch over the whole merged table; the frame assembly
+and `to_csv` (:83-84, frozen text format) stay in pandas."""
+import os
+
+import numpy as np
+import pandas as pd
+import yaml
+
+from . import engine
+
+POINTS = 100                      # calc_prob_surf.py:45
+DEFAULT_FILENAME = "prob_surf.txt"
+
+
+def sum_gaussians(temp_y, temp_gaus):
+    """Average Gaussian bin probability at the points temp_y for interleaved (mean, std) pairs
+    (calc_prob_surf.py:15-30), evaluated by the surface kernel's inner routine."""
+    temp_y = np.asarray(temp_y, dtype=np.float64)
+    dy = abs(max(temp_y) - min(temp_y)) / len(temp_y)                 # :23
+    return engine.sum_gaussians(temp_y, temp_gaus, dy / 2)
+
+
+def resolve_output_path(options_path):
+    """calc_prob_surf.py:50-65."""
+    output_file = DEFAULT_FILENAME
+    if os.path.exists(options_path):
+        with open(options_path, 'r') as f:
+            options = yaml.safe_load(f) or {}
+        output_path = options.get("out_file_name", "").strip()
+        if output_path:
+            output_file = os.path.join(output_path, DEFAULT_FILENAME) if os.path.isdir(output_path) else output_path
+    return output_file
+
+
+def surface_frame(df, ndims, points=POINTS):
+    """Merged GP-result frame -> long-format frame (dims..., quantity, prob)."""
+    values = df.to_numpy(dtype=np.float64)
+    coords, payload = values[:, :ndims], values[:, ndims:]
+    idx, y, p = engine.prob_surface(payload, points)
+    out = np.empty((idx.shape[0] * points, ndims + 2))
+    out[:, :ndims] = np.repeat(coords[idx], points, axis=0)
+    out[:, ndims] = y.reshape(-1)
+    out[:, ndims + 1] = p.reshape(-1)
+    return pd.DataFrame(out, columns=df.columns[:ndims].tolist() + ["quantity", "prob"])
+
+
+def generate_prob_surf(df, ndims, options_path="options.yaml"):
+    """Drop-in for calc_prob_surf.generate_prob_surf (:39-88): same prints, same CSV."""
+    print("Calculating Probability")
+    output_file = resolve_output_path(options_path)
+    output_df = surface_frame(df, ndims)
+    output_df.to_csv(output_file, index=False)
+    print(f"Probability results written to {output_file}")
+    return

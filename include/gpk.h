@@ -1,0 +1,91 @@
+/* libgpk -- C ABI of the B200-native GP-fitting hot path (drop-in for rferguson22/Gaussian-Process).
+ *
+ * The reference has no FFI: its boundary is the Python functions of GP_func.py, find_len_scales.py and
+ * calc_prob_surf.py.  The Python drop-in modules in gaussian-process_b200/dropin/ keep those signatures
+ * and call the entry points below through ctypes (see INTEGRATION.md for the binding).
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer to C-contiguous float64 / int32 / uint8 data unless it says HOST;
+ *   - data layout is the reference's: points are dims-first, X is (d, N), ls is (P, d);
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *   - functions return 0 on success, non-zero on error (gpk_last_error_string() explains); they never
+ *     throw, never allocate: scratch is sized by the *_workspace_bytes query and passed in;
+ *   - there is no CPU fallback anywhere behind this interface.
+ */
+#ifndef GPK_H_
+#define GPK_H_
+#include <stddef.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define GPK_API __attribute__((visibility("default")))
+#else
+#define GPK_API
+#endif
+
+#define GPK_VERSION 100
+#define GPK_NB 128            /* tile edge; N is padded to a multiple of it internally (Np) */
+#define GPK_SMALL_N_MAX 128   /* N <= this: one-CTA shared-memory path */
+#define GPK_MAX_D 8
+#define GPK_MAX_S 4096
+
+GPK_API int gpk_version(void);
+GPK_API const char* gpk_last_error_string(void);            /* HOST string, valid until the next failing call */
+GPK_API unsigned long long gpk_launch_count(void);          /* kernels launched by this library so far (process-wide) */
+GPK_API int gpk_padded_n(int N);                            /* Np = N rounded up to a multiple of GPK_NB */
+
+/* (a) kernel_func(x1, x2, l), GP_func.py:49-65, for P length-scale vectors in one launch.
+ *     K[p][i][j] = exp(-0.5 * max(|x1_i/l_p|^2 + |x2_j/l_p|^2 - 2 <x1_i/l_p, x2_j/l_p>, 0)); when e != NULL
+ *     (x1 == x2 case of GP_func.py:21) e_i^2 is added on the diagonal.  Row stride ldk, matrix stride strideK. */
+GPK_API int gpk_cov_batched(const double* X1, const double* X2, const double* e, const double* ls, int P, int N1,
+                    int N2, int d, double* K_out, long long ldk, long long strideK, void* stream);
+
+/* (b) batched blocked Cholesky, numpy.linalg.cholesky at GP_func.py:22, for P matrices [P][Np][Np]
+ *     (lower triangle read, lower triangle overwritten by L, strict upper of the diagonal blocks zeroed;
+ *     blocks above the diagonal are not touched).  info[p] = 0 or 1 + index of the first bad pivot. */
+GPK_API size_t gpk_potrf_workspace_bytes(int P, int Np);
+GPK_API int gpk_potrf_batched(double* K_inout, int P, int Np, int* info, void* workspace, size_t workspace_bytes,
+                      void* stream);
+
+/* (b) the PSO hot call: evaluate_loss for a whole swarm, find_len_scales.py:154-163 up to the counts.
+ *     counts[p][s] = #{ i : |mu_i - y_i| / max(sd_i * sigma_vals[s], 1e-12) <= 1 } (int32); the host finishes
+ *     :163-177 in NumPy.  active[p] == 0 marks an out-of-bounds particle (find_len_scales.py:156): it is not
+ *     fitted and its counts are 0.  resid_out / sig_out ([P][N], optional, may be NULL) receive mu - y and sd.
+ *     info[p] != 0: covariance not positive definite (the reference raises LinAlgError). */
+GPK_API size_t gpk_loss_workspace_bytes(int P, int N, int d);
+GPK_API int gpk_loss_batched(const double* X, const double* y, const double* e, const double* ls,
+                     const unsigned char* active, const double* sigma_vals, int P, int N, int d, int S,
+                     int* counts_out, int* info, double* resid_out, double* sig_out, void* workspace,
+                     size_t workspace_bytes, void* stream);
+
+/* (b)+(c) GP(): fit part, GP_func.py:21-24.  Produces the cached state used by gpk_predict:
+ *     W = L^-1 ([Np][Np], lower block triangle), alpha = K^-1 y ([Np]), xs = X / l ([d][Np]), sq ([Np]). */
+GPK_API size_t gpk_fit_workspace_bytes(int N, int d);
+GPK_API int gpk_fit(const double* X, const double* y, const double* e, const double* ls, int N, int d, double* W_out,
+            double* alpha_out, double* xs_out, double* sq_out, int* info, void* workspace,
+            size_t workspace_bytes, void* stream);
+
+/* (c) GP(): predict part, GP_func.py:26-45, for M grid points Xfit (d, M):
+ *     mu = K_*^T alpha, sd = sqrt(clip(1 - |W k_*|^2, 1e-12)).  chunk = grid points per internal pass. */
+GPK_API size_t gpk_predict_workspace_bytes(int N, int chunk);
+GPK_API int gpk_predict(const double* W, const double* alpha, const double* xs, const double* sq, const double* ls,
+                int N, int d, const double* Xfit, long long M, double* mu_out, double* sd_out, int chunk,
+                void* workspace, size_t workspace_bytes, void* stream);
+
+/* (d) generate_prob_surf row loop, calc_prob_surf.py:67-81 + sum_gaussians :15-30.
+ *     table: [R][ncols] payload columns of the merged frame (interleaved mean, std; non-finite = gap).
+ *     valid[r] = 1 if the row emits output; y_out/p_out [R][npoints] are written for valid rows only. */
+GPK_API int gpk_prob_surface(const double* table, long long R, int ncols, int npoints, double* y_out, double* p_out,
+                     int* valid_out, void* stream);
+
+/* (d) sum_gaussians(temp_y, temp_gaus), calc_prob_surf.py:15-30, at n caller-supplied points y; gaus holds
+ *     ng interleaved (mean, std) values; half_dy = (|max(y)-min(y)| / n) / 2 as formed at :23,:26-27. */
+GPK_API int gpk_sum_gaussians(const double* y, int n, const double* gaus, int ng, double half_dy, double* p_out,
+                      void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPK_H_ */

@@ -1,0 +1,215 @@
+"""Parity of the CUDA path (through the C ABI / drop-in modules) against the golden vectors of the
+reference and against the oracle on seeded inputs.  Run on the B200 box: pytest -m gpu."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, load_golden, case
+from oracle import gp_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+sys.path.insert(0, os.path.join(ROOT, "gaussian-process_b200", "dropin"))
+
+
+@pytest.fixture(scope="module")
+def mods():
+    import GP_func, find_len_scales, calc_prob_surf
+    from gaussian_process_b200 import engine, pso, _lib
+    _lib.load()
+    return dict(GP_func=GP_func, fls=find_len_scales, cps=calc_prob_surf, engine=engine, pso=pso)
+
+
+# ------------------------------------------------------------------ (a) covariance
+def test_kernel_func_golden(mods):
+    g = load_golden("kernel_cases.npz")
+    for i in range(int(g["n_cases"])):
+        x1, x2, ls = g[f"k{i}_x1"], g[f"k{i}_x2"], g[f"k{i}_ls"]
+        K = mods["GP_func"].kernel_func(x1, x2, ls)
+        ref = g[f"k{i}_K"]
+        assert K.shape == ref.shape and K.dtype == np.float64
+        scale = max(np.max(np.sum((x1 / ls[:, None]) ** 2, axis=0)), np.max(np.sum((x2 / ls[:, None]) ** 2, axis=0)))
+        tol = 4 * np.finfo(float).eps * max(scale, 1.0)       # cancellation in the expanded distance
+        assert np.max(np.abs(K - ref)) <= max(tol, 1e-14), (i, np.max(np.abs(K - ref)), tol)
+
+
+def test_cov_batched_many_particles(mods):
+    x, y, e = orc.synthetic_problem(300, 3, 1)
+    pos, lo, hi = orc.synthetic_particles(x, 5, 1)
+    K = mods["engine"].cov_batched(x, x, pos, e=e)
+    for p in range(5):
+        ref = orc.rbf_kernel(x, x, pos[p]) + np.diag(e ** 2)
+        assert np.max(np.abs(K[p] - ref)) < 1e-12
+
+
+# ------------------------------------------------------------------ (b) Cholesky
+@pytest.mark.parametrize("n,p", [(128, 3), (384, 2), (1024, 1)])
+def test_potrf_batched(mods, n, p):
+    rng = np.random.default_rng(n)
+    mats = []
+    for _ in range(p):
+        x, _, e = orc.synthetic_problem(n, 2, int(rng.integers(1000)))
+        mats.append(orc.rbf_kernel(x, x, np.array([0.2, 0.3])) + np.diag(e ** 2))
+    k = np.array(mats)
+    L, info = mods["engine"].potrf_batched(k)
+    assert not info.any()
+    for q in range(p):
+        ref = np.linalg.cholesky(k[q])
+        assert np.max(np.abs(L[q] - ref)) < 1e-11
+        assert np.max(np.abs(L[q] @ L[q].T - k[q])) < 1e-13
+
+
+def test_potrf_not_positive_definite(mods):
+    k = np.eye(256)[None].repeat(2, axis=0)
+    k[1, 200, 200] = -1.0
+    _, info = mods["engine"].potrf_batched(k)
+    assert info[0] == 0 and info[1] == 201
+
+
+# ------------------------------------------------------------------ (b) loss
+def _loss_check(mods, c, name):
+    s, ex = orc.sigma_grid()
+    ctx = mods["engine"].LossContext(c["x"], c["y"], c["e"], s)
+    oob = mods["pso"].out_of_bounds_mask(c["pos"], c["lower"], c["upper"])
+    counts, info, resid, sd = ctx.counts(c["pos"], active=~oob, want_detail=True)
+    assert not info.any()
+    act = ~oob
+    np.testing.assert_allclose(resid[act], c["resid"][act], rtol=1e-9, atol=1e-13, err_msg=name)
+    np.testing.assert_allclose(sd[act], c["sd"][act], rtol=1e-9, err_msg=name)
+    assert c["margin"][act].min() > 1e-9
+    np.testing.assert_array_equal(counts[act], c["counts"][act], err_msg=name)     # integer work: exact
+    assert not counts[oob].any()
+    n = c["x"].shape[1]
+    loss = mods["pso"].finish_losses(counts, n, c["pos"], s, ex, c["lower"], c["upper"], oob)
+    np.testing.assert_allclose(loss, c["loss"], rtol=1e-12, err_msg=name)
+    return loss
+
+
+def test_loss_golden(mods):
+    g = load_golden("loss_cases.npz")
+    for name in g["names"]:
+        _loss_check(mods, case(g, str(name)), str(name))
+
+
+def test_evaluate_loss_dropin_signatures(mods):
+    g = load_golden("loss_cases.npz")
+    c = case(g, "syn100_d2")
+    s, ex = orc.sigma_grid()
+    fls = mods["fls"]
+    v = fls.evaluate_loss(c["pos"][2], c["x"], c["y"], c["e"], s, ex, c["lower"], c["upper"])
+    assert isinstance(v, float) and v == pytest.approx(c["loss"][2], rel=1e-12)
+    assert fls.wass_loss(c["pos"][2], c["x"], c["y"], c["e"], s, ex, c["lower"], c["upper"]) == -v
+    assert fls.evaluate_loss_helper((c["pos"][3], c["x"], c["y"], c["e"], s, ex, c["lower"], c["upper"])) == \
+        pytest.approx(c["loss"][3], rel=1e-12)
+    assert fls.evaluate_loss(c["lower"], c["x"], c["y"], c["e"], s, ex, c["lower"], c["upper"]) == 1e13
+    np.testing.assert_array_equal(fls.sigma_to_percent(s), ex)
+
+
+@pytest.mark.parametrize("n,d,p,seed", [(1, 1, 2, 0), (2, 2, 3, 1), (33, 1, 4, 2), (127, 3, 4, 3), (129, 2, 3, 4),
+                                        (256, 3, 3, 5), (500, 2, 2, 6)])
+def test_loss_vs_oracle_seeded(mods, n, d, p, seed):
+    """Edge sizes (single point, just around the 128 small/blocked switch, ragged padding)."""
+    rng = np.random.default_rng(seed)
+    x = rng.random((d, n))
+    y = np.sin(3 * x).sum(axis=0) + 0.1 * rng.standard_normal(n)
+    e = rng.uniform(0.05, 0.2, n)
+    lo, hi = np.full(d, 0.01), np.full(d, 2.0)
+    pos = rng.uniform(0.05, 1.5, (p, d))
+    s, ex = orc.sigma_grid()
+    counts, info, resid, sd = mods["engine"].LossContext(x, y, e, s).counts(pos, want_detail=True)
+    assert not info.any()
+    for k in range(p):
+        c_ref, r_ref, sd_ref, pulls = orc.calibration_counts(pos[k], x, y, e, s)
+        np.testing.assert_allclose(resid[k], r_ref, rtol=1e-8, atol=1e-12)
+        np.testing.assert_allclose(sd[k], sd_ref, rtol=1e-8)
+        if np.min(np.abs(np.abs(pulls) - 1)) > 1e-8:
+            np.testing.assert_array_equal(counts[k], c_ref)
+        else:
+            assert np.abs(counts[k] - c_ref).max() <= 1
+
+
+def test_loss_not_positive_definite_raises(mods):
+    x = np.array([[0.0, 0.0, 1.0]])          # duplicate point, zero noise -> singular K
+    y = np.array([0.0, 1.0, 0.5])
+    e = np.zeros(3)
+    s, ex = orc.sigma_grid()
+    with pytest.raises(np.linalg.LinAlgError):
+        mods["pso"].evaluate_loss_batch(np.array([[0.5]]), x, y, e, s, ex, np.array([0.0]), np.array([2.0]))
+
+
+# ------------------------------------------------------------------ (c) fit + predict
+def test_gp_golden(mods):
+    g = load_golden("gp_cases.npz")
+    for name in g["names"]:
+        c = case(g, str(name))
+        mu, sd = mods["GP_func"].GP(c["x"], c["y"], c["e"], c["grid"].T, c["ls"])
+        assert mu.shape == c["mu"].shape and mu.dtype == np.float64
+        np.testing.assert_allclose(mu, c["mu"], rtol=1e-9, atol=1e-12, err_msg=str(name))
+        np.testing.assert_allclose(sd, c["sd"], rtol=1e-9, err_msg=str(name))
+
+
+def test_gp_edge_cases(mods):
+    x, y, e = orc.synthetic_problem(40, 2, 9)
+    ls = np.array([0.3, 0.4])
+    mu, sd = mods["GP_func"].GP(x, y, e, np.zeros((2, 0)), ls)
+    assert mu.shape == (0,) and sd.shape == (0,)
+    grid = np.asfortranarray(np.random.default_rng(1).random((2, 130)))    # non C-contiguous input, ragged M
+    mu, sd = mods["GP_func"].GP(x, y, e, grid, ls, batch_size=7)
+    mu_r, sd_r = orc.gp(x, y, e, grid, ls)
+    np.testing.assert_allclose(mu, mu_r, rtol=1e-9, atol=1e-12)
+    np.testing.assert_allclose(sd, sd_r, rtol=1e-9)
+    with pytest.raises(np.linalg.LinAlgError):
+        mods["GP_func"].GP(np.array([[0.0, 0.0]]), np.array([1.0, 2.0]), np.zeros(2), np.array([[0.5]]), np.array([1.0]))
+
+
+# ------------------------------------------------------------------ (d) surface
+def test_surface_golden(mods):
+    g = load_golden("surface_cases.npz")
+    for name in g["names"]:
+        c = case(g, str(name))
+        nd = int(c["ndims"])
+        idx, y, p = mods["engine"].prob_surface(c["table"][:, nd:])
+        np.testing.assert_array_equal(c["table"][idx, :nd], c["out_coords"])
+        np.testing.assert_array_equal(y.reshape(-1), c["out_yp"][:, 0], err_msg=str(name))     # linspace: exact
+        np.testing.assert_allclose(p.reshape(-1), c["out_yp"][:, 1], rtol=1e-9, atol=1e-15, err_msg=str(name))
+
+
+def test_generate_prob_surf_csv(mods, tmp_path, monkeypatch):
+    import pandas as pd
+    g = load_golden("surface_cases.npz")
+    c = case(g, "shipped")
+    cols = ["Plab", "cosTheta"] + [f"c{i}" for i in range(c["table"].shape[1] - 2)]
+    df = pd.DataFrame(c["table"], columns=cols)
+    monkeypatch.chdir(tmp_path)
+    (tmp_path / "options.yaml").write_text('out_file_name: "surf_out.csv"\n')
+    assert mods["cps"].generate_prob_surf(df, 2) is None
+    out = pd.read_csv(tmp_path / "surf_out.csv", float_precision="round_trip")
+    assert list(out.columns) == ["Plab", "cosTheta", "quantity", "prob"]
+    np.testing.assert_array_equal(out["quantity"].to_numpy(), c["out_yp"][:, 0])
+    np.testing.assert_allclose(out["prob"].to_numpy(), c["out_yp"][:, 1], rtol=1e-9, atol=1e-15)
+    t = np.linspace(-1, 2, 100)
+    gaus = np.array([0.3, 0.2, 0.9, 0.4])
+    np.testing.assert_allclose(mods["cps"].sum_gaussians(t, gaus), orc.sum_gaussians(t, gaus), rtol=1e-9, atol=1e-15)
+
+
+# ------------------------------------------------------------------ PSO trajectories (config C1 + N=100)
+@pytest.mark.parametrize("name", ["Test_file1_exp1", "Test_file3_exp2", "syn100_d2"])
+def test_pso_trajectory_matches_reference(mods, name, capsys):
+    g = load_golden(f"pso_trace_{name}.npz")
+    seed = int(g["seed"])
+    np.random.seed(seed)
+    trace = []
+    best = mods["fls"].len_scale_opt(g["x"], g["y"], g["e"], True, lhs_random_state=seed, trace=trace)
+    out = capsys.readouterr().out
+    pos = np.array([t[0] for t in trace])
+    sc = np.array([t[1] for t in trace])
+    assert pos.shape == g["positions"].shape, (pos.shape, g["positions"].shape)
+    first_bad = np.argwhere(np.any(pos != g["positions"], axis=(1, 2)))
+    assert first_bad.size == 0, f"trajectory diverges at swarm evaluation {first_bad[0]}"
+    mism = np.mean(sc != g["scores"])
+    print(f"{name}: score bit-mismatch rate {mism:.3e}")
+    np.testing.assert_allclose(sc, g["scores"], rtol=1e-9)
+    np.testing.assert_array_equal(best, g["best"])
+    assert out == str(g["stdout"])
