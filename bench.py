@@ -1,0 +1,351 @@
+#!/usr/bin/env python
+"""Benchmark of the GP-fitting hot path: PSO loss evaluations / second (batched GP fits) at N=4096.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+  torchrun --nproc-per-node N bench.py --gpus N ...          (one rank per GPU, NCCL)
+
+Workload (BASELINE.json configs[2], SURVEY 8d "C3"): synthetic 3-D problem with N=4096 training points,
+a swarm of 256 particles PER GPU (weak scaling: particles shard with no data-path collective; only the
+per-particle losses are all-gathered).  A step = one swarm evaluation = 256 loss evaluations per GPU,
+each a full GP fit (covariance build, blocked FP64 Cholesky, triangular inverse, self-prediction,
+count reduction) -- no KMeans subsample, nothing cached between steps.
+
+One JSON line is printed by rank 0; see the task contract for the keys.  `--impl reference` times the
+CPU implementation of the same path (the NumPy oracle port: the reference itself is NumPy) on the
+host cores."""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOAD = dict(n_points=4096, dims=3, particles_per_gpu=256, n_sigma=1000)
+METRIC = "pso_loss_evals_per_sec_n4096"
+UNIT = "loss_evals/s"
+
+
+def algorithmic_flops_per_eval(n):
+    """SURVEY 8(d), reduced form: Cholesky N^3/3 + triangular inverse N^3/3."""
+    return 2.0 / 3.0 * n ** 3
+
+
+def make_problem(seed=0):
+    from oracle import gp_oracle as orc          # synthetic-data generator only
+    x, y, e = orc.synthetic_problem(WORKLOAD["n_points"], WORKLOAD["dims"], seed)
+    return x, y, e
+
+
+def make_particles(x, p, seed):
+    from oracle import gp_oracle as orc
+    return orc.synthetic_particles(x, p, seed)
+
+
+# --------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    QUERY = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.QUERY}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, smax, power, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [v.strip() for v in r.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); smax.append(float(f[1])); power.append(float(f[2]))
+            except ValueError:
+                continue
+            for nme, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nme)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# --------------------------------------------------------------------------------------- CPU side
+def _cpu_eval(args):
+    """One reference-algorithm loss evaluation at the bench workload (runs in a worker process)."""
+    seed, k = args
+    from oracle import gp_oracle as orc
+    x, y, e = orc.synthetic_problem(WORKLOAD["n_points"], WORKLOAD["dims"], seed)
+    pos, lo, hi = orc.synthetic_particles(x, WORKLOAD["particles_per_gpu"], seed)
+    s, ex = orc.sigma_grid()
+    t0 = time.perf_counter()
+    v = orc.evaluate_loss(pos[k], x, y, e, s, ex, lo, hi)
+    return v, time.perf_counter() - t0
+
+
+class CpuPool:
+    """The reference's own parallel structure (find_len_scales.py:73-77: a process pool over particles,
+    one BLAS thread each, GP_func.py:3-7), widened to every host core."""
+
+    def __init__(self, workers, blas_threads=1):
+        import multiprocessing as mp
+        self.workers = workers
+        self.blas_threads = blas_threads
+        saved = {k: os.environ.get(k) for k in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS")}
+        for k in saved:
+            os.environ[k] = str(blas_threads)          # inherited by the spawned workers before they import numpy
+        self.pool = mp.get_context("spawn").Pool(workers)
+        self.pool.map(_noop, range(workers))
+        for k, v in saved.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+
+    def step(self, n_evals, seed=0):
+        t0 = time.perf_counter()
+        out = self.pool.map(_cpu_eval, [(seed, k) for k in range(n_evals)], chunksize=1)
+        return time.perf_counter() - t0, out
+
+    def close(self):
+        self.pool.terminate()
+        self.pool.join()
+
+
+def _noop(i):
+    import numpy  # noqa: F401
+    from oracle import gp_oracle  # noqa: F401
+    return i
+
+
+def cpu_baseline_sample():
+    """cpu_baseline of the 'ours' line: one pool pass, one evaluation per host core."""
+    cores = os.cpu_count() or 1
+    pool = CpuPool(cores, 1)
+    try:
+        wall, out = pool.step(cores)
+    finally:
+        pool.close()
+    return {"value": cores / wall, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{cores} of the {WORKLOAD['particles_per_gpu']} particles, one per process (1 BLAS thread each, "
+                      f"the reference's pool structure), N=4096 d=3; {wall:.1f} s wall, "
+                      f"{np.mean([o[1] for o in out]):.1f} s per evaluation"}
+
+
+def run_reference(args):
+    """--impl reference: the CPU implementation of the path (NumPy oracle port) on all host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    pool = CpuPool(cores, 1)
+    mode = f"process pool, {cores} workers x 1 BLAS thread, {cores} evaluations per step"
+    evals_per_step = cores
+    budget = 240.0
+    times = []
+    try:
+        for i in range(args.warmup):
+            wall, _ = pool.step(evals_per_step)
+            if i == 0 and wall * (args.steps + args.warmup) > budget:
+                # too slow for the requested step count: one evaluation per step on all cores' BLAS threads
+                pool.close()
+                pool = CpuPool(1, cores)
+                evals_per_step = 1
+                mode = f"1 worker x {cores} BLAS threads, 1 evaluation per step (pool steps would exceed {budget:.0f} s)"
+        t_all = time.perf_counter()
+        for _ in range(args.steps):
+            wall, _ = pool.step(evals_per_step)
+            times.append(wall)
+        total = time.perf_counter() - t_all
+    finally:
+        pool.close()
+    value = evals_per_step * args.steps / total
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "C3 loss evaluation: N=4096 points, d=3, swarm of 256 particles, S=1000 sigma scales",
+                   **WORKLOAD, "cpu_mode": mode},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"{evals_per_step} of the 256 particles per step; {mode}"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------- GPU side
+def measure_fp64_peak(torch, dev):
+    """FP64 dense peak measured live with a plain library DGEMM (cuBLAS via torch.matmul, 8192^3): the
+    roofline denominator for the FP64 tensor (DMMA) work; MEASURED_PEAKS.json only has HBM and bf16."""
+    n = 8192
+    a = torch.randn(n, n, dtype=torch.float64, device=dev)
+    b = torch.randn(n, n, dtype=torch.float64, device=dev)
+    for _ in range(2):
+        a @ b
+    torch.cuda.synchronize()
+    best = 1e30
+    for _ in range(3):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); a @ b; e1.record(); torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    del a, b
+    torch.cuda.empty_cache()
+    return 2.0 * n ** 3 / (best * 1e-3) / 1e12
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from gaussian_process_b200 import engine, pso, sharding, _lib
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    cpu_base = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu_base = cpu_baseline_sample()            # before CUDA is initialised in this process
+
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    _lib.load()
+    N, d, P, S = WORKLOAD["n_points"], WORKLOAD["dims"], args.particles, WORKLOAD["n_sigma"]
+    x, y, e = make_problem(0)
+    # every rank owns a different slice of the global swarm (world * P particles)
+    pos_all, lower, upper = make_particles(x, world * P, 0)
+    pos = np.ascontiguousarray(pos_all[rank * P:(rank + 1) * P])
+    sigma_vals, expected = pso.sigma_grid()
+
+    fp64_peak = measure_fp64_peak(torch, dev) if rank == 0 else None
+    ctx = engine.LossContext(x, y, e, sigma_vals)
+    dpos = engine.to_dev(pos)
+    dact = torch.ones(P, dtype=torch.uint8, device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput ("value") ----
+    for _ in range(args.warmup):
+        counts, info = ctx.counts_device(dpos, dact, P)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = _lib.launch_count()
+    st = torch.cuda.current_stream()
+    _lib.timing_begin(st.cuda_stream)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(st)
+    for _ in range(args.steps):
+        counts, info = ctx.counts_device(dpos, dact, P)
+    e1.record(st)
+    barrier()
+    classes = _lib.timing_end()
+    launches = _lib.launch_count() - launches0
+    clocks = sampler.stop() if rank == 0 else None
+    dev_ms = e0.elapsed_time(e1)
+    assert int(info.abs().sum().item()) == 0, "covariance not positive definite in the bench workload"
+
+    # ---- end to end through the public API with host buffers ("e2e") ----
+    def e2e_step():
+        local_loss = pso.evaluate_loss_batch(pos, x, y, e, sigma_vals, expected, lower, upper)
+        return sharding.all_gather_losses(local_loss, world * P) if world > 1 else local_loss
+
+    for _ in range(min(args.warmup, 2)):
+        losses = e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        losses = e2e_step()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    h2d = (d * N + 2 * N + S + P * d) * 8 + P
+    d2h = P * S * 4 + P * 4
+
+    if world > 1:
+        t = torch.tensor([dev_ms, e2e_s], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_ms, e2e_s = float(t[0]), float(t[1])
+    if rank == 0:
+        evals = world * P * args.steps
+        value = evals / (dev_ms * 1e-3)
+        top = max(classes.items(), key=lambda kv: kv[1][0])
+        total_cls_ms = sum(v[0] for v in classes.values())
+        # algorithmic FP64 flops of the top kernel class over the timed region (this rank)
+        T = (N + 127) // 128
+        alg = {"k_syrk_update": N ** 3 / 3.0, "k_inv_update": N ** 3 / 3.0}
+        flops_top = alg.get(top[0], 0.0) * P * args.steps
+        achieved = flops_top / (top[1][0] * 1e-3) / 1e12 if flops_top else None
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "C3 loss evaluation: N=4096 points, d=3, swarm of 256 particles per GPU, S=1000 sigma scales",
+                       **WORKLOAD, "particles_per_gpu": P, "algorithm": "Cholesky + triangular inverse (2/3 N^3 flop/eval)",
+                       "l2_policy": "working set 34 GB per step >> 126 MB L2 (inputs larger than L2)"},
+            "e2e": {"value": evals / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"bound": "tensor", "kernel": top[0], "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",
+                         "frac": (achieved / fp64_peak) if achieved else None, "traffic": None,
+                         "peak_source": "FP64 cuBLAS DGEMM 8192^3 measured in this run (MEASURED_PEAKS.json has no FP64 figure; "
+                                        "DMMA issue-rate probe: 37.1 TFLOP/s, profiles/r01_fp64_peak_probe.txt)",
+                         "algorithmic_flops_per_launch": flops_top / top[1][1] if flops_top else None,
+                         "avg_launch_ms": top[1][0] / top[1][1],
+                         "whole_step_tflops": algorithmic_flops_per_eval(N) * P * args.steps / (dev_ms * 1e-3) / 1e12,
+                         "kernel_share_of_step": {k: round(v[0] / total_cls_ms, 4) for k, v in sorted(classes.items(), key=lambda kv: -kv[1][0])}},
+            "cpu_baseline": cpu_base,
+            "loss_checksum": float(np.sum(losses[:P])),
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--particles", type=int, default=WORKLOAD["particles_per_gpu"], help="particles per GPU")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

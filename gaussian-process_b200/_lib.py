@@ -24,6 +24,9 @@ SIGNATURES = {
     "gpk_predict_workspace_bytes": (_sz, [_i, _i]),
     "gpk_predict": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _ll, _vp, _vp, _i, _vp, _sz, _vp]),
     "gpk_prob_surface": (_i, [_vp, _ll, _i, _i, _vp, _vp, _vp, _vp]),
+    "gpk_timing_begin": (_i, [_vp]),
+    "gpk_timing_end": (_i, []),
+    "gpk_timing_query": (_i, [_i, C.c_char_p, _i, C.POINTER(C.c_double), C.POINTER(C.c_longlong)]),
     "gpk_sum_gaussians": (_i, [_vp, _i, _vp, _i, C.c_double, _vp, _vp]),
 }
 
@@ -60,3 +63,21 @@ def check(status, what):
 
 def launch_count():
     return int(load().gpk_launch_count())
+
+
+def timing_begin(stream):
+    check(load().gpk_timing_begin(stream), "gpk_timing_begin")
+
+
+def timing_end():
+    """-> {kernel class: (total ms, launches)} since timing_begin."""
+    lib = load()
+    check(lib.gpk_timing_end(), "gpk_timing_end")
+    out, i = {}, 0
+    name = C.create_string_buffer(128)
+    ms, cnt = C.c_double(), C.c_longlong()
+    while lib.gpk_timing_query(i, name, 128, C.byref(ms), C.byref(cnt)) == 0:
+        if cnt.value:
+            out[name.value.decode()] = (ms.value, cnt.value)
+        i += 1
+    return out

@@ -4,6 +4,8 @@
 #include <cstdarg>
 #include <cstring>
 #include <mutex>
+#include <string>
+#include <vector>
 
 #include "../../include/gpk.h"
 #include "gpk_common.cuh"
@@ -24,8 +26,40 @@ void set_error(const char* fmt, ...) {
 
 void count_launch(int n) { g_launches.fetch_add((unsigned long long)n); }
 
+// ---- optional per-kernel-class device timing (bench.py's roofline) ---------------------------------
+// While enabled, every launch is followed by an event on the launching stream; with an in-order stream
+// kept busy, the gap between consecutive events is that kernel's duration.
+struct TimingRec { cudaEvent_t ev; int cls; };
+static bool g_timing = false;
+static cudaStream_t g_cur_stream = nullptr;
+static std::vector<TimingRec> g_recs;
+static std::vector<cudaEvent_t> g_pool;
+static std::vector<std::string> g_cls_names;
+static std::vector<double> g_cls_ms;
+static std::vector<long long> g_cls_n;
+
+void set_stream(cudaStream_t st) { g_cur_stream = st; }
+
+static cudaEvent_t take_event() {
+    if (!g_pool.empty()) { cudaEvent_t e = g_pool.back(); g_pool.pop_back(); return e; }
+    cudaEvent_t e; cudaEventCreate(&e); return e;
+}
+
+static int class_id(const char* what) {
+    for (size_t i = 0; i < g_cls_names.size(); ++i) if (g_cls_names[i] == what) return (int)i;
+    g_cls_names.push_back(what); g_cls_ms.push_back(0.0); g_cls_n.push_back(0);
+    return (int)g_cls_names.size() - 1;
+}
+
+static void timing_mark(const char* what) {
+    TimingRec r{take_event(), class_id(what)};
+    cudaEventRecord(r.ev, g_cur_stream);
+    g_recs.push_back(r);
+}
+
 int check_launch(const char* what) {
     count_launch(1);
+    if (g_timing) timing_mark(what);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         set_error("%s: %s", what, cudaGetErrorString(e));
@@ -100,6 +134,7 @@ int gpk_padded_n(int N) { return round_up(N, NB); }
 int gpk_cov_batched(const double* X1, const double* X2, const double* e, const double* ls, int P, int N1, int N2,
                     int d, double* K_out, long long ldk, long long strideK, void* stream) {
     if (bad_dims("gpk_cov_batched", N1, d, 0) || N2 < 1 || P < 1) return 2;
+    set_stream((cudaStream_t)stream);
     return launch_cov_full(X1, X2, e, ls, P, N1, N2, d, K_out, ldk, strideK, (cudaStream_t)stream);
 }
 
@@ -113,6 +148,7 @@ int gpk_potrf_batched(double* K_inout, int P, int Np, int* info, void* workspace
     if (Np < NB || Np % NB != 0 || P < 1) { set_error("gpk_potrf_batched: Np=%d must be a positive multiple of %d", Np, NB); return 2; }
     if (workspace_bytes < gpk_potrf_workspace_bytes(P, Np)) { set_error("gpk_potrf_batched: workspace too small"); return 3; }
     cudaStream_t st = (cudaStream_t)stream;
+    set_stream(st);
     const int T = Np / NB;
     double* dinv = (double*)workspace;
     double* dinvT = (double*)((char*)workspace + align256((size_t)P * T * NB * NB * 8));
@@ -131,6 +167,7 @@ int gpk_loss_batched(const double* X, const double* y, const double* e, const do
                      size_t workspace_bytes, void* stream) {
     if (bad_dims("gpk_loss_batched", N, d, S) || P < 1) return 2;
     cudaStream_t st = (cudaStream_t)stream;
+    set_stream(st);
     if (cudaMemsetAsync(info, 0, (size_t)P * sizeof(int), st) != cudaSuccess) { set_error("memset info failed"); return 1; }
     if (N <= SMALL_N_MAX)
         return launch_small_loss(X, y, e, ls, active, sigma_vals, P, N, d, S, counts_out, info, resid_out, sig_out, st);
@@ -180,6 +217,7 @@ int gpk_fit(const double* X, const double* y, const double* e, const double* ls,
     if (bad_dims("gpk_fit", N, d, 0)) return 2;
     if (workspace_bytes < gpk_fit_workspace_bytes(N, d)) { set_error("gpk_fit: workspace too small"); return 3; }
     cudaStream_t st = (cudaStream_t)stream;
+    set_stream(st);
     const int Np = round_up(N, NB), T = Np / NB;
     char* ws = (char*)workspace;
     size_t off = 0;
@@ -210,6 +248,7 @@ int gpk_predict(const double* W, const double* alpha, const double* xs, const do
     if (M <= 0) return 0;
     if (workspace_bytes < gpk_predict_workspace_bytes(N, chunk)) { set_error("gpk_predict: workspace too small"); return 3; }
     cudaStream_t st = (cudaStream_t)stream;
+    set_stream(st);
     const int Np = round_up(N, NB), T = Np / NB;
     const int BpMax = round_up(chunk, NB);
     double* KsT = (double*)workspace;
@@ -227,12 +266,45 @@ int gpk_predict(const double* W, const double* alpha, const double* xs, const do
 int gpk_prob_surface(const double* table, long long R, int ncols, int npoints, double* y_out, double* p_out,
                      int* valid_out, void* stream) {
     if (npoints < 1) { set_error("gpk_prob_surface: npoints=%d", npoints); return 2; }
+    set_stream((cudaStream_t)stream);
     return launch_prob_surface(table, R, ncols, npoints, y_out, p_out, valid_out, (cudaStream_t)stream);
 }
 
 int gpk_sum_gaussians(const double* y, int n, const double* gaus, int ng, double half_dy, double* p_out,
                       void* stream) {
+    set_stream((cudaStream_t)stream);
     return launch_sum_gaussians(y, n, gaus, ng, half_dy, p_out, (cudaStream_t)stream);
+}
+
+int gpk_timing_begin(void* stream) {
+    g_cur_stream = (cudaStream_t)stream;
+    for (auto& r : g_recs) g_pool.push_back(r.ev);
+    g_recs.clear();
+    g_cls_names.clear(); g_cls_ms.clear(); g_cls_n.clear();
+    g_timing = true;
+    timing_mark("(begin)");
+    return 0;
+}
+
+int gpk_timing_end(void) {
+    g_timing = false;
+    if (g_recs.empty()) return 0;
+    if (cudaEventSynchronize(g_recs.back().ev) != cudaSuccess) { set_error("timing: event sync failed"); return 1; }
+    for (size_t i = 1; i < g_recs.size(); ++i) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, g_recs[i - 1].ev, g_recs[i].ev);
+        g_cls_ms[g_recs[i].cls] += ms;
+        g_cls_n[g_recs[i].cls] += 1;
+    }
+    return 0;
+}
+
+int gpk_timing_query(int idx, char* name_out, int name_cap, double* ms_out, long long* count_out) {
+    if (idx < 0 || idx >= (int)g_cls_names.size()) return 1;
+    snprintf(name_out, name_cap, "%s", g_cls_names[idx].c_str());
+    *ms_out = g_cls_ms[idx];
+    *count_out = g_cls_n[idx];
+    return 0;
 }
 
 }  // extern "C"

@@ -85,6 +85,12 @@ GPK_API int gpk_prob_surface(const double* table, long long R, int ncols, int np
 GPK_API int gpk_sum_gaussians(const double* y, int n, const double* gaus, int ng, double half_dy, double* p_out,
                       void* stream);
 
+/* Measurement aid (bench.py roofline): per-kernel-class device time by events recorded after every launch
+ * on `stream` between begin and end.  Not thread-safe; name_out is a HOST buffer. */
+GPK_API int gpk_timing_begin(void* stream);
+GPK_API int gpk_timing_end(void);
+GPK_API int gpk_timing_query(int idx, char* name_out, int name_cap, double* ms_out, long long* count_out);
+
 #ifdef __cplusplus
 }
 #endif
