@@ -24,6 +24,7 @@ SIGNATURES = {
     "gpk_predict_workspace_bytes": (_sz, [_i, _i]),
     "gpk_predict": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _ll, _vp, _vp, _i, _vp, _sz, _vp]),
     "gpk_prob_surface": (_i, [_vp, _ll, _i, _i, _vp, _vp, _vp, _vp]),
+    "gpk_set_groups": (_i, [_i]),
     "gpk_timing_begin": (_i, [_vp]),
     "gpk_timing_end": (_i, []),
     "gpk_timing_query": (_i, [_i, C.c_char_p, _i, C.POINTER(C.c_double), C.POINTER(C.c_longlong)]),

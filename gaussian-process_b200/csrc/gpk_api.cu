@@ -68,6 +68,7 @@ int check_launch(const char* what) {
     return 0;
 }
 
+constexpr int MAX_GROUPS = 8;
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 BlockedLayout blocked_layout(int P, int N, int d) {
@@ -108,6 +109,25 @@ static int inverse_phase(double* mat, int Np, int T, int P, const double* dinvT,
     for (int J = T - 2; J >= 0; --J) {
         if (launch_inv_panel(mat, Np, T, J, P, dinvT, mt, active, st)) return 1;
         if (launch_inv_update(mat, Np, T, J, P, mt, active, st)) return 1;
+    }
+    return 0;
+}
+
+// ---- concurrent particle groups ------------------------------------------------------------------
+static int g_groups = 4;
+static cudaStream_t g_group_streams[MAX_GROUPS] = {};
+static cudaEvent_t g_join[MAX_GROUPS] = {};
+static cudaEvent_t g_fork = nullptr;
+static int g_groups_ready = 0;
+
+static int ensure_group_streams(int G) {
+    if (g_fork == nullptr && cudaEventCreateWithFlags(&g_fork, cudaEventDisableTiming) != cudaSuccess) { set_error("event create failed"); return 1; }
+    for (; g_groups_ready < G; ++g_groups_ready) {
+        if (cudaStreamCreateWithFlags(&g_group_streams[g_groups_ready], cudaStreamNonBlocking) != cudaSuccess ||
+            cudaEventCreateWithFlags(&g_join[g_groups_ready], cudaEventDisableTiming) != cudaSuccess) {
+            set_error("group stream create failed");
+            return 1;
+        }
     }
     return 0;
 }
@@ -158,7 +178,12 @@ int gpk_potrf_batched(double* K_inout, int P, int Np, int* info, void* workspace
 
 size_t gpk_loss_workspace_bytes(int P, int N, int d) {
     if (N <= SMALL_N_MAX) return 256;
-    return blocked_layout(P, N, d).total;
+    size_t best = 0;                      // enough for any particle-group split (gpk_set_groups)
+    for (int G = 1; G <= MAX_GROUPS; ++G) {
+        const size_t b = (size_t)G * blocked_layout((P + G - 1) / G, N, d).total;
+        if (b > best) best = b;
+    }
+    return best;
 }
 
 int gpk_loss_batched(const double* X, const double* y, const double* e, const double* ls,
@@ -172,35 +197,57 @@ int gpk_loss_batched(const double* X, const double* y, const double* e, const do
     if (N <= SMALL_N_MAX)
         return launch_small_loss(X, y, e, ls, active, sigma_vals, P, N, d, S, counts_out, info, resid_out, sig_out, st);
 
-    // blocked path, in waves of as many particles as the workspace holds
+    // blocked path: waves of as many particles as the workspace holds, each wave split into independent
+    // particle groups on concurrent streams (the chain SYRK -> diag -> TRSM of one group is serial; kernels of
+    // other groups fill its wave tails and hide the latency-bound diagonal kernel)
     const size_t per1 = blocked_layout(1, N, d).total;
     if (workspace == nullptr || workspace_bytes < per1) { set_error("gpk_loss_batched: workspace too small (%zu < %zu)", workspace_bytes, per1); return 3; }
+    int G = g_timing ? 1 : g_groups;
+    if (G > P / 8) G = P / 8;
+    if (G < 1) G = 1;
+    if (G > 1 && ensure_group_streams(G)) return 1;
+    auto fits = [&](int pw) { const int pg = (pw + G - 1) / G; return (size_t)G * blocked_layout(pg, N, d).total <= workspace_bytes; };
     int Pw = P;
-    while (Pw > 1 && blocked_layout(Pw, N, d).total > workspace_bytes) Pw = (Pw * 7) / 8 < Pw ? (Pw * 7) / 8 : Pw - 1;
+    while (Pw > 1 && !fits(Pw)) { --Pw; }
+    if (!fits(Pw)) { G = 1; Pw = 1; }
     for (int p0 = 0; p0 < P; p0 += Pw) {
-        const int Pc = (P - p0 < Pw) ? (P - p0) : Pw;
-        const BlockedLayout L = blocked_layout(Pc, N, d);
-        char* ws = (char*)workspace;
-        double* mat = (double*)(ws + L.mat);
-        double* dinv = (double*)(ws + L.dinv);
-        double* dinvT = (double*)(ws + L.dinvT);
-        double* mt = (double*)(ws + L.mt);
-        double* xs = (double*)(ws + L.xs);
-        double* sq = (double*)(ws + L.sq);
-        double* cn = (double*)(ws + L.cn);
-        double* z = (double*)(ws + L.z);
-        double* alpha = (double*)(ws + L.alpha);
-        const unsigned char* act = active ? active + p0 : nullptr;
-        const double* lsp = ls + (size_t)p0 * d;
-        if (launch_scale_points(X, lsp, Pc, N, L.Np, d, xs, sq, act, st)) return 1;
-        if (launch_cov_lower(xs, sq, e, Pc, N, L.Np, d, mat, act, st)) return 1;
-        if (factor_phase(mat, L.Np, L.T, Pc, dinv, dinvT, info + p0, act, DIAG_WRITE_INVERSE, st)) return 1;
-        if (inverse_phase(mat, L.Np, L.T, Pc, dinvT, mt, act, st)) return 1;
-        if (launch_wy(mat, L.Np, N, Pc, y, z, act, st)) return 1;
-        if (launch_colnorm_alpha(mat, L.Np, Pc, z, cn, alpha, act, st)) return 1;
-        if (launch_counts(alpha, cn, e, sigma_vals, Pc, N, L.Np, S, counts_out + (size_t)p0 * S,
-                          resid_out ? resid_out + (size_t)p0 * N : nullptr,
-                          sig_out ? sig_out + (size_t)p0 * N : nullptr, act, st)) return 1;
+        const int Pwave = (P - p0 < Pw) ? (P - p0) : Pw;
+        const int pg = (Pwave + G - 1) / G;
+        const size_t gbytes = blocked_layout(pg, N, d).total;
+        if (G > 1 && cudaEventRecord(g_fork, st) != cudaSuccess) { set_error("fork event failed"); return 1; }
+        for (int g = 0; g < G; ++g) {
+            const int q0 = p0 + g * pg;
+            const int Pc = (p0 + Pwave - q0 < pg) ? (p0 + Pwave - q0) : pg;
+            if (Pc <= 0) break;
+            cudaStream_t gs = (G > 1) ? g_group_streams[g] : st;
+            if (G > 1) cudaStreamWaitEvent(gs, g_fork, 0);
+            const BlockedLayout L = blocked_layout(Pc, N, d);
+            char* ws = (char*)workspace + (size_t)g * gbytes;
+            double* mat = (double*)(ws + L.mat);
+            double* dinv = (double*)(ws + L.dinv);
+            double* dinvT = (double*)(ws + L.dinvT);
+            double* mt = (double*)(ws + L.mt);
+            double* xs = (double*)(ws + L.xs);
+            double* sq = (double*)(ws + L.sq);
+            double* cn = (double*)(ws + L.cn);
+            double* z = (double*)(ws + L.z);
+            double* alpha = (double*)(ws + L.alpha);
+            const unsigned char* act = active ? active + q0 : nullptr;
+            const double* lsp = ls + (size_t)q0 * d;
+            if (launch_scale_points(X, lsp, Pc, N, L.Np, d, xs, sq, act, gs)) return 1;
+            if (launch_cov_lower(xs, sq, e, Pc, N, L.Np, d, mat, act, gs)) return 1;
+            if (factor_phase(mat, L.Np, L.T, Pc, dinv, dinvT, info + q0, act, DIAG_WRITE_INVERSE, gs)) return 1;
+            if (inverse_phase(mat, L.Np, L.T, Pc, dinvT, mt, act, gs)) return 1;
+            if (launch_wy(mat, L.Np, N, Pc, y, z, act, gs)) return 1;
+            if (launch_colnorm_alpha(mat, L.Np, Pc, z, cn, alpha, act, gs)) return 1;
+            if (launch_counts(alpha, cn, e, sigma_vals, Pc, N, L.Np, S, counts_out + (size_t)q0 * S,
+                              resid_out ? resid_out + (size_t)q0 * N : nullptr,
+                              sig_out ? sig_out + (size_t)q0 * N : nullptr, act, gs)) return 1;
+            if (G > 1) {
+                cudaEventRecord(g_join[g], gs);
+                cudaStreamWaitEvent(st, g_join[g], 0);
+            }
+        }
     }
     return 0;
 }
@@ -274,6 +321,12 @@ int gpk_sum_gaussians(const double* y, int n, const double* gaus, int ng, double
                       void* stream) {
     set_stream((cudaStream_t)stream);
     return launch_sum_gaussians(y, n, gaus, ng, half_dy, p_out, (cudaStream_t)stream);
+}
+
+int gpk_set_groups(int groups) {
+    if (groups < 1 || groups > MAX_GROUPS) { set_error("gpk_set_groups: 1..%d", MAX_GROUPS); return 2; }
+    g_groups = groups;
+    return 0;
 }
 
 int gpk_timing_begin(void* stream) {

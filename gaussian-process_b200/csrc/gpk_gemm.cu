@@ -58,6 +58,25 @@ __device__ __forceinline__ void load_stage(const Tile& t, int kc, double* As, do
 }
 
 // acc[mi][ni][h]: row = warp_m*64 + mi*8 + lane/4, col = warp_n*32 + ni*8 + (lane%4)*2 + h
+//
+// Software pipeline: the fragments of k4-step t+1 are loaded into a second register set while the 32 DMMAs of
+// step t issue, also across the chunk boundary -- the ring barrier sits *before* the last k4-step of a chunk,
+// whose DMMAs then cover the barrier, the cp.async refill and the first fragment loads of the next chunk
+// (both warps of a scheduler run in lockstep, so nothing else would hide those bubbles; ncu r01: 85 % -> v2).
+__device__ __forceinline__ void load_frags(const double* As, const double* Bs, int kk, double (&a)[8], double (&b)[4]) {
+#pragma unroll
+    for (int mi = 0; mi < 8; ++mi) a[mi] = As[mi * 8 * SLD + kk * 4];
+#pragma unroll
+    for (int ni = 0; ni < 4; ++ni) b[ni] = Bs[ni * 8 * SLD + kk * 4];
+}
+
+__device__ __forceinline__ void mma_step(double (&acc)[8][4][2], const double (&a)[8], const double (&b)[4]) {
+#pragma unroll
+    for (int mi = 0; mi < 8; ++mi)
+#pragma unroll
+        for (int ni = 0; ni < 4; ++ni) dmma884(acc[mi][ni][0], acc[mi][ni][1], a[mi], b[ni]);
+}
+
 __device__ __forceinline__ void mainloop(const Tile& t, double (&acc)[8][4][2], double* smem) {
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
@@ -68,38 +87,40 @@ __device__ __forceinline__ void mainloop(const Tile& t, double (&acc)[8][4][2], 
 #pragma unroll
         for (int ni = 0; ni < 4; ++ni) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
 
+    // prologue: fill the whole ring
 #pragma unroll
-    for (int s = 0; s < STAGES - 1; ++s) {
+    for (int s = 0; s < STAGES; ++s) {
         if (s < t.kchunks) load_stage(t, s, smem + (size_t)s * 2 * OPER_ELEMS, smem + (size_t)s * 2 * OPER_ELEMS + OPER_ELEMS, tid);
         cp_async_commit();
     }
     const int a_off = (warp_m * 64 + g) * SLD + q;
     const int b_off = (warp_n * 32 + g) * SLD + q;
+    double fa[2][8], fb[2][4];
+    cp_async_wait<STAGES - 1>();          // chunk 0 has landed
+    __syncthreads();
+    load_frags(smem + a_off, smem + OPER_ELEMS + b_off, 0, fa[0], fb[0]);
+
     for (int kc = 0; kc < t.kchunks; ++kc) {
-        cp_async_wait<STAGES - 2>();
-        __syncthreads();
-        {
-            const int nk = kc + STAGES - 1;
-            if (nk < t.kchunks) {
-                double* base = smem + (size_t)(nk % STAGES) * 2 * OPER_ELEMS;
-                load_stage(t, nk, base, base + OPER_ELEMS, tid);
+        const double* As = smem + (size_t)(kc % STAGES) * 2 * OPER_ELEMS + a_off;
+        const double* Bs = As - a_off + OPER_ELEMS + b_off;
+        load_frags(As, Bs, 1, fa[1], fb[1]);
+        mma_step(acc, fa[0], fb[0]);
+        load_frags(As, Bs, 2, fa[0], fb[0]);
+        mma_step(acc, fa[1], fb[1]);
+        load_frags(As, Bs, 3, fa[1], fb[1]);
+        mma_step(acc, fa[0], fb[0]);
+        if (kc + 1 < t.kchunks) {
+            cp_async_wait<STAGES - 2>();  // chunk kc+1 has landed (this thread's copies) ...
+            __syncthreads();              // ... everybody's; and nobody reads the slot of chunk kc any more
+            const double* An = smem + (size_t)((kc + 1) % STAGES) * 2 * OPER_ELEMS + a_off;
+            load_frags(An, An - a_off + OPER_ELEMS + b_off, 0, fa[0], fb[0]);
+            if (kc + STAGES < t.kchunks) {
+                double* base = smem + (size_t)(kc % STAGES) * 2 * OPER_ELEMS;
+                load_stage(t, kc + STAGES, base, base + OPER_ELEMS, tid);
             }
             cp_async_commit();
         }
-        const double* As = smem + (size_t)(kc % STAGES) * 2 * OPER_ELEMS + a_off;
-        const double* Bs = smem + (size_t)(kc % STAGES) * 2 * OPER_ELEMS + OPER_ELEMS + b_off;
-#pragma unroll
-        for (int kk = 0; kk < KC / 4; ++kk) {
-            double a[8], b[4];
-#pragma unroll
-            for (int mi = 0; mi < 8; ++mi) a[mi] = As[mi * 8 * SLD + kk * 4];
-#pragma unroll
-            for (int ni = 0; ni < 4; ++ni) b[ni] = Bs[ni * 8 * SLD + kk * 4];
-#pragma unroll
-            for (int mi = 0; mi < 8; ++mi)
-#pragma unroll
-                for (int ni = 0; ni < 4; ++ni) dmma884(acc[mi][ni][0], acc[mi][ni][1], a[mi], b[ni]);
-        }
+        mma_step(acc, fa[1], fb[1]);
     }
     cp_async_wait<0>();
     __syncthreads();

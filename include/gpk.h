@@ -85,6 +85,10 @@ GPK_API int gpk_prob_surface(const double* table, long long R, int ncols, int np
 GPK_API int gpk_sum_gaussians(const double* y, int n, const double* gaus, int ng, double half_dy, double* p_out,
                       void* stream);
 
+/* Number of concurrent particle groups (streams) gpk_loss_batched splits a swarm into on the blocked path
+ * (default 4, 1..8).  Results do not depend on it. */
+GPK_API int gpk_set_groups(int groups);
+
 /* Measurement aid (bench.py roofline): per-kernel-class device time by events recorded after every launch
  * on `stream` between begin and end.  Not thread-safe; name_out is a HOST buffer. */
 GPK_API int gpk_timing_begin(void* stream);
