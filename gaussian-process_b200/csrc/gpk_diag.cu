@@ -17,17 +17,25 @@ k_diag_block(double* __restrict__ mat, int Np, int J, double* __restrict__ dinv,
     const int tid = threadIdx.x;
     double* blk = mat + (size_t)p * Np * Np + (size_t)J * NB * Np + (size_t)J * NB;
 
-    // load lower triangle, initialise the X part to the identity
-    for (int idx = tid; idx < NB * NB; idx += 256) {
-        const int r = idx >> 7, c = idx & (NB - 1);
-        if (c <= r) Lm[r * CI_LD + c] = blk[(size_t)r * Np + c];
-        else Lm[r * CI_LD + c + 1] = 0.0;          // X[c][r], c > r  (strictly lower part of X) = 0
+    // each thread loads its 8x8 register tile of the lower triangle (the X part starts at zero)
+    double* v = col;
+    double* xd = xr;
+    double* piv = xr + NB;
+    double E[8][8];
+    {
+        const int R0 = (tid >> 4) * 8, C0 = (tid & 15) * 8;
+#pragma unroll
+        for (int rr = 0; rr < 8; ++rr)
+#pragma unroll
+            for (int cc = 0; cc < 8; ++cc) {
+                const int r = R0 + rr, c = C0 + cc;
+                E[rr][cc] = (c <= r) ? blk[(size_t)r * Np + c] : 0.0;
+            }
     }
-    if (tid < NB) Lm[tid * CI_LD + tid + 1] = 1.0;  // X[r][r] = 1
-    __syncthreads();
-
-    const int bad = chol_inv_inplace(Lm, NB, col, xr);
+    const int bad = chol_inv_regs(E, NB, v, xd, piv);
     if (bad && tid == 0) atomicCAS(&info[p], 0, J * NB + bad);
+    chol_inv_dump(E, xd, Lm);
+    __syncthreads();
 
     double* dI = dinv + ((size_t)p * T + J) * NB * NB;
     double* dT = dinvT + ((size_t)p * T + J) * NB * NB;

@@ -66,7 +66,8 @@ struct SmallSmem {
     static constexpr size_t z = d + NB * 8;
     static constexpr size_t a = z + NB * 8;
     static constexpr size_t sg = a + NB * 8;
-    static constexpr size_t hist = sg + NB * 8;
+    static constexpr size_t piv = sg + NB * 8;
+    static constexpr size_t hist = piv + 16;
     static constexpr size_t total = hist + (size_t)(MAX_S + 1) * 4;
 };
 
@@ -110,26 +111,32 @@ k_small_loss(const double* __restrict__ X, const double* __restrict__ y, const d
     for (int k = tid; k <= S; k += 256) hist[k] = 0;
     __syncthreads();
 
-    // K + diag(e^2) into the lower triangle; identity into the X part
-    for (int idx = tid; idx < N * N; idx += 256) {
-        const int r = idx / N, c = idx - r * N;
-        if (c <= r) {
-            double dot = __dmul_rn(xs[0][r], xs[0][c]);
-            for (int dd = 1; dd < d; ++dd) dot = fma(xs[dd][r], xs[dd][c], dot);
-            double s = __dsub_rn(__dadd_rn(sq[r], sq[c]), __dmul_rn(2.0, dot));
-            s = fmax(s, 0.0);
-            double v = exp(__dmul_rn(-0.5, s));
-            if (r == c) v = __dadd_rn(v, dv[r]);
-            Lm[r * CI_LD + c] = v;
-        } else {
-            Lm[r * CI_LD + c + 1] = 0.0;
-        }
+    // K + diag(e^2): each thread builds its 8x8 register tile of the lower triangle (zero elsewhere)
+    double E[8][8];
+    {
+        const int R0 = (tid >> 4) * 8, C0 = (tid & 15) * 8;
+#pragma unroll
+        for (int rr = 0; rr < 8; ++rr)
+#pragma unroll
+            for (int cc = 0; cc < 8; ++cc) {
+                const int r = R0 + rr, c = C0 + cc;
+                double val = 0.0;
+                if (c <= r && r < N) {
+                    double dot = __dmul_rn(xs[0][r], xs[0][c]);
+                    for (int dd = 1; dd < d; ++dd) dot = fma(xs[dd][r], xs[dd][c], dot);
+                    double s = __dsub_rn(__dadd_rn(sq[r], sq[c]), __dmul_rn(2.0, dot));
+                    s = fmax(s, 0.0);
+                    val = exp(__dmul_rn(-0.5, s));
+                    if (r == c) val = __dadd_rn(val, dv[r]);
+                }
+                E[rr][cc] = val;
+            }
     }
-    if (tid < N) Lm[tid * CI_LD + tid + 1] = 1.0;
-    __syncthreads();
-
-    const int bad = chol_inv_inplace(Lm, N, col, xr);
+    double* piv = reinterpret_cast<double*>(raw + SmallSmem::piv);
+    const int bad = chol_inv_regs(E, N, col, xr, piv);
     if (bad && tid == 0) info[p] = bad;
+    chol_inv_dump(E, xr, Lm);
+    __syncthreads();
 
     // z = W y  (W[k][c] = Lm[c][k+1])
     if (tid < N) {
