@@ -20,7 +20,10 @@ constexpr int SLD = KC + 4;            // padded row stride: 2*SLD = 8 (mod 32) 
 constexpr int STAGES = 4;
 constexpr int KSTEPS = KC / 4;         // m8n8k4 steps per chunk (even)
 constexpr int ROWCH = KC / 2;          // 16-byte chunks per operand row
-constexpr int LD_ITERS = NB * ROWCH / 256;
+constexpr int GEMM_THREADS = 512;      // 16 warps as 4 (M) x 4 (N), warp tile 32 x 32 = 4 x 4 DMMA fragments
+constexpr int MI = 4;                  // 8-row fragments per warp tile
+constexpr int WARP_M = MI * 8;
+constexpr int LD_ITERS = NB * ROWCH / GEMM_THREADS;
 constexpr int OPER_ELEMS = NB * SLD;                                  // one operand, one stage
 constexpr size_t GEMM_SMEM_BYTES = (size_t)STAGES * 2 * OPER_ELEMS * sizeof(double);
 
@@ -48,13 +51,13 @@ struct Tile {
 __device__ __forceinline__ void load_stage(const Tile& t, int kc, double* As, double* Bs, int tid) {
 #pragma unroll
     for (int i = 0; i < LD_ITERS; ++i) {
-        const int cid = tid + 256 * i;
+        const int cid = tid + GEMM_THREADS * i;
         const int row = cid / ROWCH, ch = cid % ROWCH;
         cp_async16(As + row * SLD + ch * 2, t.A + (size_t)row * t.lda + kc * KC + ch * 2);
     }
 #pragma unroll
     for (int i = 0; i < LD_ITERS; ++i) {
-        const int cid = tid + 256 * i;
+        const int cid = tid + GEMM_THREADS * i;
         const int row = cid / ROWCH, ch = cid % ROWCH;
         cp_async16(Bs + row * SLD + ch * 2, t.B + (size_t)row * t.ldb + kc * KC + ch * 2);
     }
@@ -66,27 +69,27 @@ __device__ __forceinline__ void load_stage(const Tile& t, int kc, double* As, do
 // step t issue, also across the chunk boundary -- the ring barrier sits *before* the last k4-step of a chunk,
 // whose DMMAs then cover the barrier, the cp.async refill and the first fragment loads of the next chunk
 // (both warps of a scheduler run in lockstep, so nothing else would hide those bubbles; ncu r01: 85 % -> v2).
-__device__ __forceinline__ void load_frags(const double* As, const double* Bs, int kk, double (&a)[8], double (&b)[4]) {
+__device__ __forceinline__ void load_frags(const double* As, const double* Bs, int kk, double (&a)[MI], double (&b)[4]) {
 #pragma unroll
-    for (int mi = 0; mi < 8; ++mi) a[mi] = As[mi * 8 * SLD + kk * 4];
+    for (int mi = 0; mi < MI; ++mi) a[mi] = As[mi * 8 * SLD + kk * 4];
 #pragma unroll
     for (int ni = 0; ni < 4; ++ni) b[ni] = Bs[ni * 8 * SLD + kk * 4];
 }
 
-__device__ __forceinline__ void mma_step(double (&acc)[8][4][2], const double (&a)[8], const double (&b)[4]) {
+__device__ __forceinline__ void mma_step(double (&acc)[MI][4][2], const double (&a)[MI], const double (&b)[4]) {
 #pragma unroll
-    for (int mi = 0; mi < 8; ++mi)
+    for (int mi = 0; mi < MI; ++mi)
 #pragma unroll
         for (int ni = 0; ni < 4; ++ni) dmma884(acc[mi][ni][0], acc[mi][ni][1], a[mi], b[ni]);
 }
 
-__device__ __forceinline__ void mainloop(const Tile& t, double (&acc)[8][4][2], double* smem) {
+__device__ __forceinline__ void mainloop(const Tile& t, double (&acc)[MI][4][2], double* smem) {
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
     const int warp_m = warp >> 2, warp_n = warp & 3;
     const int g = lane >> 2, q = lane & 3;
 #pragma unroll
-    for (int mi = 0; mi < 8; ++mi)
+    for (int mi = 0; mi < MI; ++mi)
 #pragma unroll
         for (int ni = 0; ni < 4; ++ni) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
 
@@ -96,9 +99,9 @@ __device__ __forceinline__ void mainloop(const Tile& t, double (&acc)[8][4][2], 
         if (s < t.kchunks) load_stage(t, s, smem + (size_t)s * 2 * OPER_ELEMS, smem + (size_t)s * 2 * OPER_ELEMS + OPER_ELEMS, tid);
         cp_async_commit();
     }
-    const int a_off = (warp_m * 64 + g) * SLD + q;
+    const int a_off = (warp_m * WARP_M + g) * SLD + q;
     const int b_off = (warp_n * 32 + g) * SLD + q;
-    double fa[2][8], fb[2][4];
+    double fa[2][MI], fb[2][4];
     cp_async_wait<STAGES - 1>();          // chunk 0 has landed
     __syncthreads();
     load_frags(smem + a_off, smem + OPER_ELEMS + b_off, 0, fa[0], fb[0]);
@@ -132,13 +135,13 @@ __device__ __forceinline__ void mainloop(const Tile& t, double (&acc)[8][4][2], 
 enum Epi { EPI_SUB = 0, EPI_STORE = 1, EPI_STORE_NEG = 2 };
 
 template <int EPI>
-__device__ __forceinline__ void store_tile(double* C, int ldc, const double (&acc)[8][4][2]) {
+__device__ __forceinline__ void store_tile(double* C, int ldc, const double (&acc)[MI][4][2]) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int warp_m = warp >> 2, warp_n = warp & 3;
     const int g = lane >> 2, q = lane & 3;
 #pragma unroll
-    for (int mi = 0; mi < 8; ++mi) {
-        const int row = warp_m * 64 + mi * 8 + g;
+    for (int mi = 0; mi < MI; ++mi) {
+        const int row = warp_m * WARP_M + mi * 8 + g;
 #pragma unroll
         for (int ni = 0; ni < 4; ++ni) {
             const int colx = warp_n * 32 + ni * 8 + q * 2;
@@ -162,7 +165,7 @@ __device__ __forceinline__ void store_tile(double* C, int ldc, const double (&ac
 
 // ---------------------------------------------------------------------------------------------
 // Left-looking Cholesky update of block column J:  A_IJ -= sum_{K<J} L_IK L_JK^T,  I = J + blockIdx.x
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
 k_syrk_update(double* __restrict__ mat, int Np, int J, const unsigned char* __restrict__ active) {
     extern __shared__ double smem[];
     const int p = blockIdx.y;
@@ -170,13 +173,13 @@ k_syrk_update(double* __restrict__ mat, int Np, int J, const unsigned char* __re
     const int I = J + blockIdx.x;
     double* M = mat + (size_t)p * Np * Np;
     Tile t{M + (size_t)I * NB * Np, M + (size_t)J * NB * Np, Np, Np, J * (NB / KC)};
-    double acc[8][4][2];
+    double acc[MI][4][2];
     mainloop(t, acc, smem);
     store_tile<EPI_SUB>(M + (size_t)I * NB * Np + (size_t)J * NB, Np, acc);
 }
 
 // L_IJ = S_IJ * D_J^T  (in place),  I = J + 1 + blockIdx.x
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
 k_trsm_panel(double* __restrict__ mat, int Np, int T, int J, const double* __restrict__ dinv,
              const unsigned char* __restrict__ active) {
     extern __shared__ double smem[];
@@ -185,13 +188,13 @@ k_trsm_panel(double* __restrict__ mat, int Np, int T, int J, const double* __res
     const int I = J + 1 + blockIdx.x;
     double* C = mat + (size_t)p * Np * Np + (size_t)I * NB * Np + (size_t)J * NB;
     Tile t{C, dinv + ((size_t)p * T + J) * NB * NB, Np, NB, NB / KC};
-    double acc[8][4][2];
+    double acc[MI][4][2];
     mainloop(t, acc, smem);     // ends with a block barrier: every read of S_IJ has landed
     store_tile<EPI_STORE>(C, Np, acc);
 }
 
 // Phase 2 panel: Mt[n][r] = sum_j D_J^T[n][j] * L[r][J*NB + j],  r in block J + 1 + blockIdx.x
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
 k_inv_panel(const double* __restrict__ mat, int Np, int T, int J, const double* __restrict__ dinvT,
             double* __restrict__ mt, const unsigned char* __restrict__ active) {
     extern __shared__ double smem[];
@@ -200,13 +203,13 @@ k_inv_panel(const double* __restrict__ mat, int Np, int T, int J, const double* 
     const int R = J + 1 + blockIdx.x;
     const double* M = mat + (size_t)p * Np * Np;
     Tile t{dinvT + ((size_t)p * T + J) * NB * NB, M + (size_t)R * NB * Np + (size_t)J * NB, NB, Np, NB / KC};
-    double acc[8][4][2];
+    double acc[MI][4][2];
     mainloop(t, acc, smem);
     store_tile<EPI_STORE>(mt + (size_t)p * NB * Np + (size_t)R * NB, Np, acc);
 }
 
 // Phase 2 update: W_IJ = - sum_{k in [(J+1)NB, (I+1)NB)} W[I-block][k] * Mt[:, k]^T,  deepest I first
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
 k_inv_update(double* __restrict__ mat, int Np, int T, int J, const double* __restrict__ mt,
              const unsigned char* __restrict__ active) {
     extern __shared__ double smem[];
@@ -216,32 +219,32 @@ k_inv_update(double* __restrict__ mat, int Np, int T, int J, const double* __res
     double* M = mat + (size_t)p * Np * Np;
     Tile t{M + (size_t)I * NB * Np + (size_t)(J + 1) * NB, mt + (size_t)p * NB * Np + (size_t)(J + 1) * NB, Np,
            Np, (I - J) * (NB / KC)};
-    double acc[8][4][2];
+    double acc[MI][4][2];
     mainloop(t, acc, smem);
     store_tile<EPI_STORE_NEG>(M + (size_t)I * NB * Np + (size_t)J * NB, Np, acc);
 }
 
 // Prediction: partial[I][b*NB + n] = sum_{m in block I} ( sum_k W[m][k] * KsT[b*NB + n][k] )^2
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
 k_predict_gemm(const double* __restrict__ W, int Np, int T, const double* __restrict__ KsT, int Bp,
                double* __restrict__ partial) {
     extern __shared__ double smem[];
     const int I = T - 1 - blockIdx.x;
     const int b = blockIdx.y;
     Tile t{W + (size_t)I * NB * Np, KsT + (size_t)b * NB * Np, Np, Np, (I + 1) * (NB / KC)};
-    double acc[8][4][2];
+    double acc[MI][4][2];
     mainloop(t, acc, smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int warp_m = warp >> 2, warp_n = warp & 3;
     const int q = lane & 3;
-    double* red = smem;   // [2][NB]
+    double* red = smem;   // [NB / WARP_M][NB]
 #pragma unroll
     for (int ni = 0; ni < 4; ++ni) {
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             double s = 0.0;
 #pragma unroll
-            for (int mi = 0; mi < 8; ++mi) s = fma(acc[mi][ni][h], acc[mi][ni][h], s);
+            for (int mi = 0; mi < MI; ++mi) s = fma(acc[mi][ni][h], acc[mi][ni][h], s);
             s += __shfl_xor_sync(0xffffffffu, s, 4);
             s += __shfl_xor_sync(0xffffffffu, s, 8);
             s += __shfl_xor_sync(0xffffffffu, s, 16);
@@ -249,8 +252,12 @@ k_predict_gemm(const double* __restrict__ W, int Np, int T, const double* __rest
         }
     }
     __syncthreads();
-    if (threadIdx.x < NB)
-        partial[(size_t)I * Bp + (size_t)b * NB + threadIdx.x] = red[threadIdx.x] + red[NB + threadIdx.x];
+    if (threadIdx.x < NB) {
+        double tot = 0.0;
+#pragma unroll
+        for (int w = 0; w < NB / WARP_M; ++w) tot += red[w * NB + threadIdx.x];
+        partial[(size_t)I * Bp + (size_t)b * NB + threadIdx.x] = tot;
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -268,7 +275,7 @@ int launch_syrk_update(double* mat, int Np, int T, int J, int P, const unsigned 
     static bool done = false;
     if (J == 0) return 0;
     if (ensure_smem(k_syrk_update, done)) return 1;
-    k_syrk_update<<<dim3(T - J, P), 256, GEMM_SMEM_BYTES, st>>>(mat, Np, J, active);
+    k_syrk_update<<<dim3(T - J, P), GEMM_THREADS, GEMM_SMEM_BYTES, st>>>(mat, Np, J, active);
     return check_launch("k_syrk_update");
 }
 
@@ -277,7 +284,7 @@ int launch_trsm_panel(double* mat, int Np, int T, int J, int P, const double* di
     static bool done = false;
     if (J >= T - 1) return 0;
     if (ensure_smem(k_trsm_panel, done)) return 1;
-    k_trsm_panel<<<dim3(T - 1 - J, P), 256, GEMM_SMEM_BYTES, st>>>(mat, Np, T, J, dinv, active);
+    k_trsm_panel<<<dim3(T - 1 - J, P), GEMM_THREADS, GEMM_SMEM_BYTES, st>>>(mat, Np, T, J, dinv, active);
     return check_launch("k_trsm_panel");
 }
 
@@ -286,7 +293,7 @@ int launch_inv_panel(const double* mat, int Np, int T, int J, int P, const doubl
     static bool done = false;
     if (J >= T - 1) return 0;
     if (ensure_smem(k_inv_panel, done)) return 1;
-    k_inv_panel<<<dim3(T - 1 - J, P), 256, GEMM_SMEM_BYTES, st>>>(mat, Np, T, J, dinvT, mt, active);
+    k_inv_panel<<<dim3(T - 1 - J, P), GEMM_THREADS, GEMM_SMEM_BYTES, st>>>(mat, Np, T, J, dinvT, mt, active);
     return check_launch("k_inv_panel");
 }
 
@@ -295,7 +302,7 @@ int launch_inv_update(double* mat, int Np, int T, int J, int P, const double* mt
     static bool done = false;
     if (J >= T - 1) return 0;
     if (ensure_smem(k_inv_update, done)) return 1;
-    k_inv_update<<<dim3(T - 1 - J, P), 256, GEMM_SMEM_BYTES, st>>>(mat, Np, T, J, mt, active);
+    k_inv_update<<<dim3(T - 1 - J, P), GEMM_THREADS, GEMM_SMEM_BYTES, st>>>(mat, Np, T, J, mt, active);
     return check_launch("k_inv_update");
 }
 
@@ -303,7 +310,7 @@ int launch_predict_gemm(const double* W, int Np, int T, const double* KsT, int B
                         cudaStream_t st) {
     static bool done = false;
     if (ensure_smem(k_predict_gemm, done)) return 1;
-    k_predict_gemm<<<dim3(T, Bp / NB), 256, GEMM_SMEM_BYTES, st>>>(W, Np, T, KsT, Bp, partial);
+    k_predict_gemm<<<dim3(T, Bp / NB), GEMM_THREADS, GEMM_SMEM_BYTES, st>>>(W, Np, T, KsT, Bp, partial);
     return check_launch("k_predict_gemm");
 }
 
