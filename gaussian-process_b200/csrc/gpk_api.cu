@@ -71,7 +71,9 @@ int check_launch(const char* what) {
 constexpr int MAX_GROUPS = 8;
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
-BlockedLayout blocked_layout(int P, int N, int d) {
+static int g_precision = 0;    // 0 = native FP64 (DMMA), 1 = emulated FP64 on the int8 tcgen05 tensor cores
+
+BlockedLayout blocked_layout(int P, int N, int d, int emulated) {
     BlockedLayout L{};
     L.P = P; L.N = N; L.d = d;
     L.Np = round_up(N, NB);
@@ -88,27 +90,65 @@ BlockedLayout blocked_layout(int P, int N, int d) {
     L.cn = take((size_t)P * Np * 8);
     L.z = take((size_t)P * Np * 8);
     L.alpha = take((size_t)P * Np * 8);
+    L.oz_slices = L.oz_mt = L.oz_rows = L.oz_mtsc = 0;
+    if (emulated) {
+        L.oz_slices = take((size_t)P * oz_slice_bytes(L.Np));
+        L.oz_mt = take((size_t)P * oz_mt_bytes(L.Np));
+        L.oz_rows = take((size_t)4 * Np * 8);
+        L.oz_mtsc = take((size_t)2 * P * NB * 8);
+    }
     L.total = off;
     return L;
 }
 
+// Buffers of the emulated-FP64 mode (null slices = native FP64 DMMA contractions).
+struct OzBuffers {
+    uint8_t* slices = nullptr;
+    uint8_t* mtslices = nullptr;
+    double *rowsig = nullptr, *rowinv = nullptr, *gam = nullptr, *gaminv = nullptr, *mtsig = nullptr, *mtinv = nullptr;
+};
+
+static OzBuffers oz_buffers(char* ws, const BlockedLayout& L) {
+    OzBuffers o;
+    if (!L.oz_slices && !L.oz_rows) return o;
+    o.slices = (uint8_t*)(ws + L.oz_slices);
+    o.mtslices = (uint8_t*)(ws + L.oz_mt);
+    double* r = (double*)(ws + L.oz_rows);
+    o.rowsig = r; o.rowinv = r + L.Np; o.gam = r + 2 * (size_t)L.Np; o.gaminv = r + 3 * (size_t)L.Np;
+    double* m = (double*)(ws + L.oz_mtsc);
+    o.mtsig = m; o.mtinv = m + (size_t)L.P * NB;
+    return o;
+}
+
 // Blocked left-looking Cholesky (phase 1).  mode: what the diagonal kernel leaves in the diagonal blocks.
 static int factor_phase(double* mat, int Np, int T, int P, double* dinv, double* dinvT, int* info,
-                        const unsigned char* active, int mode, cudaStream_t st) {
+                        const unsigned char* active, int mode, const OzBuffers& oz, cudaStream_t st) {
     for (int J = 0; J < T; ++J) {
-        if (launch_syrk_update(mat, Np, T, J, P, active, st)) return 1;
+        if (oz.slices) {
+            if (launch_oz_syrk(mat, Np, T, J, P, oz.slices, oz.rowsig, active, st)) return 1;
+        } else {
+            if (launch_syrk_update(mat, Np, T, J, P, active, st)) return 1;
+        }
         if (launch_diag_block(mat, Np, J, P, dinv, dinvT, T, info, active, mode, st)) return 1;
         if (launch_trsm_panel(mat, Np, T, J, P, dinv, active, st)) return 1;
+        if (oz.slices && launch_oz_slice_l(mat, Np, T, J, P, oz.rowinv, oz.slices, active, st)) return 1;
     }
     return 0;
 }
 
 // Blocked triangular inverse (phase 2), in place: L (with D_I already in the diagonal blocks) -> W = L^-1.
 static int inverse_phase(double* mat, int Np, int T, int P, const double* dinvT, double* mt,
-                         const unsigned char* active, cudaStream_t st) {
+                         const unsigned char* active, const OzBuffers& oz, cudaStream_t st) {
+    if (oz.slices && launch_oz_slice_w(mat, Np, T, 0, 1, P, oz.gam, oz.slices, active, st)) return 1;
     for (int J = T - 2; J >= 0; --J) {
         if (launch_inv_panel(mat, Np, T, J, P, dinvT, mt, active, st)) return 1;
-        if (launch_inv_update(mat, Np, T, J, P, mt, active, st)) return 1;
+        if (oz.slices) {
+            if (launch_oz_mt(mt, Np, T, J, P, oz.gaminv, oz.mtsig, oz.mtinv, oz.mtslices, active, st)) return 1;
+            if (launch_oz_invu(mat, Np, T, J, P, oz.slices, oz.mtslices, oz.mtsig, active, st)) return 1;
+            if (J > 0 && launch_oz_slice_w(mat, Np, T, J, 0, P, oz.gam, oz.slices, active, st)) return 1;
+        } else {
+            if (launch_inv_update(mat, Np, T, J, P, mt, active, st)) return 1;
+        }
     }
     return 0;
 }
@@ -173,14 +213,14 @@ int gpk_potrf_batched(double* K_inout, int P, int Np, int* info, void* workspace
     double* dinv = (double*)workspace;
     double* dinvT = (double*)((char*)workspace + align256((size_t)P * T * NB * NB * 8));
     if (cudaMemsetAsync(info, 0, (size_t)P * sizeof(int), st) != cudaSuccess) { set_error("memset info failed"); return 1; }
-    return factor_phase(K_inout, Np, T, P, dinv, dinvT, info, nullptr, DIAG_WRITE_FACTOR, st);
+    return factor_phase(K_inout, Np, T, P, dinv, dinvT, info, nullptr, DIAG_WRITE_FACTOR, OzBuffers{}, st);
 }
 
 size_t gpk_loss_workspace_bytes(int P, int N, int d) {
     if (N <= SMALL_N_MAX) return 256;
     size_t best = 0;                      // enough for any particle-group split (gpk_set_groups)
     for (int G = 1; G <= MAX_GROUPS; ++G) {
-        const size_t b = (size_t)G * blocked_layout((P + G - 1) / G, N, d).total;
+        const size_t b = (size_t)G * blocked_layout((P + G - 1) / G, N, d, g_precision).total;
         if (b > best) best = b;
     }
     return best;
@@ -200,20 +240,21 @@ int gpk_loss_batched(const double* X, const double* y, const double* e, const do
     // blocked path: waves of as many particles as the workspace holds, each wave split into independent
     // particle groups on concurrent streams (the chain SYRK -> diag -> TRSM of one group is serial; kernels of
     // other groups fill its wave tails and hide the latency-bound diagonal kernel)
-    const size_t per1 = blocked_layout(1, N, d).total;
+    const int emu = g_precision;
+    const size_t per1 = blocked_layout(1, N, d, emu).total;
     if (workspace == nullptr || workspace_bytes < per1) { set_error("gpk_loss_batched: workspace too small (%zu < %zu)", workspace_bytes, per1); return 3; }
     int G = g_timing ? 1 : g_groups;
     if (G > P / 8) G = P / 8;
     if (G < 1) G = 1;
     if (G > 1 && ensure_group_streams(G)) return 1;
-    auto fits = [&](int pw) { const int pg = (pw + G - 1) / G; return (size_t)G * blocked_layout(pg, N, d).total <= workspace_bytes; };
+    auto fits = [&](int pw) { const int pg = (pw + G - 1) / G; return (size_t)G * blocked_layout(pg, N, d, emu).total <= workspace_bytes; };
     int Pw = P;
     while (Pw > 1 && !fits(Pw)) { --Pw; }
     if (!fits(Pw)) { G = 1; Pw = 1; }
     for (int p0 = 0; p0 < P; p0 += Pw) {
         const int Pwave = (P - p0 < Pw) ? (P - p0) : Pw;
         const int pg = (Pwave + G - 1) / G;
-        const size_t gbytes = blocked_layout(pg, N, d).total;
+        const size_t gbytes = blocked_layout(pg, N, d, emu).total;
         if (G > 1 && cudaEventRecord(g_fork, st) != cudaSuccess) { set_error("fork event failed"); return 1; }
         for (int g = 0; g < G; ++g) {
             const int q0 = p0 + g * pg;
@@ -221,8 +262,10 @@ int gpk_loss_batched(const double* X, const double* y, const double* e, const do
             if (Pc <= 0) break;
             cudaStream_t gs = (G > 1) ? g_group_streams[g] : st;
             if (G > 1) cudaStreamWaitEvent(gs, g_fork, 0);
-            const BlockedLayout L = blocked_layout(Pc, N, d);
+            const BlockedLayout L = blocked_layout(Pc, N, d, emu);
             char* ws = (char*)workspace + (size_t)g * gbytes;
+            const OzBuffers oz = oz_buffers(ws, L);
+            if (emu && launch_oz_prep(e, N, L.Np, oz.rowsig, oz.rowinv, oz.gam, oz.gaminv, gs)) return 1;
             double* mat = (double*)(ws + L.mat);
             double* dinv = (double*)(ws + L.dinv);
             double* dinvT = (double*)(ws + L.dinvT);
@@ -236,8 +279,8 @@ int gpk_loss_batched(const double* X, const double* y, const double* e, const do
             const double* lsp = ls + (size_t)q0 * d;
             if (launch_scale_points(X, lsp, Pc, N, L.Np, d, xs, sq, act, gs)) return 1;
             if (launch_cov_lower(xs, sq, e, Pc, N, L.Np, d, mat, act, gs)) return 1;
-            if (factor_phase(mat, L.Np, L.T, Pc, dinv, dinvT, info + q0, act, DIAG_WRITE_INVERSE, gs)) return 1;
-            if (inverse_phase(mat, L.Np, L.T, Pc, dinvT, mt, act, gs)) return 1;
+            if (factor_phase(mat, L.Np, L.T, Pc, dinv, dinvT, info + q0, act, DIAG_WRITE_INVERSE, oz, gs)) return 1;
+            if (inverse_phase(mat, L.Np, L.T, Pc, dinvT, mt, act, oz, gs)) return 1;
             if (launch_wy(mat, L.Np, N, Pc, y, z, act, gs)) return 1;
             if (launch_colnorm_alpha(mat, L.Np, Pc, z, cn, alpha, act, gs)) return 1;
             if (launch_counts(alpha, cn, e, sigma_vals, Pc, N, L.Np, S, counts_out + (size_t)q0 * S,
@@ -255,7 +298,10 @@ int gpk_loss_batched(const double* X, const double* y, const double* e, const do
 size_t gpk_fit_workspace_bytes(int N, int d) {
     (void)d;
     const size_t Np = round_up(N, NB), T = Np / NB;
-    return 2 * align256(T * NB * NB * 8) + align256(NB * Np * 8) + 2 * align256(Np * 8);
+    size_t b = 2 * align256(T * NB * NB * 8) + align256(NB * Np * 8) + 2 * align256(Np * 8);
+    if (g_precision)
+        b += align256(oz_slice_bytes((int)Np)) + align256(oz_mt_bytes((int)Np)) + align256(4 * Np * 8) + align256(2 * NB * 8);
+    return b;
 }
 
 int gpk_fit(const double* X, const double* y, const double* e, const double* ls, int N, int d, double* W_out,
@@ -272,12 +318,21 @@ int gpk_fit(const double* X, const double* y, const double* e, const double* ls,
     double* dinvT = (double*)(ws + off); off += align256((size_t)T * NB * NB * 8);
     double* mt = (double*)(ws + off); off += align256((size_t)NB * Np * 8);
     double* z = (double*)(ws + off); off += align256((size_t)Np * 8);
-    double* cn = (double*)(ws + off);
+    double* cn = (double*)(ws + off); off += align256((size_t)Np * 8);
+    OzBuffers oz;
+    if (g_precision) {
+        oz.slices = (uint8_t*)(ws + off); off += align256(oz_slice_bytes(Np));
+        oz.mtslices = (uint8_t*)(ws + off); off += align256(oz_mt_bytes(Np));
+        double* r = (double*)(ws + off); off += align256((size_t)4 * Np * 8);
+        oz.rowsig = r; oz.rowinv = r + Np; oz.gam = r + 2 * (size_t)Np; oz.gaminv = r + 3 * (size_t)Np;
+        oz.mtsig = (double*)(ws + off); oz.mtinv = oz.mtsig + NB;
+        if (launch_oz_prep(e, N, Np, oz.rowsig, oz.rowinv, oz.gam, oz.gaminv, st)) return 1;
+    }
     if (cudaMemsetAsync(info, 0, sizeof(int), st) != cudaSuccess) { set_error("memset info failed"); return 1; }
     if (launch_scale_points(X, ls, 1, N, Np, d, xs_out, sq_out, nullptr, st)) return 1;
     if (launch_cov_lower(xs_out, sq_out, e, 1, N, Np, d, W_out, nullptr, st)) return 1;
-    if (factor_phase(W_out, Np, T, 1, dinv, dinvT, info, nullptr, DIAG_WRITE_INVERSE, st)) return 1;
-    if (inverse_phase(W_out, Np, T, 1, dinvT, mt, nullptr, st)) return 1;
+    if (factor_phase(W_out, Np, T, 1, dinv, dinvT, info, nullptr, DIAG_WRITE_INVERSE, oz, st)) return 1;
+    if (inverse_phase(W_out, Np, T, 1, dinvT, mt, nullptr, oz, st)) return 1;
     if (launch_wy(W_out, Np, N, 1, y, z, nullptr, st)) return 1;
     if (launch_colnorm_alpha(W_out, Np, 1, z, cn, alpha_out, nullptr, st)) return 1;
     return 0;
@@ -321,6 +376,29 @@ int gpk_sum_gaussians(const double* y, int n, const double* gaus, int ng, double
                       void* stream) {
     set_stream((cudaStream_t)stream);
     return launch_sum_gaussians(y, n, gaus, ng, half_dy, p_out, (cudaStream_t)stream);
+}
+
+int gpk_set_precision(int mode) {
+    if (mode != 0 && mode != 1) { set_error("gpk_set_precision: 0 (native FP64) or 1 (emulated FP64 on int8 tensor cores)"); return 2; }
+    g_precision = mode;
+    return 0;
+}
+int gpk_get_precision(void) { return g_precision; }
+
+size_t gpk_oz_slice_bytes(int rows, int cols) { return (size_t)(rows / NB) * (cols / 32) * (oz_mt_bytes(32)); }
+
+int gpk_oz_slice(const double* src, int ld, int rows, int cols, const double* rowinv, void* dst, void* stream) {
+    if (rows < NB || rows % NB || cols < NB || cols % NB) { set_error("gpk_oz_slice: rows and cols must be positive multiples of %d", NB); return 2; }
+    set_stream((cudaStream_t)stream);
+    return launch_oz_slice_generic(src, ld, rows, cols, rowinv, (uint8_t*)dst, (cudaStream_t)stream);
+}
+
+int gpk_oz_gemm_tn(const void* A, const void* B, int M, int N, int K, const double* sa, const double* sb, double* C,
+                   int ldc, int* dbg, unsigned int idesc, unsigned long long sdesc, void* stream) {
+    if (M < NB || M % NB || N < NB || N % NB || K < NB || K % NB) { set_error("gpk_oz_gemm_tn: M, N, K must be positive multiples of %d", NB); return 2; }
+    set_stream((cudaStream_t)stream);
+    return launch_oz_gemm_tn((const uint8_t*)A, (const uint8_t*)B, M, N, K, sa, sb, C, ldc, dbg, idesc, sdesc,
+                             (cudaStream_t)stream);
 }
 
 int gpk_set_groups(int groups) {

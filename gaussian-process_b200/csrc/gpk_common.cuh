@@ -31,9 +31,14 @@ struct BlockedLayout {
     size_t cn;       // [P][Np]        column sums of squares of W  (= diag K^-1)
     size_t z;        // [P][Np]        W y
     size_t alpha;    // [P][Np]        W^T z = K^-1 y
+    // emulated-FP64 (int8 digit) mode only, gpk_oz.cu:
+    size_t oz_slices;  // [P] digit records of L (phase 1) then W gamma (phase 2), oz_slice_bytes(Np) each
+    size_t oz_mt;      // [P] digit records of the phase-2 panel, oz_mt_bytes(Np) each
+    size_t oz_rows;    // [4][Np]   rowsig, rowinv, gamma, 1/gamma (particle independent)
+    size_t oz_mtsc;    // [2][P][NB] row scales of the phase-2 panel and their inverses
     size_t total;
 };
-BlockedLayout blocked_layout(int P, int N, int d);
+BlockedLayout blocked_layout(int P, int N, int d, int emulated);
 
 // ---- kernels launchers (implemented across the .cu files) ---------------------------------
 // gpk_cov.cu
@@ -62,6 +67,26 @@ int launch_inv_update(double* mat, int Np, int T, int J, int P, const double* mt
                       const unsigned char* active, cudaStream_t st);
 int launch_predict_gemm(const double* W, int Np, int T, const double* KsT, int Bp, double* partial,
                         cudaStream_t st);
+
+// gpk_oz.cu -- emulated FP64 on tcgen05 int8 tensor cores
+size_t oz_slice_bytes(int Np);
+size_t oz_mt_bytes(int Np);
+int launch_oz_prep(const double* e, int N, int Np, double* rowsig, double* rowinv, double* gam, double* gaminv,
+                   cudaStream_t st);
+int launch_oz_syrk(double* mat, int Np, int T, int J, int P, const uint8_t* slices, const double* rowsig,
+                   const unsigned char* active, cudaStream_t st);
+int launch_oz_slice_l(const double* mat, int Np, int T, int J, int P, const double* rowinv, uint8_t* slices,
+                      const unsigned char* active, cudaStream_t st);
+int launch_oz_slice_w(const double* mat, int Np, int T, int J, int diag, int P, const double* gam, uint8_t* slices,
+                      const unsigned char* active, cudaStream_t st);
+int launch_oz_mt(const double* mt, int Np, int T, int J, int P, const double* gaminv, double* mtsig, double* mtinv,
+                 uint8_t* mtslices, const unsigned char* active, cudaStream_t st);
+int launch_oz_invu(double* mat, int Np, int T, int J, int P, const uint8_t* slices, const uint8_t* mtslices,
+                   const double* mtsig, const unsigned char* active, cudaStream_t st);
+int launch_oz_slice_generic(const double* src, int ld, int rows, int cols, const double* rowinv, uint8_t* dst,
+                            cudaStream_t st);
+int launch_oz_gemm_tn(const uint8_t* A, const uint8_t* B, int M, int N, int K, const double* sa, const double* sb,
+                      double* C, int ldc, int* dbg, uint32_t idesc, uint64_t sdesc, cudaStream_t st);
 
 // gpk_loss.cu
 int launch_small_loss(const double* X, const double* y, const double* e, const double* ls,

@@ -1,0 +1,526 @@
+// Emulated-FP64 contractions on the 5th-generation tensor cores (tcgen05 / TMEM), sm_100a.
+//
+// sm_100a has no FP64 kind of tcgen05.mma; the FP64 tensor instruction is the warp-level DMMA (37 TFLOP/s, see
+// gpk_gemm.cu).  The two contractions that make up 85 % of a loss evaluation (GP_func.py:22 Cholesky trailing
+// updates and GP_func.py:38 the N-right-hand-side solve, restated as a triangular inverse) are instead computed
+// here by an error-free split of each FP64 operand into OZ_NS = 7 signed 8-bit digits (Ozaki scheme):
+//
+//     x = sigma * u,  |u| <= 1/2,  sigma a power of two (row scale; a-priori bounds, see the slicers)
+//     v = rint(u * 2^55) = sum_s b_s 2^(48 - 8 s),   b_s in [-128, 127]   (balanced digits: bytes of v + 0x..8080)
+//     <x_a, x_b> = sigma_a sigma_b 2^-14 sum_g 2^(-8 g) acc_g,   acc_g = sum_k sum_{s+t=g} b_s[a,k] b_t[b,k]
+//
+// acc_g are exact int32 sums produced by tcgen05.mma.kind::i8; the 28 digit products with g = s+t <= 6 are kept
+// (the dropped ones are mean-zero and below 2^-50 of the row scales, the rounding level of an FP64 dot product of
+// this length).  7 accumulators x 64 columns live in TMEM for one 128 x 64 output tile; the epilogue rebuilds the
+// FP64 value with two fused multiply-adds and applies it to the FP64 matrix in HBM.
+//
+// Operand storage ("sliced matrix"): for every 128-row block and every 32-wide K chunk one 28 KB record
+//     [16 row groups][7 digits][2 k-halves][8 rows][16 bytes]
+// which is exactly the shared-memory image tcgen05.mma reads through a no-swizzle K-major descriptor
+// (core matrix = 8 rows x 16 B, LBO = 128 B between the k-halves, SBO = 1792 B between row groups), so a pipeline
+// stage is filled by two plain bulk copies (cp.async.bulk, one elected thread) and needs no tensor map.
+#include "gpk_common.cuh"
+
+namespace gpk {
+
+constexpr int OZ_NS = 7;                        // int8 digits per FP64 value
+constexpr int OZ_RG = OZ_NS * 256;              // bytes of one 8-row group (all digits, 32 k)
+constexpr int OZ_CHUNK = 16 * OZ_RG;            // 128 rows x 32 k x 7 digits = 28672 B
+constexpr int OZ_HALF = 8 * OZ_RG;              // 64 rows
+constexpr int OZ_STAGE = OZ_CHUNK + OZ_HALF;    // A (128 rows) + B (64 rows)
+constexpr int OZ_STAGES = 5;
+constexpr int OZ_THREADS = 192;                 // warp 0 producer, warp 1 MMA issuer, warps 2..5 epilogue
+constexpr int OZ_TMEM_COLS = 512;
+constexpr int OZ_TILE_N = 64;
+constexpr size_t OZ_SMEM_BYTES = (size_t)OZ_STAGES * OZ_STAGE + 128;
+constexpr long long OZ_BIAS = 0x0000808080808080LL;
+// kind::i8, D = S32, A = B = signed 8 bit, both K-major, N = 64, M = 128
+constexpr uint32_t OZ_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((OZ_TILE_N >> 3) << 17) | ((128u >> 4) << 24);
+// no-swizzle K-major shared-memory descriptor without the start address: LBO = 128 B, SBO = OZ_RG, version 1
+constexpr uint64_t OZ_SDESC = ((uint64_t)(128 >> 4) << 16) | ((uint64_t)(OZ_RG >> 4) << 32) | (1ull << 46);
+
+// ---- PTX wrappers ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n.reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n}\n"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+// A wait that can never hang the device: a barrier that does not complete within ~2 s traps the kernel.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    if (mbar_try_wait(bar, parity)) return;
+    const long long t0 = clock64();
+    while (!mbar_try_wait(bar, parity)) {
+        if (clock64() - t0 > 4000000000LL) __trap();
+    }
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                        uint32_t accumulate) {
+    asm volatile(
+        "{\n.reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n}\n" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];\n"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory"); }
+
+// exact int64 -> double for |v| < 2^51 without the slow I2F path
+__device__ __forceinline__ double ll2d_exact(long long v) {
+    return __longlong_as_double(0x4338000000000000LL + v) - 6755399441055744.0;
+}
+
+enum OzEpi { OZ_SUB = 0, OZ_STORE = 1, OZ_STORE_NEG = 2 };
+
+struct OzTile {
+    const uint8_t* a;     // first chunk of the A row block (128 rows), chunks are consecutive in K
+    const uint8_t* b;     // first chunk of the B half block (64 rows): chunk base + half * OZ_HALF
+    int nk;               // number of 32-wide K chunks
+    double* c;            // &C[row0][col0] of the 128 x 64 FP64 tile
+    int ldc;
+    const double* sa;     // row scales sigma of the 128 A rows, or nullptr
+    double sa_const;      // multiplies every row scale (use it alone when sa == nullptr)
+    const double* sb;     // scales of the 64 B rows, or nullptr (= 1)
+    int* dbg;             // optional raw accumulator dump [7][128][64]
+    uint32_t idesc;
+    uint64_t sdesc;
+};
+
+// One 128 x 64 output tile per CTA.
+template <int EPI>
+__device__ __forceinline__ void oz_tile(const OzTile& t, uint8_t* smem) {
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    uint8_t* ctrl = smem + (size_t)OZ_STAGES * OZ_STAGE;
+    const uint32_t full0 = smem_u32(ctrl);                 // OZ_STAGES x 8 B
+    const uint32_t empty0 = full0 + 8 * OZ_STAGES;         // OZ_STAGES x 8 B
+    const uint32_t accbar = empty0 + 8 * OZ_STAGES;        // 8 B
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(ctrl + 8 * (2 * OZ_STAGES + 1));
+    const uint32_t stage0 = smem_u32(smem);
+
+    if (tid == 0) {
+        for (int s = 0; s < OZ_STAGES; ++s) {
+            mbar_init(full0 + 8 * s, 1);
+            mbar_init(empty0 + 8 * s, 1);
+        }
+        mbar_init(accbar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(
+                         smem_u32((const void*)tmem_slot)),
+                     "r"((uint32_t)OZ_TMEM_COLS)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int k = 0; k < t.nk; ++k) {
+                const int s = k % OZ_STAGES;
+                const uint32_t ph = (uint32_t)(k / OZ_STAGES) & 1u;
+                mbar_wait(empty0 + 8 * s, ph ^ 1u);
+                mbar_expect_tx(full0 + 8 * s, OZ_STAGE);
+                bulk_g2s(stage0 + s * OZ_STAGE, t.a + (size_t)k * OZ_CHUNK, OZ_CHUNK, full0 + 8 * s);
+                bulk_g2s(stage0 + s * OZ_STAGE + OZ_CHUNK, t.b + (size_t)k * OZ_CHUNK, OZ_HALF, full0 + 8 * s);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            for (int k = 0; k < t.nk; ++k) {
+                const int s = k % OZ_STAGES;
+                const uint32_t ph = (uint32_t)(k / OZ_STAGES) & 1u;
+                mbar_wait(full0 + 8 * s, ph);
+                tc_fence_after();
+                const uint64_t da = t.sdesc | (uint64_t)(((stage0 + s * OZ_STAGE) >> 4) & 0x3FFF);
+                const uint64_t db = t.sdesc | (uint64_t)(((stage0 + s * OZ_STAGE + OZ_CHUNK) >> 4) & 0x3FFF);
+#pragma unroll
+                for (int g = 0; g < OZ_NS; ++g) {
+#pragma unroll
+                    for (int sa = 0; sa <= g; ++sa) {
+                        const int sb = g - sa;
+                        umma_i8(tmem + g * OZ_TILE_N, da + (uint64_t)(sa * (256 >> 4)), db + (uint64_t)(sb * (256 >> 4)),
+                                t.idesc, (k > 0 || sa > 0) ? 1u : 0u);
+                    }
+                }
+                umma_commit(empty0 + 8 * s);     // frees the stage when these MMAs have read it
+            }
+            umma_commit(accbar);                 // accumulators complete
+        }
+    } else {
+        // epilogue warps 2..5: TMEM lane quadrant = warp % 4, one output row per thread
+        const int q = warp & 3;
+        const int row = q * 32 + lane;
+        mbar_wait(accbar, 0);
+        tc_fence_after();
+        const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16);
+        const double rs = (t.sa ? t.sa[row] : 1.0) * t.sa_const * 0x1p-14;
+        double* crow = t.c + (size_t)row * t.ldc;
+#pragma unroll 1
+        for (int cc = 0; cc < OZ_TILE_N; cc += 8) {
+            uint32_t a[OZ_NS][8];
+#pragma unroll
+            for (int g = 0; g < OZ_NS; ++g) tmem_ld8(taddr + g * OZ_TILE_N + cc, a[g]);
+            tmem_wait_ld();
+            if (t.dbg) {
+#pragma unroll
+                for (int g = 0; g < OZ_NS; ++g)
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) t.dbg[(g * 128 + row) * OZ_TILE_N + cc + j] = (int)a[g][j];
+            }
+            double v[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const long long hi = ((long long)(int)a[0][j] << 16) + ((long long)(int)a[1][j] << 8) + (long long)(int)a[2][j];
+                const long long mid = ((long long)(int)a[3][j] << 16) + ((long long)(int)a[4][j] << 8) + (long long)(int)a[5][j];
+                const long long lo = (long long)(int)a[6][j];
+                double x = fma(ll2d_exact(mid), 0x1p-40, ll2d_exact(lo) * 0x1p-48);
+                x = fma(ll2d_exact(hi), 0x1p-16, x);
+                const double sc = rs * (t.sb ? t.sb[cc + j] : 1.0);
+                v[j] = x * sc;
+            }
+            double2* cp = reinterpret_cast<double2*>(crow + cc);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                double2 o;
+                if (EPI == OZ_SUB) {
+                    o = cp[j];
+                    o.x -= v[2 * j];
+                    o.y -= v[2 * j + 1];
+                } else if (EPI == OZ_STORE) {
+                    o.x = v[2 * j];
+                    o.y = v[2 * j + 1];
+                } else {
+                    o.x = -v[2 * j];
+                    o.y = -v[2 * j + 1];
+                }
+                cp[j] = o;
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem), "r"((uint32_t)OZ_TMEM_COLS)
+                     : "memory");
+    }
+}
+
+// ---- kernels ----------------------------------------------------------------------------------------------
+// Left-looking Cholesky update of block column J: A_IJ -= sum_{K<J} L_IK L_JK^T from the digit slices of L.
+// blockIdx.x = 2 * (I - J) + half, blockIdx.y = particle.
+__global__ void __launch_bounds__(OZ_THREADS, 1)
+k_oz_syrk(double* __restrict__ mat, int Np, int J, const uint8_t* __restrict__ slices, size_t slice_stride,
+          const double* __restrict__ rowsig, const unsigned char* __restrict__ active) {
+    extern __shared__ __align__(128) uint8_t oz_smem[];
+    const int p = blockIdx.y;
+    if (active && !active[p]) return;
+    const int I = J + (blockIdx.x >> 1), h = blockIdx.x & 1;
+    const int kch = Np / 32;
+    const uint8_t* S = slices + (size_t)p * slice_stride;
+    OzTile t;
+    t.a = S + (size_t)I * kch * OZ_CHUNK;
+    t.b = S + (size_t)J * kch * OZ_CHUNK + (size_t)h * OZ_HALF;
+    t.nk = 4 * J;
+    t.c = mat + (size_t)p * Np * Np + (size_t)I * NB * Np + (size_t)J * NB + h * OZ_TILE_N;
+    t.ldc = Np;
+    t.sa = rowsig + I * NB;
+    t.sa_const = 1.0;
+    t.sb = rowsig + J * NB + h * OZ_TILE_N;
+    t.dbg = nullptr;
+    t.idesc = OZ_IDESC;
+    t.sdesc = OZ_SDESC;
+    oz_tile<OZ_SUB>(t, oz_smem);
+}
+
+// Phase-2 update W_IJ = - sum_{k in [(J+1)NB, (I+1)NB)} (W gamma)[I-block][k] * (Mt / gamma)[:, k]^T.
+// blockIdx.x = 2 * (T - 1 - I) + half (deepest contraction first), blockIdx.y = particle.
+__global__ void __launch_bounds__(OZ_THREADS, 1)
+k_oz_invu(double* __restrict__ mat, int Np, int T, int J, const uint8_t* __restrict__ slices, size_t slice_stride,
+          const uint8_t* __restrict__ mtslices, size_t mt_stride, const double* __restrict__ mtsig,
+          const unsigned char* __restrict__ active) {
+    extern __shared__ __align__(128) uint8_t oz_smem[];
+    const int p = blockIdx.y;
+    if (active && !active[p]) return;
+    const int I = T - 1 - (blockIdx.x >> 1), h = blockIdx.x & 1;
+    const int kch = Np / 32;
+    OzTile t;
+    t.a = slices + (size_t)p * slice_stride + ((size_t)I * kch + 4 * (J + 1)) * OZ_CHUNK;
+    t.b = mtslices + (size_t)p * mt_stride + (size_t)(4 * (J + 1)) * OZ_CHUNK + (size_t)h * OZ_HALF;
+    t.nk = 4 * (I - J);
+    t.c = mat + (size_t)p * Np * Np + (size_t)I * NB * Np + (size_t)J * NB + h * OZ_TILE_N;
+    t.ldc = Np;
+    t.sa = nullptr;
+    t.sa_const = 2.0;                              // W gamma is sliced with sigma = 2
+    t.sb = mtsig + (size_t)p * NB + h * OZ_TILE_N;
+    t.dbg = nullptr;
+    t.idesc = OZ_IDESC;
+    t.sdesc = OZ_SDESC;
+    oz_tile<OZ_STORE_NEG>(t, oz_smem);
+}
+
+// Generic C = A B^T over sliced operands (test / library primitive): grid (N / 64, M / 128).
+__global__ void __launch_bounds__(OZ_THREADS, 1)
+k_oz_gemm_tn(const uint8_t* __restrict__ A, const uint8_t* __restrict__ B, int kch, const double* __restrict__ sa,
+             const double* __restrict__ sb, double* __restrict__ C, int ldc, int* dbg, uint32_t idesc, uint64_t sdesc) {
+    extern __shared__ __align__(128) uint8_t oz_smem[];
+    const int nb = blockIdx.x, mb = blockIdx.y;
+    OzTile t;
+    t.a = A + (size_t)mb * kch * OZ_CHUNK;
+    t.b = B + (size_t)(nb >> 1) * kch * OZ_CHUNK + (size_t)(nb & 1) * OZ_HALF;
+    t.nk = kch;
+    t.c = C + (size_t)mb * NB * ldc + (size_t)nb * OZ_TILE_N;
+    t.ldc = ldc;
+    t.sa = sa ? sa + mb * NB : nullptr;
+    t.sa_const = 1.0;
+    t.sb = sb ? sb + nb * OZ_TILE_N : nullptr;
+    t.dbg = dbg ? dbg + ((size_t)mb * gridDim.x + nb) * (OZ_NS * 128 * OZ_TILE_N) : nullptr;
+    t.idesc = idesc;
+    t.sdesc = sdesc;
+    oz_tile<OZ_STORE>(t, oz_smem);
+}
+
+// ---- slicers: FP64 128 x 128 tile -> 4 chunk records ----------------------------------------------------------
+__device__ __forceinline__ uint32_t pack_digit(const uint32_t* w, int b) {
+    const uint32_t sel = (uint32_t)b | ((uint32_t)(4 + b) << 4);
+    const uint32_t t0 = __byte_perm(w[0], w[1], sel);
+    const uint32_t t1 = __byte_perm(w[2], w[3], sel);
+    return __byte_perm(t0, t1, 0x5410);
+}
+
+// u = x * rs[row] * rconst * cs[col];  |u| <= 1/2 is the caller's contract (a-priori bounds / measured maxima)
+__device__ __forceinline__ void oz_slice_tile(const double* __restrict__ src, int ld, const double* __restrict__ rs,
+                                              double rconst, const double* __restrict__ cs, uint8_t* __restrict__ dst) {
+    for (int unit = threadIdx.x; unit < 1024; unit += blockDim.x) {
+        const int kcl = unit >> 8, rg = (unit >> 4) & 15, kg = (unit >> 3) & 1, r8 = unit & 7;
+        const int row = rg * 8 + r8, col0 = kcl * 32 + kg * 16;
+        const double2* s2 = reinterpret_cast<const double2*>(src + (size_t)row * ld + col0);
+        const double rsv = (rs ? rs[row] : 1.0) * rconst * 0x1p55;
+        uint32_t lo[16], hi[16];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const double2 x = s2[j];
+            double u0 = x.x * rsv, u1 = x.y * rsv;
+            if (cs) {
+                u0 *= cs[col0 + 2 * j];
+                u1 *= cs[col0 + 2 * j + 1];
+            }
+            const long long v0 = (__double2ll_rn(u0) + OZ_BIAS) ^ OZ_BIAS;
+            const long long v1 = (__double2ll_rn(u1) + OZ_BIAS) ^ OZ_BIAS;
+            lo[2 * j] = (uint32_t)v0;
+            hi[2 * j] = (uint32_t)(v0 >> 32);
+            lo[2 * j + 1] = (uint32_t)v1;
+            hi[2 * j + 1] = (uint32_t)(v1 >> 32);
+        }
+        uint8_t* d = dst + (size_t)kcl * OZ_CHUNK + rg * OZ_RG + kg * 128 + r8 * 16;
+#pragma unroll
+        for (int s = 0; s < OZ_NS; ++s) {
+            const int bytepos = 6 - s;                 // digit s = byte (6 - s) of the biased fixed-point word
+            const uint32_t* w = (bytepos >= 4) ? hi : lo;
+            const int b = bytepos & 3;
+            uint4 o;
+            o.x = pack_digit(w + 0, b);
+            o.y = pack_digit(w + 4, b);
+            o.z = pack_digit(w + 8, b);
+            o.w = pack_digit(w + 12, b);
+            *reinterpret_cast<uint4*>(d + s * 256) = o;
+        }
+    }
+}
+
+// particle-independent scales: row bound of L (|L_ik| <= sqrt(K_ii) = sqrt(1 + e_i^2)) and the column scaling
+// gamma_k = 2^floor(log2 e_k) of W = L^-1 (|W_ik| <= 1 / e_k because K >= diag(e^2))
+__global__ void k_oz_prep(const double* __restrict__ e, int N, int Np, double* __restrict__ rowsig,
+                          double* __restrict__ rowinv, double* __restrict__ gam, double* __restrict__ gaminv) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= Np) return;
+    double sig = 4.0, g = 1.0;
+    if (i < N) {
+        const double ei = fabs(e[i]);
+        sig = scalbn(1.0, ilogb(sqrt(1.0 + ei * ei)) + 2);
+        g = scalbn(1.0, ilogb(ei));
+    }
+    rowsig[i] = sig;
+    rowinv[i] = 1.0 / sig;
+    gam[i] = g;
+    gaminv[i] = 1.0 / g;
+}
+
+// digits of the block column J of L (rows below the diagonal block): blockIdx.x -> I = J + 1 + bx
+__global__ void __launch_bounds__(256)
+k_oz_slice_l(const double* __restrict__ mat, int Np, int J, const double* __restrict__ rowinv,
+             uint8_t* __restrict__ slices, size_t slice_stride, const unsigned char* __restrict__ active) {
+    const int p = blockIdx.y;
+    if (active && !active[p]) return;
+    const int I = J + 1 + blockIdx.x;
+    const int kch = Np / 32;
+    oz_slice_tile(mat + (size_t)p * Np * Np + (size_t)I * NB * Np + (size_t)J * NB, Np, rowinv + I * NB, 1.0, nullptr,
+                  slices + (size_t)p * slice_stride + ((size_t)I * kch + 4 * J) * OZ_CHUNK);
+}
+
+// digits of W gamma / 2: diag != 0 -> diagonal blocks I = 1 + bx; else block column J, rows I = J + 1 + bx
+__global__ void __launch_bounds__(256)
+k_oz_slice_w(const double* __restrict__ mat, int Np, int J, int diag, const double* __restrict__ gam,
+             uint8_t* __restrict__ slices, size_t slice_stride, const unsigned char* __restrict__ active) {
+    const int p = blockIdx.y;
+    if (active && !active[p]) return;
+    const int I = diag ? 1 + blockIdx.x : J + 1 + blockIdx.x;
+    const int Jc = diag ? I : J;
+    const int kch = Np / 32;
+    oz_slice_tile(mat + (size_t)p * Np * Np + (size_t)I * NB * Np + (size_t)Jc * NB, Np, nullptr, 0.5, gam + Jc * NB,
+                  slices + (size_t)p * slice_stride + ((size_t)I * kch + 4 * Jc) * OZ_CHUNK);
+}
+
+// row scales of the phase-2 panel: sigma_n = 2^(ilogb(max_k |Mt[n][k] / gamma_k|) + 2), k >= (J+1) NB
+__global__ void __launch_bounds__(256)
+k_oz_mt_scale(const double* __restrict__ mt, int Np, int J, const double* __restrict__ gaminv,
+              double* __restrict__ mtsig, double* __restrict__ mtinv, const unsigned char* __restrict__ active) {
+    const int p = blockIdx.y;
+    if (active && !active[p]) return;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n = blockIdx.x * 8 + warp;
+    const double* row = mt + (size_t)p * NB * Np + (size_t)n * Np;
+    double m = 0.0;
+    for (int k = (J + 1) * NB + lane; k < Np; k += 32) m = fmax(m, fabs(row[k] * gaminv[k]));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if (lane == 0) {
+        const double sig = (m > 0.0 && m < 1e300) ? scalbn(1.0, ilogb(m) + 2) : 1.0;
+        mtsig[(size_t)p * NB + n] = sig;
+        mtinv[(size_t)p * NB + n] = 1.0 / sig;
+    }
+}
+
+// digits of Mt / gamma: blockIdx.x -> R = J + 1 + bx (128 columns of the panel)
+__global__ void __launch_bounds__(256)
+k_oz_slice_mt(const double* __restrict__ mt, int Np, int J, const double* __restrict__ gaminv,
+              const double* __restrict__ mtinv, uint8_t* __restrict__ mtslices, size_t mt_stride,
+              const unsigned char* __restrict__ active) {
+    const int p = blockIdx.y;
+    if (active && !active[p]) return;
+    const int R = J + 1 + blockIdx.x;
+    oz_slice_tile(mt + (size_t)p * NB * Np + (size_t)R * NB, Np, mtinv + (size_t)p * NB, 1.0, gaminv + R * NB,
+                  mtslices + (size_t)p * mt_stride + (size_t)(4 * R) * OZ_CHUNK);
+}
+
+// generic slicer (test / library primitive): rows x cols FP64 (multiples of 128), grid (cols / 128, rows / 128)
+__global__ void __launch_bounds__(256)
+k_oz_slice_generic(const double* __restrict__ src, int ld, int kch, const double* __restrict__ rowinv,
+                   uint8_t* __restrict__ dst) {
+    const int cb = blockIdx.x, rb = blockIdx.y;
+    oz_slice_tile(src + (size_t)rb * NB * ld + (size_t)cb * NB, ld, rowinv ? rowinv + rb * NB : nullptr, 1.0, nullptr,
+                  dst + ((size_t)rb * kch + 4 * cb) * OZ_CHUNK);
+}
+
+// ---- launchers ------------------------------------------------------------------------------------------------
+template <typename K>
+static int oz_smem_attr(K kernel, bool& done) {
+    if (!done) {
+        cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OZ_SMEM_BYTES);
+        if (e != cudaSuccess) { set_error("oz smem attr: %s", cudaGetErrorString(e)); return 1; }
+        done = true;
+    }
+    return 0;
+}
+
+size_t oz_slice_bytes(int Np) { return (size_t)(Np / NB) * (Np / 32) * OZ_CHUNK; }
+size_t oz_mt_bytes(int Np) { return (size_t)(Np / 32) * OZ_CHUNK; }
+
+int launch_oz_prep(const double* e, int N, int Np, double* rowsig, double* rowinv, double* gam, double* gaminv,
+                   cudaStream_t st) {
+    k_oz_prep<<<(Np + 255) / 256, 256, 0, st>>>(e, N, Np, rowsig, rowinv, gam, gaminv);
+    return check_launch("k_oz_prep");
+}
+
+int launch_oz_syrk(double* mat, int Np, int T, int J, int P, const uint8_t* slices, const double* rowsig,
+                   const unsigned char* active, cudaStream_t st) {
+    static bool done = false;
+    if (J == 0) return 0;
+    if (oz_smem_attr(k_oz_syrk, done)) return 1;
+    k_oz_syrk<<<dim3(2 * (T - J), P), OZ_THREADS, OZ_SMEM_BYTES, st>>>(mat, Np, J, slices, oz_slice_bytes(Np), rowsig,
+                                                                       active);
+    return check_launch("k_oz_syrk");
+}
+
+int launch_oz_slice_l(const double* mat, int Np, int T, int J, int P, const double* rowinv, uint8_t* slices,
+                      const unsigned char* active, cudaStream_t st) {
+    if (J >= T - 1) return 0;
+    k_oz_slice_l<<<dim3(T - 1 - J, P), 256, 0, st>>>(mat, Np, J, rowinv, slices, oz_slice_bytes(Np), active);
+    return check_launch("k_oz_slice_l");
+}
+
+int launch_oz_slice_w(const double* mat, int Np, int T, int J, int diag, int P, const double* gam, uint8_t* slices,
+                      const unsigned char* active, cudaStream_t st) {
+    const int nblk = T - 1 - (diag ? 0 : J);
+    if (nblk <= 0) return 0;
+    k_oz_slice_w<<<dim3(nblk, P), 256, 0, st>>>(mat, Np, J, diag, gam, slices, oz_slice_bytes(Np), active);
+    return check_launch("k_oz_slice_w");
+}
+
+int launch_oz_mt(const double* mt, int Np, int T, int J, int P, const double* gaminv, double* mtsig, double* mtinv,
+                 uint8_t* mtslices, const unsigned char* active, cudaStream_t st) {
+    if (J >= T - 1) return 0;
+    k_oz_mt_scale<<<dim3(NB / 8, P), 256, 0, st>>>(mt, Np, J, gaminv, mtsig, mtinv, active);
+    if (check_launch("k_oz_mt_scale")) return 1;
+    k_oz_slice_mt<<<dim3(T - 1 - J, P), 256, 0, st>>>(mt, Np, J, gaminv, mtinv, mtslices, oz_mt_bytes(Np), active);
+    return check_launch("k_oz_slice_mt");
+}
+
+int launch_oz_invu(double* mat, int Np, int T, int J, int P, const uint8_t* slices, const uint8_t* mtslices,
+                   const double* mtsig, const unsigned char* active, cudaStream_t st) {
+    static bool done = false;
+    if (J >= T - 1) return 0;
+    if (oz_smem_attr(k_oz_invu, done)) return 1;
+    k_oz_invu<<<dim3(2 * (T - 1 - J), P), OZ_THREADS, OZ_SMEM_BYTES, st>>>(mat, Np, T, J, slices, oz_slice_bytes(Np),
+                                                                          mtslices, oz_mt_bytes(Np), mtsig, active);
+    return check_launch("k_oz_invu");
+}
+
+int launch_oz_slice_generic(const double* src, int ld, int rows, int cols, const double* rowinv, uint8_t* dst,
+                            cudaStream_t st) {
+    k_oz_slice_generic<<<dim3(cols / NB, rows / NB), 256, 0, st>>>(src, ld, cols / 32, rowinv, dst);
+    return check_launch("k_oz_slice_generic");
+}
+
+int launch_oz_gemm_tn(const uint8_t* A, const uint8_t* B, int M, int N, int K, const double* sa, const double* sb,
+                      double* C, int ldc, int* dbg, uint32_t idesc, uint64_t sdesc, cudaStream_t st) {
+    static bool done = false;
+    if (oz_smem_attr(k_oz_gemm_tn, done)) return 1;
+    k_oz_gemm_tn<<<dim3(N / OZ_TILE_N, M / NB), OZ_THREADS, OZ_SMEM_BYTES, st>>>(
+        A, B, K / 32, sa, sb, C, ldc, dbg, idesc ? idesc : OZ_IDESC, sdesc ? sdesc : OZ_SDESC);
+    return check_launch("k_oz_gemm_tn");
+}
+
+}  // namespace gpk

@@ -39,6 +39,19 @@ def to_dev(a, dtype=None):
     return t.to(device(), non_blocking=False)
 
 
+PRECISION_FP64, PRECISION_EMULATED = 0, 1
+
+
+def set_precision(mode):
+    """0: native FP64 tensor instructions (DMMA).  1: emulated FP64 on the int8 tcgen05 tensor cores
+    (7-digit Ozaki split, include/gpk.h gpk_set_precision) for the blocked path (N > 128); needs e > 0."""
+    _lib.check(_lib.load().gpk_set_precision(int(mode)), "gpk_set_precision")
+
+
+def get_precision():
+    return int(_lib.load().gpk_get_precision())
+
+
 _ws_cache = {}
 
 
