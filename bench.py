@@ -28,6 +28,10 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 WORKLOAD = dict(n_points=4096, dims=3, particles_per_gpu=256, n_sigma=1000)
+INT8_PEAK_TOPS = 4497.0
+INT8_PEAK_SOURCE = ("int8 tcgen05.mma issue-rate probe on this pool's B200 (tools/umma_probe.cu, 148 CTAs, N=256: 4497 TOP/s, "
+                    "profiles/r01_umma_probe.log; nominal 4500).  MEASURED_PEAKS.json has only bf16 (1645 burst / 1379 "
+                    "sustained TFLOP/s, cuBLAS); twice that, 3291 / 2757, is the library-GEMM-equivalent int8 figure")
 METRIC = "pso_loss_evals_per_sec_n4096"
 UNIT = "loss_evals/s"
 
@@ -237,6 +241,7 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
     _lib.load()
+    engine.set_precision(args.precision)
     N, d, P, S = WORKLOAD["n_points"], WORKLOAD["dims"], args.particles, WORKLOAD["n_sigma"]
     x, y, e = make_problem(0)
     # every rank owns a different slice of the global swarm (world * P particles)
@@ -308,23 +313,32 @@ def run_ours(args):
         total_cls_ms = sum(v[0] for v in classes.values())
         # algorithmic FP64 flops of the top kernel class over the timed region (this rank)
         T = (N + 127) // 128
-        alg = {"k_syrk_update": N ** 3 / 3.0, "k_inv_update": N ** 3 / 3.0}
+        alg = {"k_syrk_update": N ** 3 / 3.0, "k_inv_update": N ** 3 / 3.0, "k_oz_syrk": N ** 3 / 3.0, "k_oz_invu": N ** 3 / 3.0}
         flops_top = alg.get(top[0], 0.0) * P
         achieved = flops_top / (top[1][0] * 1e-3) / 1e12 if flops_top else None
+        emulated = top[0].startswith("k_oz_")
+        if emulated:
+            # the digit GEMM does `prods` int8 multiply-adds per FP64 multiply-add: report it as int8 tensor work
+            prods = 28 if args.precision == "emu28" else 34
+            achieved = achieved * prods
+            flops_top = flops_top * prods
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": "C3 loss evaluation: N=4096 points, d=3, swarm of 256 particles per GPU, S=1000 sigma scales",
-                       **WORKLOAD, "particles_per_gpu": P, "algorithm": "Cholesky + triangular inverse (2/3 N^3 flop/eval)",
+                       **WORKLOAD, "particles_per_gpu": P, "algorithm": "Cholesky + triangular inverse (2/3 N^3 flop/eval)", "precision": args.precision,
                        "l2_policy": "working set 34 GB per step >> 126 MB L2 (inputs larger than L2)"},
             "e2e": {"value": evals / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"bound": "tensor", "kernel": top[0], "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",
-                         "frac": (achieved / fp64_peak) if achieved else None, "traffic": None,
-                         "peak_source": "FP64 cuBLAS DGEMM 8192^3 measured in this run (MEASURED_PEAKS.json has no FP64 figure; "
+            "roofline": {"bound": "tensor", "kernel": top[0], "achieved": achieved,
+                         "peak": INT8_PEAK_TOPS if emulated else fp64_peak, "unit": "TOP/s (int8)" if emulated else "TFLOP/s",
+                         "frac": (achieved / (INT8_PEAK_TOPS if emulated else fp64_peak)) if achieved else None, "traffic": None,
+                         "peak_source": INT8_PEAK_SOURCE if emulated else
+                                        "FP64 cuBLAS DGEMM 8192^3 measured in this run (MEASURED_PEAKS.json has no FP64 figure; "
                                         "DMMA issue-rate probe: 37.1 TFLOP/s, profiles/r01_fp64_peak_probe.txt)",
+                         "fp64_dgemm_tflops_measured": fp64_peak,
                          "algorithmic_flops_per_launch": flops_top / top[1][1] if flops_top else None,
                          "avg_launch_ms": top[1][0] / top[1][1],
                          "whole_step_tflops": algorithmic_flops_per_eval(N) * P * args.steps / (dev_ms * 1e-3) / 1e12,
@@ -345,6 +359,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--particles", type=int, default=WORKLOAD["particles_per_gpu"], help="particles per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--precision", default="emu", choices=["fp64", "emu", "emu28"],
+                    help="fp64: native DMMA contractions; emu: FP64 emulated on the int8 tcgen05 tensor cores "
+                         "(34 digit products); emu28: 28 digit products")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -379,11 +379,12 @@ int gpk_sum_gaussians(const double* y, int n, const double* gaus, int ng, double
 }
 
 int gpk_set_precision(int mode) {
-    if (mode != 0 && mode != 1) { set_error("gpk_set_precision: 0 (native FP64) or 1 (emulated FP64 on int8 tensor cores)"); return 2; }
-    g_precision = mode;
+    if (mode < 0 || mode > 2) { set_error("gpk_set_precision: 0 (native FP64), 1 (emulated FP64, 34 digit products) or 2 (emulated, 28 digit products)"); return 2; }
+    g_precision = mode ? 1 : 0;
+    if (mode) oz_set_groups(mode == 2 ? 7 : 8);
     return 0;
 }
-int gpk_get_precision(void) { return g_precision; }
+int gpk_get_precision(void) { return g_precision ? (oz_get_groups() == 7 ? 2 : 1) : 0; }
 
 size_t gpk_oz_slice_bytes(int rows, int cols) { return (size_t)(rows / NB) * (cols / 32) * (oz_mt_bytes(32)); }
 
@@ -394,11 +395,11 @@ int gpk_oz_slice(const double* src, int ld, int rows, int cols, const double* ro
 }
 
 int gpk_oz_gemm_tn(const void* A, const void* B, int M, int N, int K, const double* sa, const double* sb, double* C,
-                   int ldc, int* dbg, unsigned int idesc, unsigned long long sdesc, void* stream) {
+                   int ldc, int* dbg, int groups, void* stream) {
+    oz_set_groups(groups);
     if (M < NB || M % NB || N < NB || N % NB || K < NB || K % NB) { set_error("gpk_oz_gemm_tn: M, N, K must be positive multiples of %d", NB); return 2; }
     set_stream((cudaStream_t)stream);
-    return launch_oz_gemm_tn((const uint8_t*)A, (const uint8_t*)B, M, N, K, sa, sb, C, ldc, dbg, idesc, sdesc,
-                             (cudaStream_t)stream);
+    return launch_oz_gemm_tn((const uint8_t*)A, (const uint8_t*)B, M, N, K, sa, sb, C, ldc, dbg, (cudaStream_t)stream);
 }
 
 int gpk_set_groups(int groups) {

@@ -86,7 +86,9 @@ int launch_oz_invu(double* mat, int Np, int T, int J, int P, const uint8_t* slic
 int launch_oz_slice_generic(const double* src, int ld, int rows, int cols, const double* rowinv, uint8_t* dst,
                             cudaStream_t st);
 int launch_oz_gemm_tn(const uint8_t* A, const uint8_t* B, int M, int N, int K, const double* sa, const double* sb,
-                      double* C, int ldc, int* dbg, uint32_t idesc, uint64_t sdesc, cudaStream_t st);
+                      double* C, int ldc, int* dbg, cudaStream_t st);
+void oz_set_groups(int ng);
+int oz_get_groups();
 
 // gpk_loss.cu
 int launch_small_loss(const double* X, const double* y, const double* e, const double* ls,

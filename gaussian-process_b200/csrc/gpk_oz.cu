@@ -5,39 +5,47 @@
 // updates and GP_func.py:38 the N-right-hand-side solve, restated as a triangular inverse) are instead computed
 // here by an error-free split of each FP64 operand into OZ_NS = 7 signed 8-bit digits (Ozaki scheme):
 //
-//     x = sigma * u,  |u| <= 1/2,  sigma a power of two (row scale; a-priori bounds, see the slicers)
+//     x = sigma * u,  |u| <= 0.98,  sigma a power of two (row scale; a-priori bounds, see the slicers)
 //     v = rint(u * 2^55) = sum_s b_s 2^(48 - 8 s),   b_s in [-128, 127]   (balanced digits: bytes of v + 0x..8080)
 //     <x_a, x_b> = sigma_a sigma_b 2^-14 sum_g 2^(-8 g) acc_g,   acc_g = sum_k sum_{s+t=g} b_s[a,k] b_t[b,k]
 //
-// acc_g are exact int32 sums produced by tcgen05.mma.kind::i8; the 28 digit products with g = s+t <= 6 are kept
-// (the dropped ones are mean-zero and below 2^-50 of the row scales, the rounding level of an FP64 dot product of
-// this length).  7 accumulators x 64 columns live in TMEM for one 128 x 64 output tile; the epilogue rebuilds the
-// FP64 value with two fused multiply-adds and applies it to the FP64 matrix in HBM.
+// acc_g are exact int32 sums produced by tcgen05.mma.kind::i8; the 34 digit products with g = s+t <= 7 are kept
+// (the dropped ones are mean-zero and of weight <= 2^-64 sigma_a sigma_b per term, below the rounding level of an
+// FP64 dot product of this length; a 28-product mode, g <= 6, is selectable).  8 accumulators x 64 columns = all 512
+// TMEM columns hold one 128 x 64 output tile; the epilogue rebuilds the FP64 value with two fused multiply-adds and
+// applies it to the FP64 matrix in HBM.
 //
 // Operand storage ("sliced matrix"): for every 128-row block and every 32-wide K chunk one 28 KB record
-//     [16 row groups][7 digits][2 k-halves][8 rows][16 bytes]
+//     [7 digits][16 row groups][2 k-halves][8 rows][16 bytes]
 // which is exactly the shared-memory image tcgen05.mma reads through a no-swizzle K-major descriptor
-// (core matrix = 8 rows x 16 B, LBO = 128 B between the k-halves, SBO = 1792 B between row groups), so a pipeline
-// stage is filled by two plain bulk copies (cp.async.bulk, one elected thread) and needs no tensor map.
+// (core matrix = 8 rows x 16 B, LBO = 128 B between the k-halves, SBO = 256 B between row groups), so a pipeline
+// stage is filled by plain bulk copies (cp.async.bulk, one elected thread) and needs no tensor map.
+//
+// Instruction shape: a 128 x 64 x 32 MMA is bound by its shared-memory operand reads (58 clk measured instead of 32,
+// tools/umma_probe.cu).  The 64-row B digits t = 0.. of a stage are therefore stored back to back, so that ONE
+// instruction with N = 64 * count multiplies the A digit s with `count` consecutive B digits and lands in the
+// accumulators of the groups s + t0 .. s + t0 + count - 1, which are adjacent TMEM columns: 10-11 instructions of
+// N <= 256 per K chunk instead of 28-34 of N = 64.
 #include "gpk_common.cuh"
 
 namespace gpk {
 
 constexpr int OZ_NS = 7;                        // int8 digits per FP64 value
-constexpr int OZ_RG = OZ_NS * 256;              // bytes of one 8-row group (all digits, 32 k)
-constexpr int OZ_CHUNK = 16 * OZ_RG;            // 128 rows x 32 k x 7 digits = 28672 B
-constexpr int OZ_HALF = 8 * OZ_RG;              // 64 rows
+constexpr int OZ_DIGIT = 4096;                  // one digit of a 128-row block x 32 k: [16 row groups][256 B]
+constexpr int OZ_DIGIT_HALF = 2048;             // 64 rows
+constexpr int OZ_CHUNK = OZ_NS * OZ_DIGIT;      // 128 rows x 32 k x 7 digits = 28672 B
+constexpr int OZ_HALF = OZ_NS * OZ_DIGIT_HALF;  // 64 rows, digits back to back (shared-memory image of B)
 constexpr int OZ_STAGE = OZ_CHUNK + OZ_HALF;    // A (128 rows) + B (64 rows)
 constexpr int OZ_STAGES = 5;
-constexpr int OZ_THREADS = 192;                 // warp 0 producer, warp 1 MMA issuer, warps 2..5 epilogue
+constexpr int OZ_THREADS = 320;                 // warp 0 producer, warp 1 MMA issuer, warps 2..9 epilogue
 constexpr int OZ_TMEM_COLS = 512;
 constexpr int OZ_TILE_N = 64;
 constexpr size_t OZ_SMEM_BYTES = (size_t)OZ_STAGES * OZ_STAGE + 128;
 constexpr long long OZ_BIAS = 0x0000808080808080LL;
-// kind::i8, D = S32, A = B = signed 8 bit, both K-major, N = 64, M = 128
-constexpr uint32_t OZ_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((OZ_TILE_N >> 3) << 17) | ((128u >> 4) << 24);
-// no-swizzle K-major shared-memory descriptor without the start address: LBO = 128 B, SBO = OZ_RG, version 1
-constexpr uint64_t OZ_SDESC = ((uint64_t)(128 >> 4) << 16) | ((uint64_t)(OZ_RG >> 4) << 32) | (1ull << 46);
+// kind::i8, D = S32, A = B = signed 8 bit, both K-major, M = 128; the N field (bits 17..22, N >> 3) is added per MMA
+constexpr uint32_t OZ_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((128u >> 4) << 24);
+// no-swizzle K-major shared-memory descriptor without the start address: LBO = 128 B, SBO = 256 B, version 1
+constexpr uint64_t OZ_SDESC = ((uint64_t)(128 >> 4) << 16) | ((uint64_t)(256 >> 4) << 32) | (1ull << 46);
 
 // ---- PTX wrappers ---------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -102,20 +110,39 @@ enum OzEpi { OZ_SUB = 0, OZ_STORE = 1, OZ_STORE_NEG = 2 };
 
 struct OzTile {
     const uint8_t* a;     // first chunk of the A row block (128 rows), chunks are consecutive in K
-    const uint8_t* b;     // first chunk of the B half block (64 rows): chunk base + half * OZ_HALF
+    const uint8_t* b;     // first chunk of the B row block + half * OZ_DIGIT_HALF (64 rows of every digit)
     int nk;               // number of 32-wide K chunks
     double* c;            // &C[row0][col0] of the 128 x 64 FP64 tile
     int ldc;
     const double* sa;     // row scales sigma of the 128 A rows, or nullptr
     double sa_const;      // multiplies every row scale (use it alone when sa == nullptr)
     const double* sb;     // scales of the 64 B rows, or nullptr (= 1)
-    int* dbg;             // optional raw accumulator dump [7][128][64]
-    uint32_t idesc;
-    uint64_t sdesc;
+    int* dbg;             // optional raw accumulator dump [NG][128][64]
 };
 
+// The MMAs of one K chunk.  NG = number of digit groups kept (g = s + t < NG): 7 -> 28 digit products, 8 -> 34.
+// A digit s meets the B digits t = 0 .. min(7, NG - s) - 1 in pieces of at most 4 digits (N <= 256); the piece
+// starting at t0 accumulates into the TMEM columns of the groups s + t0 ...  With NG = 8 the digit s = 4 goes first
+// so that at the first chunk every accumulator is initialised by an instruction that covers it completely.
+template <int NG>
+__device__ __forceinline__ void oz_issue_chunk(uint32_t tmem, uint64_t da, uint64_t db, bool first) {
+#pragma unroll
+    for (int si = 0; si < OZ_NS; ++si) {
+        const int s = (NG == 8) ? (si == 0 ? 4 : (si <= 4 ? si - 1 : si)) : si;
+        const int total = (NG - s < OZ_NS) ? (NG - s) : OZ_NS;
+#pragma unroll
+        for (int t0 = 0; t0 < total; t0 += 4) {
+            const int cnt = (total - t0 < 4) ? (total - t0) : 4;
+            const bool init_piece = (NG == 8) ? (s == 4 || (s == 0 && t0 == 0)) : (s == 0);
+            const uint32_t idesc = OZ_IDESC | ((uint32_t)((cnt * OZ_TILE_N) >> 3) << 17);
+            umma_i8(tmem + (s + t0) * OZ_TILE_N, da + (uint64_t)(s * (OZ_DIGIT >> 4)),
+                    db + (uint64_t)(t0 * (OZ_DIGIT_HALF >> 4)), idesc, (init_piece && first) ? 0u : 1u);
+        }
+    }
+}
+
 // One 128 x 64 output tile per CTA.
-template <int EPI>
+template <int EPI, int NG>
 __device__ __forceinline__ void oz_tile(const OzTile& t, uint8_t* smem) {
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
@@ -153,8 +180,12 @@ __device__ __forceinline__ void oz_tile(const OzTile& t, uint8_t* smem) {
                 const uint32_t ph = (uint32_t)(k / OZ_STAGES) & 1u;
                 mbar_wait(empty0 + 8 * s, ph ^ 1u);
                 mbar_expect_tx(full0 + 8 * s, OZ_STAGE);
-                bulk_g2s(stage0 + s * OZ_STAGE, t.a + (size_t)k * OZ_CHUNK, OZ_CHUNK, full0 + 8 * s);
-                bulk_g2s(stage0 + s * OZ_STAGE + OZ_CHUNK, t.b + (size_t)k * OZ_CHUNK, OZ_HALF, full0 + 8 * s);
+                const uint32_t dst = stage0 + s * OZ_STAGE;
+                bulk_g2s(dst, t.a + (size_t)k * OZ_CHUNK, OZ_CHUNK, full0 + 8 * s);
+#pragma unroll
+                for (int d = 0; d < OZ_NS; ++d)       // 64 rows of every B digit, stored back to back
+                    bulk_g2s(dst + OZ_CHUNK + d * OZ_DIGIT_HALF, t.b + (size_t)k * OZ_CHUNK + d * OZ_DIGIT, OZ_DIGIT_HALF,
+                             full0 + 8 * s);
             }
         }
     } else if (warp == 1) {
@@ -164,59 +195,58 @@ __device__ __forceinline__ void oz_tile(const OzTile& t, uint8_t* smem) {
                 const uint32_t ph = (uint32_t)(k / OZ_STAGES) & 1u;
                 mbar_wait(full0 + 8 * s, ph);
                 tc_fence_after();
-                const uint64_t da = t.sdesc | (uint64_t)(((stage0 + s * OZ_STAGE) >> 4) & 0x3FFF);
-                const uint64_t db = t.sdesc | (uint64_t)(((stage0 + s * OZ_STAGE + OZ_CHUNK) >> 4) & 0x3FFF);
-#pragma unroll
-                for (int g = 0; g < OZ_NS; ++g) {
-#pragma unroll
-                    for (int sa = 0; sa <= g; ++sa) {
-                        const int sb = g - sa;
-                        umma_i8(tmem + g * OZ_TILE_N, da + (uint64_t)(sa * (256 >> 4)), db + (uint64_t)(sb * (256 >> 4)),
-                                t.idesc, (k > 0 || sa > 0) ? 1u : 0u);
-                    }
-                }
+                const uint64_t da = OZ_SDESC | (uint64_t)(((stage0 + s * OZ_STAGE) >> 4) & 0x3FFF);
+                const uint64_t db = OZ_SDESC | (uint64_t)(((stage0 + s * OZ_STAGE + OZ_CHUNK) >> 4) & 0x3FFF);
+                oz_issue_chunk<NG>(tmem, da, db, k == 0);
                 umma_commit(empty0 + 8 * s);     // frees the stage when these MMAs have read it
             }
             umma_commit(accbar);                 // accumulators complete
         }
     } else {
-        // epilogue warps 2..5: TMEM lane quadrant = warp % 4, one output row per thread
+        // epilogue warps 2..9: TMEM lane quadrant = warp % 4, one output row and 32 of the 64 columns per thread
         const int q = warp & 3;
+        const int ch = (warp - 2) >> 2;
         const int row = q * 32 + lane;
+        const double rs = (t.sa ? t.sa[row] : 1.0) * t.sa_const * 0x1p-14;
+        double* crow = t.c + (size_t)row * t.ldc + ch * 32;
+        const double* sbp = t.sb ? t.sb + ch * 32 : nullptr;
+        double2 cold[16];
+        if (EPI == OZ_SUB) {                     // the tile is final input data: fetch it while the MMAs run
+#pragma unroll
+            for (int j = 0; j < 16; ++j) cold[j] = reinterpret_cast<const double2*>(crow)[j];
+        }
         mbar_wait(accbar, 0);
         tc_fence_after();
-        const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16);
-        const double rs = (t.sa ? t.sa[row] : 1.0) * t.sa_const * 0x1p-14;
-        double* crow = t.c + (size_t)row * t.ldc;
-#pragma unroll 1
-        for (int cc = 0; cc < OZ_TILE_N; cc += 8) {
-            uint32_t a[OZ_NS][8];
+        const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + ch * 32;
 #pragma unroll
-            for (int g = 0; g < OZ_NS; ++g) tmem_ld8(taddr + g * OZ_TILE_N + cc, a[g]);
+        for (int cc = 0; cc < 32; cc += 8) {
+            uint32_t a[NG][8];
+#pragma unroll
+            for (int g = 0; g < NG; ++g) tmem_ld8(taddr + g * OZ_TILE_N + cc, a[g]);
             tmem_wait_ld();
             if (t.dbg) {
 #pragma unroll
-                for (int g = 0; g < OZ_NS; ++g)
+                for (int g = 0; g < NG; ++g)
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) t.dbg[(g * 128 + row) * OZ_TILE_N + cc + j] = (int)a[g][j];
+                    for (int j = 0; j < 8; ++j) t.dbg[(g * 128 + row) * OZ_TILE_N + ch * 32 + cc + j] = (int)a[g][j];
             }
             double v[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
                 const long long hi = ((long long)(int)a[0][j] << 16) + ((long long)(int)a[1][j] << 8) + (long long)(int)a[2][j];
                 const long long mid = ((long long)(int)a[3][j] << 16) + ((long long)(int)a[4][j] << 8) + (long long)(int)a[5][j];
-                const long long lo = (long long)(int)a[6][j];
-                double x = fma(ll2d_exact(mid), 0x1p-40, ll2d_exact(lo) * 0x1p-48);
+                long long lo = (long long)(int)a[6][j] << 8;
+                if (NG == 8) lo += (long long)(int)a[NG - 1][j];
+                double x = fma(ll2d_exact(mid), 0x1p-40, ll2d_exact(lo) * 0x1p-56);
                 x = fma(ll2d_exact(hi), 0x1p-16, x);
-                const double sc = rs * (t.sb ? t.sb[cc + j] : 1.0);
-                v[j] = x * sc;
+                v[j] = x * (rs * (sbp ? sbp[cc + j] : 1.0));
             }
             double2* cp = reinterpret_cast<double2*>(crow + cc);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 double2 o;
                 if (EPI == OZ_SUB) {
-                    o = cp[j];
+                    o = cold[cc / 2 + j];
                     o.x -= v[2 * j];
                     o.y -= v[2 * j + 1];
                 } else if (EPI == OZ_STORE) {
@@ -241,6 +271,7 @@ __device__ __forceinline__ void oz_tile(const OzTile& t, uint8_t* smem) {
 // ---- kernels ----------------------------------------------------------------------------------------------
 // Left-looking Cholesky update of block column J: A_IJ -= sum_{K<J} L_IK L_JK^T from the digit slices of L.
 // blockIdx.x = 2 * (I - J) + half, blockIdx.y = particle.
+template <int NG>
 __global__ void __launch_bounds__(OZ_THREADS, 1)
 k_oz_syrk(double* __restrict__ mat, int Np, int J, const uint8_t* __restrict__ slices, size_t slice_stride,
           const double* __restrict__ rowsig, const unsigned char* __restrict__ active) {
@@ -252,7 +283,7 @@ k_oz_syrk(double* __restrict__ mat, int Np, int J, const uint8_t* __restrict__ s
     const uint8_t* S = slices + (size_t)p * slice_stride;
     OzTile t;
     t.a = S + (size_t)I * kch * OZ_CHUNK;
-    t.b = S + (size_t)J * kch * OZ_CHUNK + (size_t)h * OZ_HALF;
+    t.b = S + (size_t)J * kch * OZ_CHUNK + (size_t)h * OZ_DIGIT_HALF;
     t.nk = 4 * J;
     t.c = mat + (size_t)p * Np * Np + (size_t)I * NB * Np + (size_t)J * NB + h * OZ_TILE_N;
     t.ldc = Np;
@@ -260,13 +291,12 @@ k_oz_syrk(double* __restrict__ mat, int Np, int J, const uint8_t* __restrict__ s
     t.sa_const = 1.0;
     t.sb = rowsig + J * NB + h * OZ_TILE_N;
     t.dbg = nullptr;
-    t.idesc = OZ_IDESC;
-    t.sdesc = OZ_SDESC;
-    oz_tile<OZ_SUB>(t, oz_smem);
+    oz_tile<OZ_SUB, NG>(t, oz_smem);
 }
 
 // Phase-2 update W_IJ = - sum_{k in [(J+1)NB, (I+1)NB)} (W gamma)[I-block][k] * (Mt / gamma)[:, k]^T.
 // blockIdx.x = 2 * (T - 1 - I) + half (deepest contraction first), blockIdx.y = particle.
+template <int NG>
 __global__ void __launch_bounds__(OZ_THREADS, 1)
 k_oz_invu(double* __restrict__ mat, int Np, int T, int J, const uint8_t* __restrict__ slices, size_t slice_stride,
           const uint8_t* __restrict__ mtslices, size_t mt_stride, const double* __restrict__ mtsig,
@@ -278,7 +308,7 @@ k_oz_invu(double* __restrict__ mat, int Np, int T, int J, const uint8_t* __restr
     const int kch = Np / 32;
     OzTile t;
     t.a = slices + (size_t)p * slice_stride + ((size_t)I * kch + 4 * (J + 1)) * OZ_CHUNK;
-    t.b = mtslices + (size_t)p * mt_stride + (size_t)(4 * (J + 1)) * OZ_CHUNK + (size_t)h * OZ_HALF;
+    t.b = mtslices + (size_t)p * mt_stride + (size_t)(4 * (J + 1)) * OZ_CHUNK + (size_t)h * OZ_DIGIT_HALF;
     t.nk = 4 * (I - J);
     t.c = mat + (size_t)p * Np * Np + (size_t)I * NB * Np + (size_t)J * NB + h * OZ_TILE_N;
     t.ldc = Np;
@@ -286,30 +316,27 @@ k_oz_invu(double* __restrict__ mat, int Np, int T, int J, const uint8_t* __restr
     t.sa_const = 2.0;                              // W gamma is sliced with sigma = 2
     t.sb = mtsig + (size_t)p * NB + h * OZ_TILE_N;
     t.dbg = nullptr;
-    t.idesc = OZ_IDESC;
-    t.sdesc = OZ_SDESC;
-    oz_tile<OZ_STORE_NEG>(t, oz_smem);
+    oz_tile<OZ_STORE_NEG, NG>(t, oz_smem);
 }
 
 // Generic C = A B^T over sliced operands (test / library primitive): grid (N / 64, M / 128).
+template <int NG>
 __global__ void __launch_bounds__(OZ_THREADS, 1)
 k_oz_gemm_tn(const uint8_t* __restrict__ A, const uint8_t* __restrict__ B, int kch, const double* __restrict__ sa,
-             const double* __restrict__ sb, double* __restrict__ C, int ldc, int* dbg, uint32_t idesc, uint64_t sdesc) {
+             const double* __restrict__ sb, double* __restrict__ C, int ldc, int* dbg) {
     extern __shared__ __align__(128) uint8_t oz_smem[];
     const int nb = blockIdx.x, mb = blockIdx.y;
     OzTile t;
     t.a = A + (size_t)mb * kch * OZ_CHUNK;
-    t.b = B + (size_t)(nb >> 1) * kch * OZ_CHUNK + (size_t)(nb & 1) * OZ_HALF;
+    t.b = B + (size_t)(nb >> 1) * kch * OZ_CHUNK + (size_t)(nb & 1) * OZ_DIGIT_HALF;
     t.nk = kch;
     t.c = C + (size_t)mb * NB * ldc + (size_t)nb * OZ_TILE_N;
     t.ldc = ldc;
     t.sa = sa ? sa + mb * NB : nullptr;
     t.sa_const = 1.0;
     t.sb = sb ? sb + nb * OZ_TILE_N : nullptr;
-    t.dbg = dbg ? dbg + ((size_t)mb * gridDim.x + nb) * (OZ_NS * 128 * OZ_TILE_N) : nullptr;
-    t.idesc = idesc;
-    t.sdesc = sdesc;
-    oz_tile<OZ_STORE>(t, oz_smem);
+    t.dbg = dbg ? dbg + ((size_t)mb * gridDim.x + nb) * (NG * 128 * OZ_TILE_N) : nullptr;
+    oz_tile<OZ_STORE, NG>(t, oz_smem);
 }
 
 // ---- slicers: FP64 128 x 128 tile -> 4 chunk records ----------------------------------------------------------
@@ -320,7 +347,7 @@ __device__ __forceinline__ uint32_t pack_digit(const uint32_t* w, int b) {
     return __byte_perm(t0, t1, 0x5410);
 }
 
-// u = x * rs[row] * rconst * cs[col];  |u| <= 1/2 is the caller's contract (a-priori bounds / measured maxima)
+// u = x * rs[row] * rconst * cs[col];  |u| <= 0.98 is the caller's contract (a-priori bounds / measured maxima)
 __device__ __forceinline__ void oz_slice_tile(const double* __restrict__ src, int ld, const double* __restrict__ rs,
                                               double rconst, const double* __restrict__ cs, uint8_t* __restrict__ dst) {
     for (int unit = threadIdx.x; unit < 1024; unit += blockDim.x) {
@@ -344,7 +371,7 @@ __device__ __forceinline__ void oz_slice_tile(const double* __restrict__ src, in
             lo[2 * j + 1] = (uint32_t)v1;
             hi[2 * j + 1] = (uint32_t)(v1 >> 32);
         }
-        uint8_t* d = dst + (size_t)kcl * OZ_CHUNK + rg * OZ_RG + kg * 128 + r8 * 16;
+        uint8_t* d = dst + (size_t)kcl * OZ_CHUNK + rg * 256 + kg * 128 + r8 * 16;
 #pragma unroll
         for (int s = 0; s < OZ_NS; ++s) {
             const int bytepos = 6 - s;                 // digit s = byte (6 - s) of the biased fixed-point word
@@ -355,9 +382,17 @@ __device__ __forceinline__ void oz_slice_tile(const double* __restrict__ src, in
             o.y = pack_digit(w + 4, b);
             o.z = pack_digit(w + 8, b);
             o.w = pack_digit(w + 12, b);
-            *reinterpret_cast<uint4*>(d + s * 256) = o;
+            *reinterpret_cast<uint4*>(d + s * OZ_DIGIT) = o;
         }
     }
+}
+
+// smallest power of two sigma with bound / sigma <= 0.98 (the top digit then stays inside [-126, 126])
+__device__ __forceinline__ double oz_scale_for(double bound) {
+    if (!(bound > 0.0) || !(bound < 1e300)) return 1.0;
+    double sig = scalbn(1.0, ilogb(bound) + 1);
+    if (bound > 0.98 * sig) sig *= 2.0;
+    return sig;
 }
 
 // particle-independent scales: row bound of L (|L_ik| <= sqrt(K_ii) = sqrt(1 + e_i^2)) and the column scaling
@@ -366,11 +401,11 @@ __global__ void k_oz_prep(const double* __restrict__ e, int N, int Np, double* _
                           double* __restrict__ rowinv, double* __restrict__ gam, double* __restrict__ gaminv) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= Np) return;
-    double sig = 4.0, g = 1.0;
+    double sig = 2.0, g = 1.0;
     if (i < N) {
         const double ei = fabs(e[i]);
-        sig = scalbn(1.0, ilogb(sqrt(1.0 + ei * ei)) + 2);
-        g = scalbn(1.0, ilogb(ei));
+        sig = oz_scale_for(sqrt(1.0 + ei * ei));
+        g = (ei > 1e-290 && ei < 1e290) ? scalbn(1.0, ilogb(ei)) : 1.0;     // e = 0 is outside this mode's contract
     }
     rowsig[i] = sig;
     rowinv[i] = 1.0 / sig;
@@ -417,7 +452,7 @@ k_oz_mt_scale(const double* __restrict__ mt, int Np, int J, const double* __rest
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
     if (lane == 0) {
-        const double sig = (m > 0.0 && m < 1e300) ? scalbn(1.0, ilogb(m) + 2) : 1.0;
+        const double sig = oz_scale_for(m);
         mtsig[(size_t)p * NB + n] = sig;
         mtinv[(size_t)p * NB + n] = 1.0 / sig;
     }
@@ -464,13 +499,22 @@ int launch_oz_prep(const double* e, int N, int Np, double* rowsig, double* rowin
     return check_launch("k_oz_prep");
 }
 
+static int g_oz_groups = 8;     // digit groups kept: 8 -> 34 digit products (default), 7 -> 28
+void oz_set_groups(int ng) { g_oz_groups = (ng == 7) ? 7 : 8; }
+int oz_get_groups() { return g_oz_groups; }
+
 int launch_oz_syrk(double* mat, int Np, int T, int J, int P, const uint8_t* slices, const double* rowsig,
                    const unsigned char* active, cudaStream_t st) {
-    static bool done = false;
+    static bool done7 = false, done8 = false;
     if (J == 0) return 0;
-    if (oz_smem_attr(k_oz_syrk, done)) return 1;
-    k_oz_syrk<<<dim3(2 * (T - J), P), OZ_THREADS, OZ_SMEM_BYTES, st>>>(mat, Np, J, slices, oz_slice_bytes(Np), rowsig,
-                                                                       active);
+    const dim3 grid(2 * (T - J), P);
+    if (g_oz_groups == 7) {
+        if (oz_smem_attr(k_oz_syrk<7>, done7)) return 1;
+        k_oz_syrk<7><<<grid, OZ_THREADS, OZ_SMEM_BYTES, st>>>(mat, Np, J, slices, oz_slice_bytes(Np), rowsig, active);
+    } else {
+        if (oz_smem_attr(k_oz_syrk<8>, done8)) return 1;
+        k_oz_syrk<8><<<grid, OZ_THREADS, OZ_SMEM_BYTES, st>>>(mat, Np, J, slices, oz_slice_bytes(Np), rowsig, active);
+    }
     return check_launch("k_oz_syrk");
 }
 
@@ -500,11 +544,18 @@ int launch_oz_mt(const double* mt, int Np, int T, int J, int P, const double* ga
 
 int launch_oz_invu(double* mat, int Np, int T, int J, int P, const uint8_t* slices, const uint8_t* mtslices,
                    const double* mtsig, const unsigned char* active, cudaStream_t st) {
-    static bool done = false;
+    static bool done7 = false, done8 = false;
     if (J >= T - 1) return 0;
-    if (oz_smem_attr(k_oz_invu, done)) return 1;
-    k_oz_invu<<<dim3(2 * (T - 1 - J), P), OZ_THREADS, OZ_SMEM_BYTES, st>>>(mat, Np, T, J, slices, oz_slice_bytes(Np),
-                                                                          mtslices, oz_mt_bytes(Np), mtsig, active);
+    const dim3 grid(2 * (T - 1 - J), P);
+    if (g_oz_groups == 7) {
+        if (oz_smem_attr(k_oz_invu<7>, done7)) return 1;
+        k_oz_invu<7><<<grid, OZ_THREADS, OZ_SMEM_BYTES, st>>>(mat, Np, T, J, slices, oz_slice_bytes(Np), mtslices,
+                                                              oz_mt_bytes(Np), mtsig, active);
+    } else {
+        if (oz_smem_attr(k_oz_invu<8>, done8)) return 1;
+        k_oz_invu<8><<<grid, OZ_THREADS, OZ_SMEM_BYTES, st>>>(mat, Np, T, J, slices, oz_slice_bytes(Np), mtslices,
+                                                              oz_mt_bytes(Np), mtsig, active);
+    }
     return check_launch("k_oz_invu");
 }
 
@@ -515,11 +566,16 @@ int launch_oz_slice_generic(const double* src, int ld, int rows, int cols, const
 }
 
 int launch_oz_gemm_tn(const uint8_t* A, const uint8_t* B, int M, int N, int K, const double* sa, const double* sb,
-                      double* C, int ldc, int* dbg, uint32_t idesc, uint64_t sdesc, cudaStream_t st) {
-    static bool done = false;
-    if (oz_smem_attr(k_oz_gemm_tn, done)) return 1;
-    k_oz_gemm_tn<<<dim3(N / OZ_TILE_N, M / NB), OZ_THREADS, OZ_SMEM_BYTES, st>>>(
-        A, B, K / 32, sa, sb, C, ldc, dbg, idesc ? idesc : OZ_IDESC, sdesc ? sdesc : OZ_SDESC);
+                      double* C, int ldc, int* dbg, cudaStream_t st) {
+    static bool done7 = false, done8 = false;
+    const dim3 grid(N / OZ_TILE_N, M / NB);
+    if (g_oz_groups == 7) {
+        if (oz_smem_attr(k_oz_gemm_tn<7>, done7)) return 1;
+        k_oz_gemm_tn<7><<<grid, OZ_THREADS, OZ_SMEM_BYTES, st>>>(A, B, K / 32, sa, sb, C, ldc, dbg);
+    } else {
+        if (oz_smem_attr(k_oz_gemm_tn<8>, done8)) return 1;
+        k_oz_gemm_tn<8><<<grid, OZ_THREADS, OZ_SMEM_BYTES, st>>>(A, B, K / 32, sa, sb, C, ldc, dbg);
+    }
     return check_launch("k_oz_gemm_tn");
 }
 

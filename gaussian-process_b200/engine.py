@@ -39,17 +39,41 @@ def to_dev(a, dtype=None):
     return t.to(device(), non_blocking=False)
 
 
-PRECISION_FP64, PRECISION_EMULATED = 0, 1
+# Arithmetic of the two dense contractions of the blocked path (N > 128), include/gpk.h gpk_set_precision:
+#   "fp64"   native FP64 tensor instructions (DMMA)
+#   "emu"    FP64 emulated on the int8 tcgen05 tensor cores (7-digit Ozaki split, 34 digit products): same rounding
+#            level as an FP64 dot product, 1.7x the loss-evaluation throughput at N = 4096; needs e > 0
+#   "emu28"  28 digit products (~2^8 larger truncation error)
+#   "auto"   "emu" whenever every e_i is finite and > 0, else "fp64"            (default; env GPK_PRECISION)
+_MODES = {"fp64": 0, "emu": 1, "emu28": 2}
+_precision_pref = os.environ.get("GPK_PRECISION", "auto")
 
 
 def set_precision(mode):
-    """0: native FP64 tensor instructions (DMMA).  1: emulated FP64 on the int8 tcgen05 tensor cores
-    (7-digit Ozaki split, include/gpk.h gpk_set_precision) for the blocked path (N > 128); needs e > 0."""
-    _lib.check(_lib.load().gpk_set_precision(int(mode)), "gpk_set_precision")
+    global _precision_pref
+    mode = {0: "fp64", 1: "emu", 2: "emu28"}.get(mode, mode)
+    if mode != "auto" and mode not in _MODES:
+        raise ValueError(f"precision must be one of auto, fp64, emu, emu28 (got {mode!r})")
+    _precision_pref = mode
 
 
 def get_precision():
-    return int(_lib.load().gpk_get_precision())
+    return _precision_pref
+
+
+def _resolve_precision(e_host):
+    """Mode number for a problem with uncertainties e_host (host array)."""
+    pref = _precision_pref
+    ok = bool(np.all(np.isfinite(e_host)) and np.all(np.abs(e_host) > 1e-150)) if e_host.size else False
+    if pref == "auto":
+        return 1 if ok else 0
+    if pref != "fp64" and not ok:
+        raise ValueError("emulated-FP64 mode needs finite, non-zero e_known (use GPK_PRECISION=fp64)")
+    return _MODES[pref]
+
+
+def _apply_precision(mode):
+    _lib.check(_lib.load().gpk_set_precision(int(mode)), "gpk_set_precision")
 
 
 _ws_cache = {}
@@ -121,10 +145,13 @@ class LossContext:
         self.s = sigma_vals.shape[0]
         self.x, self.y, self.e, self.sig = to_dev(x), to_dev(y), to_dev(e), to_dev(sigma_vals)
         self.mem_fraction = mem_fraction
+        self._e_ok = e
         self._pin_pos = None
         self._pin_counts = None
 
     def _ws(self, p):
+        self.mode = _resolve_precision(self._e_ok)       # also sizes the workspace
+        _apply_precision(self.mode)
         need = self.lib.gpk_loss_workspace_bytes(p, self.n, self.d)
         have = _ws_cache.get((torch.cuda.current_device(), "loss"))
         if have is not None and have.numel() >= need:
@@ -193,6 +220,8 @@ class GPFit:
         self.xs = torch.empty((self.d, self.np_), dtype=torch.float64, device=dev)
         self.sq = torch.empty(self.np_, dtype=torch.float64, device=dev)
         info = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.mode = _resolve_precision(e)
+        _apply_precision(self.mode)
         ws = workspace(lib.gpk_fit_workspace_bytes(self.n, self.d), "fit")
         st = lib.gpk_fit(dx.data_ptr(), dy.data_ptr(), de.data_ptr(), self.ls.data_ptr(), self.n, self.d,
                          self.W.data_ptr(), self.alpha.data_ptr(), self.xs.data_ptr(), self.sq.data_ptr(),

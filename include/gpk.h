@@ -92,10 +92,12 @@ GPK_API int gpk_set_groups(int groups);
 /* Arithmetic of the two dense contractions of the blocked path (Cholesky trailing updates, GP_func.py:22, and the
  * triangular-inverse updates that replace the N-right-hand-side solve of GP_func.py:38):
  *   0  native FP64 tensor instructions (DMMA, mma.sync.m8n8k4.f64) -- sm_100a has no FP64 kind of tcgen05.mma;
- *   1  emulated FP64: every operand is split error-free into 7 signed 8-bit digits (Ozaki scheme), the 28 digit
- *      products run on the int8 tcgen05 tensor cores with exact int32 accumulation in TMEM, and the FP64 result is
- *      rebuilt in the epilogue.  Rounding level: that of an FP64 dot product of the same length (checked against the
- *      reference in tests/test_gpu_parity.py).  Requires e > 0 (the column bound |L^-1[i][k]| <= 1 / e_k is used).
+ *   1  emulated FP64: every operand is split error-free into 7 signed 8-bit digits (Ozaki scheme), the 34 digit
+ *      products of weight >= 2^-56 run on the int8 tcgen05 tensor cores with exact int32 accumulation in TMEM, and
+ *      the FP64 result is rebuilt in the epilogue.  Rounding level: that of an FP64 dot product of the same length
+ *      (checked against the reference in tests/test_gpu_parity.py).  Requires e > 0 (the column bound
+ *      |L^-1[i][k]| <= 1 / e_k is used);
+ *   2  as 1 with the 28 digit products of weight >= 2^-48 only (21 % less tensor work, ~2^8 larger truncation).
  * The mode also sizes gpk_loss_workspace_bytes / gpk_fit_workspace_bytes: set it before querying them. */
 GPK_API int gpk_set_precision(int mode);
 GPK_API int gpk_get_precision(void);
@@ -104,12 +106,12 @@ GPK_API int gpk_get_precision(void);
  *   gpk_oz_slice: rows x cols FP64 (both multiples of 128, row stride ld) -> digit records; rowinv[r] (optional) is
  *     the reciprocal power-of-two row scale: |src[r][c] * rowinv[r]| <= 1/2 is the caller's contract.
  *   gpk_oz_gemm_tn: C[M][N] = sum_k A[m][k] B[n][k] over sliced operands, scaled by sa[m] * sb[n] (the row scales).
- *     dbg (optional) receives the raw int32 accumulators [M/128][N/64][7][128][64]; idesc / sdesc = 0 selects the
- *     library's instruction / shared-memory descriptors. */
+ *     groups = 8 (34 digit products) or 7 (28); dbg (optional) receives the raw int32 accumulators
+ *     [M/128][N/64][groups][128][64]. */
 GPK_API size_t gpk_oz_slice_bytes(int rows, int cols);
 GPK_API int gpk_oz_slice(const double* src, int ld, int rows, int cols, const double* rowinv, void* dst, void* stream);
 GPK_API int gpk_oz_gemm_tn(const void* A, const void* B, int M, int N, int K, const double* sa, const double* sb,
-                   double* C, int ldc, int* dbg, unsigned int idesc, unsigned long long sdesc, void* stream);
+                   double* C, int ldc, int* dbg, int groups, void* stream);
 
 /* Measurement aid (bench.py roofline): per-kernel-class device time by events recorded after every launch
  * on `stream` between begin and end.  Not thread-safe; name_out is a HOST buffer. */

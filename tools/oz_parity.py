@@ -13,7 +13,7 @@ from oracle import gp_oracle as orc  # noqa: E402
 
 
 def run(n, d, p, seed, mode):
-    engine.set_precision(mode)
+    engine.set_precision(mode)  # 0 fp64, 1 emu, 2 emu28
     x, y, e = orc.synthetic_problem(n, d, seed)
     pos, lo, hi = orc.synthetic_particles(x, p, seed)
     s, ex = orc.sigma_grid()

@@ -21,13 +21,13 @@
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__); exit(2); } } while (0)
 #define GK(x) do { int s_ = (x); if (s_ != 0) { printf("gpk error %d: %s at %s:%d\n", s_, gpk_last_error_string(), __FILE__, __LINE__); exit(3); } } while (0)
 
-static const int NS = 7, RG = NS * 256, CHUNK = 16 * RG;
+static const int NS = 7, DIGIT = 4096, CHUNK = NS * DIGIT;
 static const long long BIAS = 0x0000808080808080LL;
 
 // host restatement of the record layout: digit s of element (r, k) of a rows x K matrix
 static size_t rec_offset(int r, int k, int s, int kch) {
     const int rb = r / 128, rr = r % 128, kc = k / 32, kk = k % 32;
-    return ((size_t)rb * kch + kc) * CHUNK + (size_t)(rr / 8) * RG + s * 256 + (kk / 16) * 128 + (rr % 8) * 16 + (kk % 16);
+    return ((size_t)rb * kch + kc) * CHUNK + (size_t)s * DIGIT + (rr / 8) * 256 + (kk / 16) * 128 + (rr % 8) * 16 + (kk % 16);
 }
 static void host_digits(double x, double rowinv, int8_t* d) {
     long long v = llrint(x * rowinv * 0x1p55);
@@ -51,7 +51,8 @@ static Problem make_problem(int M, int N, int K, unsigned seed) {
             const double amp = std::ldexp(1.0, (int)(rng() % 9) - 4) * (1.0 + 0.3 * U(rng));
             double mx = 0;
             for (int k = 0; k < K; ++k) { double v = amp * U(rng) * ((k % 7 == 0) ? 1e-6 : 1.0); X[(size_t)r * K + k] = v; mx = std::fmax(mx, std::fabs(v)); }
-            sg[r] = std::ldexp(1.0, std::ilogb(mx) + 2);
+            sg[r] = std::ldexp(1.0, std::ilogb(mx) + 1);
+            if (mx > 0.98 * sg[r]) sg[r] *= 2;
             inv[r] = 1.0 / sg[r];
         }
     };
@@ -109,49 +110,43 @@ int main(int argc, char** argv) {
             maxrec = std::fmax(maxrec, (double)fabsl(u * p.sa[r] - p.A[(size_t)r * K + k]) / p.sa[r]);
         }
         printf("[slicer] max |reconstruction - x| / sigma = %.3e (expect <= 2^-56 = 1.4e-17)\n", maxrec);
-        // 2. GEMM
-        std::vector<long long> acc((size_t)M * N * NS, 0);
+        // 2. GEMM: groups g = s + t < NG; host integer sums for all 13 groups, FP64 reference in long double
+        const int NGMAX = 8;
+        std::vector<long long> acc((size_t)M * N * NGMAX, 0);
         std::vector<double> Cref((size_t)M * N);
         for (int m = 0; m < M; ++m) for (int n = 0; n < N; ++n) {
             long double ref = 0;
-            long long* a = &acc[((size_t)m * N + n) * NS];
+            long long* a = &acc[((size_t)m * N + n) * NGMAX];
             for (int k = 0; k < K; ++k) {
                 ref += (long double)p.A[(size_t)m * K + k] * (long double)p.B[(size_t)n * K + k];
                 const int8_t* da = &DA[((size_t)m * K + k) * NS]; const int8_t* db = &DB[((size_t)n * K + k) * NS];
-                for (int s = 0; s < NS; ++s) for (int t = 0; s + t < NS; ++t) a[s + t] += (long long)da[s] * db[t];
+                for (int s = 0; s < NS; ++s) for (int t = 0; t < NS && s + t < NGMAX; ++t) a[s + t] += (long long)da[s] * db[t];
             }
             Cref[(size_t)m * N + n] = (double)ref;
         }
-        struct Variant { const char* name; unsigned long long sdesc; };
-        const unsigned long long base = (1ull << 46);
-        Variant vars[] = {
-            {"default (LBO=128, SBO=1792)", 0ull},
-            {"swapped (LBO=1792, SBO=128)", base | ((unsigned long long)(1792 >> 4) << 16) | ((unsigned long long)(128 >> 4) << 32)},
-            {"default without version bit", ((unsigned long long)(128 >> 4) << 16) | ((unsigned long long)(1792 >> 4) << 32)},
-        };
-        bool ok_any = false;
-        for (auto& v : vars) {
-            CK(cudaMemset(dC, 0xFF, (size_t)M * N * 8)); CK(cudaMemset(dbg, 0xFF, (size_t)tiles * NS * 128 * 64 * 4));
-            GK(gpk_oz_gemm_tn(sA, sB, M, N, K, dsa, dsb, dC, N, dbg, 0, v.sdesc, nullptr));
+        cudaFree(dbg);
+        CK(cudaMalloc(&dbg, (size_t)tiles * NGMAX * 128 * 64 * 4));
+        for (int NG : {7, 8}) {
+            CK(cudaMemset(dC, 0xFF, (size_t)M * N * 8)); CK(cudaMemset(dbg, 0xFF, (size_t)tiles * NGMAX * 128 * 64 * 4));
+            GK(gpk_oz_gemm_tn(sA, sB, M, N, K, dsa, dsb, dC, N, dbg, NG, nullptr));
             cudaError_t e = cudaDeviceSynchronize();
-            if (e != cudaSuccess) { printf("[gemm %s] kernel failed: %s\n", v.name, cudaGetErrorString(e)); fails++; break; }
-            std::vector<int> hd((size_t)tiles * NS * 128 * 64);
+            if (e != cudaSuccess) { printf("[gemm NG=%d] kernel failed: %s\n", NG, cudaGetErrorString(e)); fails++; break; }
+            std::vector<int> hd((size_t)tiles * NG * 128 * 64);
             std::vector<double> hC((size_t)M * N);
             CK(cudaMemcpy(hd.data(), dbg, hd.size() * 4, cudaMemcpyDeviceToHost)); CK(cudaMemcpy(hC.data(), dC, hC.size() * 8, cudaMemcpyDeviceToHost));
             long long ibad = 0; double maxerr = 0;
             for (int m = 0; m < M; ++m) for (int n = 0; n < N; ++n) {
                 const int mb = m / 128, nb = n / 64, tile = mb * (N / 64) + nb;
-                for (int g = 0; g < NS; ++g) {
-                    const int got = hd[(((size_t)tile * NS + g) * 128 + (m % 128)) * 64 + (n % 64)];
-                    if ((long long)got != acc[((size_t)m * N + n) * NS + g]) { if (ibad < 6) printf("  acc mismatch m=%d n=%d g=%d gpu=%d host=%lld\n", m, n, g, got, acc[((size_t)m * N + n) * NS + g]); ++ibad; }
+                for (int g = 0; g < NG; ++g) {
+                    const int got = hd[(((size_t)tile * NG + g) * 128 + (m % 128)) * 64 + (n % 64)];
+                    if ((long long)got != acc[((size_t)m * N + n) * NGMAX + g]) { if (ibad < 6) printf("  acc mismatch m=%d n=%d g=%d gpu=%d host=%lld\n", m, n, g, got, acc[((size_t)m * N + n) * NGMAX + g]); ++ibad; }
                 }
                 const double scale = p.sa[m] * p.sb[n];
                 maxerr = std::fmax(maxerr, std::fabs(hC[(size_t)m * N + n] - Cref[(size_t)m * N + n]) / scale);
             }
-            printf("[gemm %s] int32 accumulators differing: %lld of %d; max |C - ref| / (sigma_a sigma_b) = %.3e\n", v.name, ibad, M * N * NS, maxerr);
-            if (ibad == 0 && maxerr < 1e-13) { ok_any = true; if (&v != &vars[0]) printf("  NOTE: non-default descriptor variant is the correct one\n"); break; }
+            printf("[gemm NG=%d] int32 accumulators differing: %lld of %d; max |C - ref| / (sigma_a sigma_b) = %.3e\n", NG, ibad, M * N * NG, maxerr);
+            fails += !(ibad == 0 && maxerr < 1e-13);
         }
-        fails += !ok_any;
     }
     if (perf && fails == 0) {
         // many tiles, K = 2048: 2 M N K FP64-equivalent flop, 28 int8 MACs each
@@ -161,24 +156,28 @@ int main(int argc, char** argv) {
         CK(cudaMalloc(&sA, bA)); CK(cudaMalloc(&sB, bB)); CK(cudaMalloc(&dC, (size_t)M * N * 8));
         CK(cudaMemset(sA, 0x11, bA)); CK(cudaMemset(sB, 0x07, bB));
         cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
-        for (int it = 0; it < 2; ++it) GK(gpk_oz_gemm_tn(sA, sB, M, N, K, nullptr, nullptr, dC, N, nullptr, 0, 0, nullptr));
-        CK(cudaDeviceSynchronize());
         const int reps = 5;
-        CK(cudaEventRecord(e0));
-        for (int it = 0; it < reps; ++it) GK(gpk_oz_gemm_tn(sA, sB, M, N, K, nullptr, nullptr, dC, N, nullptr, 0, 0, nullptr));
-        CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
-        float ms; CK(cudaEventElapsedTime(&ms, e0, e1)); ms /= reps;
-        const double flop = 2.0 * M * N * K;
-        printf("[perf] M=%d N=%d K=%d: %.3f ms per GEMM, %.1f TFLOP/s FP64-equivalent, %.0f int8 TOPS\n", M, N, K, ms, flop / ms * 1e-9, 28 * flop / ms * 1e-9);
+        float ms;
+        for (int ng : {7, 8}) {
+            for (int it = 0; it < 2; ++it) GK(gpk_oz_gemm_tn(sA, sB, M, N, K, nullptr, nullptr, dC, N, nullptr, ng, nullptr));
+            CK(cudaDeviceSynchronize());
+            CK(cudaEventRecord(e0));
+            for (int it = 0; it < reps; ++it) GK(gpk_oz_gemm_tn(sA, sB, M, N, K, nullptr, nullptr, dC, N, nullptr, ng, nullptr));
+            CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
+            CK(cudaEventElapsedTime(&ms, e0, e1)); ms /= reps;
+            const double flop = 2.0 * M * N * K;
+            const int prods = ng == 7 ? 28 : 34;
+            printf("[perf] groups %d (%d digit products) M=%d N=%d K=%d: %.3f ms per GEMM, %.1f TFLOP/s FP64-equivalent, %.0f int8 TOPS\n", ng, prods, M, N, K, ms, flop / ms * 1e-9, prods * flop / ms * 1e-9);
+        }
         // K sweep (per-tile overheads)
         for (int k2 : {256, 1024, 4096}) {
             if ((size_t)gpk_oz_slice_bytes(M, k2) > bA * 2) continue;
             uint8_t *tA, *tB; CK(cudaMalloc(&tA, gpk_oz_slice_bytes(M, k2))); CK(cudaMalloc(&tB, gpk_oz_slice_bytes(N, k2)));
             CK(cudaMemset(tA, 0x11, gpk_oz_slice_bytes(M, k2))); CK(cudaMemset(tB, 0x07, gpk_oz_slice_bytes(N, k2)));
-            GK(gpk_oz_gemm_tn(tA, tB, M, N, k2, nullptr, nullptr, dC, N, nullptr, 0, 0, nullptr));
+            GK(gpk_oz_gemm_tn(tA, tB, M, N, k2, nullptr, nullptr, dC, N, nullptr, 8, nullptr));
             CK(cudaDeviceSynchronize());
             CK(cudaEventRecord(e0));
-            for (int it = 0; it < reps; ++it) GK(gpk_oz_gemm_tn(tA, tB, M, N, k2, nullptr, nullptr, dC, N, nullptr, 0, 0, nullptr));
+            for (int it = 0; it < reps; ++it) GK(gpk_oz_gemm_tn(tA, tB, M, N, k2, nullptr, nullptr, dC, N, nullptr, 8, nullptr));
             CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
             CK(cudaEventElapsedTime(&ms, e0, e1)); ms /= reps;
             printf("[perf] K=%d: %.3f ms, %.1f TFLOP/s FP64-equivalent\n", k2, ms, 2.0 * M * N * k2 / ms * 1e-9);

@@ -26,14 +26,16 @@ __device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t da, uint64_t d
 }
 
 // mode 0: every MMA reads a different A slice and B slice (like the digit GEMM); mode 1: same A for all MMAs of a batch
-__global__ void __launch_bounds__(128, 1) k_probe(int N, int batches, int per_batch, int mode, long long* clocks_out) {
+template <int N, int MODE>
+__global__ void __launch_bounds__(128, 1) k_probe(int batches, long long* clocks_out) {
+    constexpr int per_batch = 28;
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ uint64_t bar;
+    __shared__ uint64_t bar[4];
     __shared__ uint32_t tmem_slot;
     const int tid = threadIdx.x, warp = tid >> 5;
     for (int i = tid; i < 160 * 1024 / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0x01010101u * (i & 3);
     if (tid == 0) {
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(smem_u32(&bar)));
+        for (int i = 0; i < 4; ++i) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(smem_u32(&bar[i])));
         asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
     }
     if (warp == 0) {
@@ -50,19 +52,20 @@ __global__ void __launch_bounds__(128, 1) k_probe(int N, int batches, int per_ba
         // K-major no-swizzle, slice-major layout: [slice][row group][2][8 x 16 B]: LBO = 128, SBO = 256
         const uint64_t sdesc = ((uint64_t)(128 >> 4) << 16) | ((uint64_t)(256 >> 4) << 32) | (1ull << 46);
         const uint32_t a0 = smem_u32(smem), b0 = a0 + 32 * 1024;     // A: 8 slices x 4 KB; B: up to 128 KB
-        const int nacc = 512 / N;
-        uint32_t ph = 0;
+        constexpr int nacc = 512 / N;
+        const uint64_t da = sdesc | ((a0 >> 4) & 0x3FFF), db = sdesc | ((b0 >> 4) & 0x3FFF);
         const long long t0 = clock64();
         for (int it = 0; it < batches; ++it) {
+#pragma unroll
             for (int j = 0; j < per_batch; ++j) {
-                const uint32_t aa = a0 + ((mode == 1) ? 0 : (j & 7) * 4096);
-                const uint32_t bb = b0 + (j % 4) * (N * 32);
-                umma_i8(tmem + (j % nacc) * N, sdesc | ((aa >> 4) & 0x3FFF), sdesc | ((bb >> 4) & 0x3FFF), idesc, (it | j) ? 1u : 0u);
+                const uint32_t ao = (MODE == 1) ? 0 : (j & 7) * (4096 >> 4);
+                const uint32_t bo = (j % 4) * ((N * 32) >> 4);
+                umma_i8(tmem + (j % nacc) * N, da + ao, db + bo, idesc, (it > 0 || j >= nacc) ? 1u : 0u);
             }
-            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(smem_u32(&bar)) : "memory");
-            if (it >= 2) { mbar_wait(smem_u32(&bar), ph); ph ^= 1; }   // keep at most 3 batches in flight
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(smem_u32(&bar[it & 3])) : "memory");
+            if (it >= 2) mbar_wait(smem_u32(&bar[(it - 2) & 3]), ((it - 2) >> 2) & 1);   // at most 3 batches in flight
         }
-        for (int r = 0; r < 2 && r < batches; ++r) { mbar_wait(smem_u32(&bar), ph); ph ^= 1; }
+        for (int it = (batches >= 2 ? batches - 2 : 0); it < batches; ++it) mbar_wait(smem_u32(&bar[it & 3]), (it >> 2) & 1);
         clocks_out[blockIdx.x] = clock64() - t0;
     }
     asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
@@ -73,19 +76,22 @@ __global__ void __launch_bounds__(128, 1) k_probe(int N, int batches, int per_ba
 int main() {
     alarm(120);
     const int smem_bytes = 160 * 1024;
-    CK(cudaFuncSetAttribute(k_probe, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
     long long* d_clk;
     CK(cudaMalloc(&d_clk, 148 * 8));
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
     const int batches = 400, per_batch = 28;
+    typedef void (*kern_t)(int, long long*);
+    kern_t kerns[2][3] = {{k_probe<64, 0>, k_probe<128, 0>, k_probe<256, 0>}, {k_probe<64, 1>, k_probe<128, 1>, k_probe<256, 1>}};
+    for (int m = 0; m < 2; ++m) for (int n = 0; n < 3; ++n) CK(cudaFuncSetAttribute(kerns[m][n], cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
     for (int grid : {1, 148}) {
         for (int mode = 0; mode < 2; ++mode) {
-            for (int N : {64, 128, 256}) {
-                k_probe<<<grid, 128, smem_bytes>>>(N, 20, per_batch, mode, d_clk);      // warm-up
+            for (int ni = 0; ni < 3; ++ni) {
+                const int N = 64 << ni;
+                kerns[mode][ni]<<<grid, 128, smem_bytes>>>(20, d_clk);      // warm-up
                 CK(cudaDeviceSynchronize());
                 CK(cudaEventRecord(e0));
-                k_probe<<<grid, 128, smem_bytes>>>(N, batches, per_batch, mode, d_clk);
+                kerns[mode][ni]<<<grid, 128, smem_bytes>>>(batches, d_clk);
                 CK(cudaEventRecord(e1));
                 CK(cudaEventSynchronize(e1));
                 float ms;
