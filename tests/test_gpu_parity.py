@@ -22,6 +22,14 @@ def mods():
     return dict(GP_func=GP_func, fls=find_len_scales, cps=calc_prob_surf, engine=engine, pso=pso)
 
 
+@pytest.fixture(params=["fp64", "emu"])
+def precision(request, mods):
+    """Both arithmetic modes of the blocked path (N > 128): native DMMA and emulated FP64 on int8 tcgen05."""
+    mods["engine"].set_precision(request.param)
+    yield request.param
+    mods["engine"].set_precision("auto")
+
+
 # ------------------------------------------------------------------ (a) covariance
 def test_kernel_func_golden(mods):
     g = load_golden("kernel_cases.npz")
@@ -90,7 +98,7 @@ def _loss_check(mods, c, name):
     return loss
 
 
-def test_loss_golden(mods):
+def test_loss_golden(mods, precision):
     g = load_golden("loss_cases.npz")
     for name in g["names"]:
         _loss_check(mods, case(g, str(name)), str(name))
@@ -112,7 +120,7 @@ def test_evaluate_loss_dropin_signatures(mods):
 
 @pytest.mark.parametrize("n,d,p,seed", [(1, 1, 2, 0), (2, 2, 3, 1), (33, 1, 4, 2), (127, 3, 4, 3), (129, 2, 3, 4),
                                         (256, 3, 3, 5), (500, 2, 2, 6)])
-def test_loss_vs_oracle_seeded(mods, n, d, p, seed):
+def test_loss_vs_oracle_seeded(mods, precision, n, d, p, seed):
     """Edge sizes (single point, just around the 128 small/blocked switch, ragged padding)."""
     rng = np.random.default_rng(seed)
     x = rng.random((d, n))
@@ -143,7 +151,7 @@ def test_loss_not_positive_definite_raises(mods):
 
 
 # ------------------------------------------------------------------ (c) fit + predict
-def test_gp_golden(mods):
+def test_gp_golden(mods, precision):
     g = load_golden("gp_cases.npz")
     for name in g["names"]:
         c = case(g, str(name))

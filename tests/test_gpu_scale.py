@@ -14,6 +14,14 @@ def eng():
     return engine, pso
 
 
+@pytest.fixture(params=["fp64", "emu"], autouse=True)
+def precision(request, eng):
+    """Every full-size check runs in both arithmetic modes of the blocked path."""
+    eng[0].set_precision(request.param)
+    yield request.param
+    eng[0].set_precision("auto")
+
+
 def test_loss_n4096_two_routes_agree(eng):
     """C3 shape.  The loss kernels use mu-y = -D alpha and var = d - d^2 diag(K^-1) (blocked inverse);
     the predict kernels use the reference's form mu = K_s^T alpha, var = 1 - |L^-1 k|^2.  Two independent
