@@ -90,12 +90,15 @@ BlockedLayout blocked_layout(int P, int N, int d, int emulated) {
     L.cn = take((size_t)P * Np * 8);
     L.z = take((size_t)P * Np * 8);
     L.alpha = take((size_t)P * Np * 8);
-    L.oz_slices = L.oz_mt = L.oz_rows = L.oz_mtsc = 0;
+    L.oz_slices = L.oz_mt = L.oz_rows = L.oz_mtsc = L.oz_sdig = L.oz_ddig = L.oz_dsc = 0;
     if (emulated) {
         L.oz_slices = take((size_t)P * oz_slice_bytes(L.Np));
         L.oz_mt = take((size_t)P * oz_mt_bytes(L.Np));
         L.oz_rows = take((size_t)4 * Np * 8);
         L.oz_mtsc = take((size_t)2 * P * NB * 8);
+        L.oz_sdig = take((size_t)P * oz_panel_bytes(L.Np));
+        L.oz_ddig = take((size_t)P * oz_ddig_bytes(L.Np));
+        L.oz_dsc = take((size_t)P * T * 2 * NB * 8);
     }
     L.total = off;
     return L;
@@ -105,6 +108,9 @@ BlockedLayout blocked_layout(int P, int N, int d, int emulated) {
 struct OzBuffers {
     uint8_t* slices = nullptr;
     uint8_t* mtslices = nullptr;
+    uint8_t* sdig = nullptr;
+    uint8_t* ddig = nullptr;
+    double* dsc = nullptr;
     double *rowsig = nullptr, *rowinv = nullptr, *gam = nullptr, *gaminv = nullptr, *mtsig = nullptr, *mtinv = nullptr;
 };
 
@@ -117,6 +123,9 @@ static OzBuffers oz_buffers(char* ws, const BlockedLayout& L) {
     o.rowsig = r; o.rowinv = r + L.Np; o.gam = r + 2 * (size_t)L.Np; o.gaminv = r + 3 * (size_t)L.Np;
     double* m = (double*)(ws + L.oz_mtsc);
     o.mtsig = m; o.mtinv = m + (size_t)L.P * NB;
+    o.sdig = (uint8_t*)(ws + L.oz_sdig);
+    o.ddig = (uint8_t*)(ws + L.oz_ddig);
+    o.dsc = (double*)(ws + L.oz_dsc);
     return o;
 }
 
@@ -124,14 +133,25 @@ static OzBuffers oz_buffers(char* ws, const BlockedLayout& L) {
 static int factor_phase(double* mat, int Np, int T, int P, double* dinv, double* dinvT, int* info,
                         const unsigned char* active, int mode, const OzBuffers& oz, cudaStream_t st) {
     for (int J = 0; J < T; ++J) {
-        if (oz.slices) {
-            if (launch_oz_syrk(mat, Np, T, J, P, oz.slices, oz.rowsig, active, st)) return 1;
-        } else {
+        if (!oz.slices) {
             if (launch_syrk_update(mat, Np, T, J, P, active, st)) return 1;
+            if (launch_diag_block(mat, Np, J, P, dinv, dinvT, T, info, active, mode, st)) return 1;
+            if (launch_trsm_panel(mat, Np, T, J, P, dinv, active, st)) return 1;
+            continue;
+        }
+        // emulated FP64: every contraction on the digit GEMM.  The SYRK epilogue leaves the digits of S_IJ, the
+        // TRSM reads them with the digits of D_J and leaves L_IJ and its digits for the later SYRKs.
+        if (J > 0) {
+            if (launch_oz_syrk(mat, Np, T, J, P, oz.slices, oz.rowsig, oz.rowinv, oz.sdig, active, st)) return 1;
         }
         if (launch_diag_block(mat, Np, J, P, dinv, dinvT, T, info, active, mode, st)) return 1;
-        if (launch_trsm_panel(mat, Np, T, J, P, dinv, active, st)) return 1;
-        if (oz.slices && launch_oz_slice_l(mat, Np, T, J, P, oz.rowinv, oz.slices, active, st)) return 1;
+        if (launch_oz_slice_d(dinv, dinvT, T, J, P, oz.rowsig, oz.ddig, oz.dsc, active, st)) return 1;
+        if (J == 0) {        // no SYRK ran: the first block column is still the raw covariance, no digits of it exist
+            if (launch_trsm_panel(mat, Np, T, J, P, dinv, active, st)) return 1;
+            if (launch_oz_slice_l(mat, Np, T, J, P, oz.rowinv, oz.slices, active, st)) return 1;
+        } else {
+            if (launch_oz_trsm(mat, Np, T, J, P, oz.sdig, oz.ddig, oz.dsc, oz.rowsig, oz.rowinv, oz.slices, active, st)) return 1;
+        }
     }
     return 0;
 }
@@ -141,12 +161,12 @@ static int inverse_phase(double* mat, int Np, int T, int P, const double* dinvT,
                          const unsigned char* active, const OzBuffers& oz, cudaStream_t st) {
     if (oz.slices && launch_oz_slice_w(mat, Np, T, 0, 1, P, oz.gam, oz.slices, active, st)) return 1;
     for (int J = T - 2; J >= 0; --J) {
-        if (launch_inv_panel(mat, Np, T, J, P, dinvT, mt, active, st)) return 1;
         if (oz.slices) {
+            if (launch_oz_invp(mt, Np, T, J, P, oz.ddig, oz.dsc, oz.slices, oz.rowsig, active, st)) return 1;
             if (launch_oz_mt(mt, Np, T, J, P, oz.gaminv, oz.mtsig, oz.mtinv, oz.mtslices, active, st)) return 1;
-            if (launch_oz_invu(mat, Np, T, J, P, oz.slices, oz.mtslices, oz.mtsig, active, st)) return 1;
-            if (J > 0 && launch_oz_slice_w(mat, Np, T, J, 0, P, oz.gam, oz.slices, active, st)) return 1;
+            if (launch_oz_invu(mat, Np, T, J, P, oz.slices, oz.mtslices, oz.mtsig, oz.gam, 1, active, st)) return 1;
         } else {
+            if (launch_inv_panel(mat, Np, T, J, P, dinvT, mt, active, st)) return 1;
             if (launch_inv_update(mat, Np, T, J, P, mt, active, st)) return 1;
         }
     }
@@ -300,7 +320,8 @@ size_t gpk_fit_workspace_bytes(int N, int d) {
     const size_t Np = round_up(N, NB), T = Np / NB;
     size_t b = 2 * align256(T * NB * NB * 8) + align256(NB * Np * 8) + 2 * align256(Np * 8);
     if (g_precision)
-        b += align256(oz_slice_bytes((int)Np)) + align256(oz_mt_bytes((int)Np)) + align256(4 * Np * 8) + align256(2 * NB * 8);
+        b += align256(oz_slice_bytes((int)Np)) + align256(oz_mt_bytes((int)Np)) + align256(4 * Np * 8) + align256(2 * NB * 8) +
+             align256(oz_panel_bytes((int)Np)) + align256(oz_ddig_bytes((int)Np)) + align256(T * 2 * NB * 8);
     return b;
 }
 
@@ -325,7 +346,10 @@ int gpk_fit(const double* X, const double* y, const double* e, const double* ls,
         oz.mtslices = (uint8_t*)(ws + off); off += align256(oz_mt_bytes(Np));
         double* r = (double*)(ws + off); off += align256((size_t)4 * Np * 8);
         oz.rowsig = r; oz.rowinv = r + Np; oz.gam = r + 2 * (size_t)Np; oz.gaminv = r + 3 * (size_t)Np;
-        oz.mtsig = (double*)(ws + off); oz.mtinv = oz.mtsig + NB;
+        oz.mtsig = (double*)(ws + off); oz.mtinv = oz.mtsig + NB; off += align256((size_t)2 * NB * 8);
+        oz.sdig = (uint8_t*)(ws + off); off += align256(oz_panel_bytes(Np));
+        oz.ddig = (uint8_t*)(ws + off); off += align256(oz_ddig_bytes(Np));
+        oz.dsc = (double*)(ws + off);
         if (launch_oz_prep(e, N, Np, oz.rowsig, oz.rowinv, oz.gam, oz.gaminv, st)) return 1;
     }
     if (cudaMemsetAsync(info, 0, sizeof(int), st) != cudaSuccess) { set_error("memset info failed"); return 1; }

@@ -106,6 +106,14 @@ __device__ __forceinline__ double ll2d_exact(long long v) {
     return __longlong_as_double(0x4338000000000000LL + v) - 6755399441055744.0;
 }
 
+// byte b of four 32-bit words -> one word (digit b of four consecutive k)
+__device__ __forceinline__ uint32_t pack_digit(const uint32_t* w, int b) {
+    const uint32_t sel = (uint32_t)b | ((uint32_t)(4 + b) << 4);
+    const uint32_t t0 = __byte_perm(w[0], w[1], sel);
+    const uint32_t t1 = __byte_perm(w[2], w[3], sel);
+    return __byte_perm(t0, t1, 0x5410);
+}
+
 enum OzEpi { OZ_SUB = 0, OZ_STORE = 1, OZ_STORE_NEG = 2 };
 
 struct OzTile {
@@ -118,6 +126,11 @@ struct OzTile {
     double sa_const;      // multiplies every row scale (use it alone when sa == nullptr)
     const double* sb;     // scales of the 64 B rows, or nullptr (= 1)
     int* dbg;             // optional raw accumulator dump [NG][128][64]
+    // optional fused slicing of the tile's FP64 output (the next contraction's operand):
+    uint8_t* dig;          // record of (output row block, K chunk of the tile's first column); nullptr = none
+    const double* dig_rs;  // 128 row multipliers or nullptr
+    double dig_rconst;     // u = value * dig_rs[row] * dig_rconst * dig_cs[col], |u| <= 0.98
+    const double* dig_cs;  // 64 column multipliers or nullptr
 };
 
 // The MMAs of one K chunk.  NG = number of digit groups kept (g = s + t < NG): 7 -> 28 digit products, 8 -> 34.
@@ -210,6 +223,9 @@ __device__ __forceinline__ void oz_tile(const OzTile& t, uint8_t* smem) {
         const double rs = (t.sa ? t.sa[row] : 1.0) * t.sa_const * 0x1p-14;
         double* crow = t.c + (size_t)row * t.ldc + ch * 32;
         const double* sbp = t.sb ? t.sb + ch * 32 : nullptr;
+        const double drs = (t.dig_rs ? t.dig_rs[row] : 1.0) * t.dig_rconst * 0x1p55;
+        const double* dcs = t.dig_cs ? t.dig_cs + ch * 32 : nullptr;
+        uint8_t* drow = t.dig ? t.dig + (size_t)ch * OZ_CHUNK + (row >> 3) * 256 + (row & 7) * 16 : nullptr;
         double2 cold[16];
         if (EPI == OZ_SUB) {                     // the tile is final input data: fetch it while the MMAs run
 #pragma unroll
@@ -257,6 +273,28 @@ __device__ __forceinline__ void oz_tile(const OzTile& t, uint8_t* smem) {
                     o.y = -v[2 * j + 1];
                 }
                 cp[j] = o;
+                v[2 * j] = o.x;
+                v[2 * j + 1] = o.y;
+            }
+            if (drow) {                          // digits of the stored values, 8 consecutive k of one record row
+                uint32_t lo[8], hi[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const double u = v[j] * (drs * (dcs ? dcs[cc + j] : 1.0));
+                    const long long w = (__double2ll_rn(u) + OZ_BIAS) ^ OZ_BIAS;
+                    lo[j] = (uint32_t)w;
+                    hi[j] = (uint32_t)(w >> 32);
+                }
+                uint8_t* d = drow + (cc >> 4) * 128 + (cc & 15);
+#pragma unroll
+                for (int s = 0; s < OZ_NS; ++s) {
+                    const int bytepos = 6 - s;
+                    const uint32_t* w = (bytepos >= 4) ? hi : lo;
+                    uint2 o2;
+                    o2.x = pack_digit(w, bytepos & 3);
+                    o2.y = pack_digit(w + 4, bytepos & 3);
+                    *reinterpret_cast<uint2*>(d + s * OZ_DIGIT) = o2;
+                }
             }
         }
     }
@@ -274,7 +312,8 @@ __device__ __forceinline__ void oz_tile(const OzTile& t, uint8_t* smem) {
 template <int NG>
 __global__ void __launch_bounds__(OZ_THREADS, 1)
 k_oz_syrk(double* __restrict__ mat, int Np, int J, const uint8_t* __restrict__ slices, size_t slice_stride,
-          const double* __restrict__ rowsig, const unsigned char* __restrict__ active) {
+          const double* __restrict__ rowsig, const double* __restrict__ rowinv, uint8_t* __restrict__ sdig,
+          size_t sdig_stride, const unsigned char* __restrict__ active) {
     extern __shared__ __align__(128) uint8_t oz_smem[];
     const int p = blockIdx.y;
     if (active && !active[p]) return;
@@ -291,6 +330,12 @@ k_oz_syrk(double* __restrict__ mat, int Np, int J, const uint8_t* __restrict__ s
     t.sa_const = 1.0;
     t.sb = rowsig + J * NB + h * OZ_TILE_N;
     t.dbg = nullptr;
+    t.dig = nullptr; t.dig_rs = nullptr; t.dig_rconst = 1.0; t.dig_cs = nullptr;
+    if (sdig && I > J) {                           // digits of S_IJ / (rowsig_i rowsig_j): A operand of the TRSM
+        t.dig = sdig + (size_t)p * sdig_stride + ((size_t)I * 4 + 2 * h) * OZ_CHUNK;
+        t.dig_rs = rowinv + I * NB;
+        t.dig_cs = rowinv + J * NB + h * OZ_TILE_N;
+    }
     oz_tile<OZ_SUB, NG>(t, oz_smem);
 }
 
@@ -298,9 +343,9 @@ k_oz_syrk(double* __restrict__ mat, int Np, int J, const uint8_t* __restrict__ s
 // blockIdx.x = 2 * (T - 1 - I) + half (deepest contraction first), blockIdx.y = particle.
 template <int NG>
 __global__ void __launch_bounds__(OZ_THREADS, 1)
-k_oz_invu(double* __restrict__ mat, int Np, int T, int J, const uint8_t* __restrict__ slices, size_t slice_stride,
+k_oz_invu(double* __restrict__ mat, int Np, int T, int J, uint8_t* slices, size_t slice_stride,
           const uint8_t* __restrict__ mtslices, size_t mt_stride, const double* __restrict__ mtsig,
-          const unsigned char* __restrict__ active) {
+          const double* __restrict__ gam, int emit, const unsigned char* __restrict__ active) {
     extern __shared__ __align__(128) uint8_t oz_smem[];
     const int p = blockIdx.y;
     if (active && !active[p]) return;
@@ -316,6 +361,11 @@ k_oz_invu(double* __restrict__ mat, int Np, int T, int J, const uint8_t* __restr
     t.sa_const = 2.0;                              // W gamma is sliced with sigma = 2
     t.sb = mtsig + (size_t)p * NB + h * OZ_TILE_N;
     t.dbg = nullptr;
+    t.dig = nullptr; t.dig_rs = nullptr; t.dig_rconst = 0.5; t.dig_cs = nullptr;
+    if (emit && J > 0) {                           // digits of W gamma / 2 for the later steps J' < J
+        t.dig = slices + (size_t)p * slice_stride + ((size_t)I * kch + 4 * J + 2 * h) * OZ_CHUNK;
+        t.dig_cs = gam + J * NB + h * OZ_TILE_N;
+    }
     oz_tile<OZ_STORE_NEG, NG>(t, oz_smem);
 }
 
@@ -336,16 +386,11 @@ k_oz_gemm_tn(const uint8_t* __restrict__ A, const uint8_t* __restrict__ B, int k
     t.sa_const = 1.0;
     t.sb = sb ? sb + nb * OZ_TILE_N : nullptr;
     t.dbg = dbg ? dbg + ((size_t)mb * gridDim.x + nb) * (NG * 128 * OZ_TILE_N) : nullptr;
+    t.dig = nullptr; t.dig_rs = nullptr; t.dig_rconst = 1.0; t.dig_cs = nullptr;
     oz_tile<OZ_STORE, NG>(t, oz_smem);
 }
 
 // ---- slicers: FP64 128 x 128 tile -> 4 chunk records ----------------------------------------------------------
-__device__ __forceinline__ uint32_t pack_digit(const uint32_t* w, int b) {
-    const uint32_t sel = (uint32_t)b | ((uint32_t)(4 + b) << 4);
-    const uint32_t t0 = __byte_perm(w[0], w[1], sel);
-    const uint32_t t1 = __byte_perm(w[2], w[3], sel);
-    return __byte_perm(t0, t1, 0x5410);
-}
 
 // u = x * rs[row] * rconst * cs[col];  |u| <= 0.98 is the caller's contract (a-priori bounds / measured maxima)
 __device__ __forceinline__ void oz_slice_tile(const double* __restrict__ src, int ld, const double* __restrict__ rs,
@@ -479,6 +524,94 @@ k_oz_slice_generic(const double* __restrict__ src, int ld, int kch, const double
                   dst + ((size_t)rb * kch + 4 * cb) * OZ_CHUNK);
 }
 
+// Digits of the inverse diagonal block D_J = L_JJ^-1 for the two panel contractions, with measured row scales:
+//   blockIdx.x = 0: D_J[n][j] * rowsig_j   (B operand of the TRSM  L_IJ = S_IJ D_J^T, whose A digits carry 1/rowsig_j)
+//   blockIdx.x = 1: D_J^T[n][j]            (A operand of the phase-2 panel  Mt = D_J^T L_RJ^T)
+// dig: [P][T][2][4 chunks], dsc: [P][T][2][NB] row scales sigma_n.
+__global__ void __launch_bounds__(256)
+k_oz_slice_d(const double* __restrict__ dinv, const double* __restrict__ dinvT, int T, int J,
+             const double* __restrict__ rowsig, uint8_t* __restrict__ dig, double* __restrict__ dsc,
+             const unsigned char* __restrict__ active) {
+    __shared__ double inv[NB];
+    const int p = blockIdx.y, which = blockIdx.x;
+    if (active && !active[p]) return;
+    const double* src = (which ? dinvT : dinv) + ((size_t)p * T + J) * NB * NB;
+    const double* cs = which ? nullptr : rowsig + J * NB;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int n = warp; n < NB; n += 8) {
+        double m = 0.0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int j = lane + 32 * q;
+            m = fmax(m, fabs(src[n * NB + j] * (cs ? cs[j] : 1.0)));
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if (lane == 0) {
+            const double sig = oz_scale_for(m);
+            inv[n] = 1.0 / sig;
+            dsc[(((size_t)p * T + J) * 2 + which) * NB + n] = sig;
+        }
+    }
+    __syncthreads();
+    oz_slice_tile(src, NB, inv, 1.0, cs, dig + (((size_t)p * T + J) * 2 + which) * (4 * (size_t)OZ_CHUNK));
+}
+
+// Panel solve on the digit GEMM: L_IJ = S_IJ D_J^T, I = J + 1 + blockIdx.x / 2.  A = digits of S_IJ / (rowsig_i rowsig_j)
+// left by the SYRK epilogue, B = digits of D_J rowsig_j; the epilogue stores L_IJ and its digits (L / rowsig_i).
+template <int NG>
+__global__ void __launch_bounds__(OZ_THREADS, 1)
+k_oz_trsm(double* __restrict__ mat, int Np, int T, int J, const uint8_t* __restrict__ sdig, size_t sdig_stride,
+          const uint8_t* __restrict__ ddig, const double* __restrict__ dsc, const double* __restrict__ rowsig,
+          const double* __restrict__ rowinv, uint8_t* __restrict__ slices, size_t slice_stride,
+          const unsigned char* __restrict__ active) {
+    extern __shared__ __align__(128) uint8_t oz_smem[];
+    const int p = blockIdx.y;
+    if (active && !active[p]) return;
+    const int I = J + 1 + (blockIdx.x >> 1), h = blockIdx.x & 1;
+    const int kch = Np / 32;
+    OzTile t;
+    t.a = sdig + (size_t)p * sdig_stride + (size_t)I * 4 * OZ_CHUNK;
+    t.b = ddig + (((size_t)p * T + J) * 2 + 0) * (4 * (size_t)OZ_CHUNK) + (size_t)h * OZ_DIGIT_HALF;
+    t.nk = 4;
+    t.c = mat + (size_t)p * Np * Np + (size_t)I * NB * Np + (size_t)J * NB + h * OZ_TILE_N;
+    t.ldc = Np;
+    t.sa = rowsig + I * NB;
+    t.sa_const = 1.0;
+    t.sb = dsc + (((size_t)p * T + J) * 2 + 0) * NB + h * OZ_TILE_N;
+    t.dbg = nullptr;
+    t.dig = slices + (size_t)p * slice_stride + ((size_t)I * kch + 4 * J + 2 * h) * OZ_CHUNK;
+    t.dig_rs = rowinv + I * NB;
+    t.dig_rconst = 1.0;
+    t.dig_cs = nullptr;
+    oz_tile<OZ_STORE, NG>(t, oz_smem);
+}
+
+// Phase-2 panel on the digit GEMM: Mt[n][r] = sum_j D_J^T[n][j] L[r][J NB + j], r in block R = J + 1 + blockIdx.x / 2.
+template <int NG>
+__global__ void __launch_bounds__(OZ_THREADS, 1)
+k_oz_invp(double* __restrict__ mt, int Np, int T, int J, const uint8_t* __restrict__ ddig,
+          const double* __restrict__ dsc, const uint8_t* __restrict__ slices, size_t slice_stride,
+          const double* __restrict__ rowsig, const unsigned char* __restrict__ active) {
+    extern __shared__ __align__(128) uint8_t oz_smem[];
+    const int p = blockIdx.y;
+    if (active && !active[p]) return;
+    const int R = J + 1 + (blockIdx.x >> 1), h = blockIdx.x & 1;
+    const int kch = Np / 32;
+    OzTile t;
+    t.a = ddig + (((size_t)p * T + J) * 2 + 1) * (4 * (size_t)OZ_CHUNK);
+    t.b = slices + (size_t)p * slice_stride + ((size_t)R * kch + 4 * J) * OZ_CHUNK + (size_t)h * OZ_DIGIT_HALF;
+    t.nk = 4;
+    t.c = mt + (size_t)p * NB * Np + (size_t)R * NB + h * OZ_TILE_N;
+    t.ldc = Np;
+    t.sa = dsc + (((size_t)p * T + J) * 2 + 1) * NB;
+    t.sa_const = 1.0;
+    t.sb = rowsig + R * NB + h * OZ_TILE_N;
+    t.dbg = nullptr;
+    t.dig = nullptr; t.dig_rs = nullptr; t.dig_rconst = 1.0; t.dig_cs = nullptr;
+    oz_tile<OZ_STORE, NG>(t, oz_smem);
+}
+
 // ---- launchers ------------------------------------------------------------------------------------------------
 template <typename K>
 static int oz_smem_attr(K kernel, bool& done) {
@@ -503,19 +636,53 @@ static int g_oz_groups = 8;     // digit groups kept: 8 -> 34 digit products (de
 void oz_set_groups(int ng) { g_oz_groups = (ng == 7) ? 7 : 8; }
 int oz_get_groups() { return g_oz_groups; }
 
+// launches KERNEL<7> or KERNEL<8> according to the digit-group setting (one smem-attribute call per instantiation)
+#define OZ_LAUNCH(KERNEL, GRID, ST, ...)                                                         \
+    do {                                                                                         \
+        static bool done7_ = false, done8_ = false;                                              \
+        if (g_oz_groups == 7) {                                                                  \
+            if (oz_smem_attr(KERNEL<7>, done7_)) return 1;                                       \
+            KERNEL<7><<<GRID, OZ_THREADS, OZ_SMEM_BYTES, ST>>>(__VA_ARGS__);                     \
+        } else {                                                                                 \
+            if (oz_smem_attr(KERNEL<8>, done8_)) return 1;                                       \
+            KERNEL<8><<<GRID, OZ_THREADS, OZ_SMEM_BYTES, ST>>>(__VA_ARGS__);                     \
+        }                                                                                        \
+    } while (0)
+
+size_t oz_panel_bytes(int Np) { return (size_t)(Np / NB) * 4 * OZ_CHUNK; }      // [T][4 chunks]: S digits of one block column
+size_t oz_ddig_bytes(int Np) { return (size_t)(Np / NB) * 2 * 4 * OZ_CHUNK; }   // [T][2][4 chunks]: D_J and D_J^T digits
+
+// sdig != nullptr: the epilogue also leaves the digits of S_IJ (I > J) for launch_oz_trsm
 int launch_oz_syrk(double* mat, int Np, int T, int J, int P, const uint8_t* slices, const double* rowsig,
-                   const unsigned char* active, cudaStream_t st) {
-    static bool done7 = false, done8 = false;
+                   const double* rowinv, uint8_t* sdig, const unsigned char* active, cudaStream_t st) {
     if (J == 0) return 0;
     const dim3 grid(2 * (T - J), P);
-    if (g_oz_groups == 7) {
-        if (oz_smem_attr(k_oz_syrk<7>, done7)) return 1;
-        k_oz_syrk<7><<<grid, OZ_THREADS, OZ_SMEM_BYTES, st>>>(mat, Np, J, slices, oz_slice_bytes(Np), rowsig, active);
-    } else {
-        if (oz_smem_attr(k_oz_syrk<8>, done8)) return 1;
-        k_oz_syrk<8><<<grid, OZ_THREADS, OZ_SMEM_BYTES, st>>>(mat, Np, J, slices, oz_slice_bytes(Np), rowsig, active);
-    }
+    OZ_LAUNCH(k_oz_syrk, grid, st, mat, Np, J, slices, oz_slice_bytes(Np), rowsig, rowinv, sdig, oz_panel_bytes(Np), active);
     return check_launch("k_oz_syrk");
+}
+
+int launch_oz_slice_d(const double* dinv, const double* dinvT, int T, int J, int P, const double* rowsig, uint8_t* ddig,
+                      double* dsc, const unsigned char* active, cudaStream_t st) {
+    k_oz_slice_d<<<dim3(2, P), 256, 0, st>>>(dinv, dinvT, T, J, rowsig, ddig, dsc, active);
+    return check_launch("k_oz_slice_d");
+}
+
+int launch_oz_trsm(double* mat, int Np, int T, int J, int P, const uint8_t* sdig, const uint8_t* ddig, const double* dsc,
+                   const double* rowsig, const double* rowinv, uint8_t* slices, const unsigned char* active,
+                   cudaStream_t st) {
+    if (J >= T - 1) return 0;
+    const dim3 grid(2 * (T - 1 - J), P);
+    OZ_LAUNCH(k_oz_trsm, grid, st, mat, Np, T, J, sdig, oz_panel_bytes(Np), ddig, dsc, rowsig, rowinv, slices,
+              oz_slice_bytes(Np), active);
+    return check_launch("k_oz_trsm");
+}
+
+int launch_oz_invp(double* mt, int Np, int T, int J, int P, const uint8_t* ddig, const double* dsc, const uint8_t* slices,
+                   const double* rowsig, const unsigned char* active, cudaStream_t st) {
+    if (J >= T - 1) return 0;
+    const dim3 grid(2 * (T - 1 - J), P);
+    OZ_LAUNCH(k_oz_invp, grid, st, mt, Np, T, J, ddig, dsc, slices, oz_slice_bytes(Np), rowsig, active);
+    return check_launch("k_oz_invp");
 }
 
 int launch_oz_slice_l(const double* mat, int Np, int T, int J, int P, const double* rowinv, uint8_t* slices,
@@ -542,20 +709,13 @@ int launch_oz_mt(const double* mt, int Np, int T, int J, int P, const double* ga
     return check_launch("k_oz_slice_mt");
 }
 
-int launch_oz_invu(double* mat, int Np, int T, int J, int P, const uint8_t* slices, const uint8_t* mtslices,
-                   const double* mtsig, const unsigned char* active, cudaStream_t st) {
-    static bool done7 = false, done8 = false;
+// emit != 0: the epilogue also writes the digits of W_IJ gamma / 2 (replaces launch_oz_slice_w for column J)
+int launch_oz_invu(double* mat, int Np, int T, int J, int P, uint8_t* slices, const uint8_t* mtslices,
+                   const double* mtsig, const double* gam, int emit, const unsigned char* active, cudaStream_t st) {
     if (J >= T - 1) return 0;
     const dim3 grid(2 * (T - 1 - J), P);
-    if (g_oz_groups == 7) {
-        if (oz_smem_attr(k_oz_invu<7>, done7)) return 1;
-        k_oz_invu<7><<<grid, OZ_THREADS, OZ_SMEM_BYTES, st>>>(mat, Np, T, J, slices, oz_slice_bytes(Np), mtslices,
-                                                              oz_mt_bytes(Np), mtsig, active);
-    } else {
-        if (oz_smem_attr(k_oz_invu<8>, done8)) return 1;
-        k_oz_invu<8><<<grid, OZ_THREADS, OZ_SMEM_BYTES, st>>>(mat, Np, T, J, slices, oz_slice_bytes(Np), mtslices,
-                                                              oz_mt_bytes(Np), mtsig, active);
-    }
+    OZ_LAUNCH(k_oz_invu, grid, st, mat, Np, T, J, slices, oz_slice_bytes(Np), mtslices, oz_mt_bytes(Np), mtsig, gam, emit,
+              active);
     return check_launch("k_oz_invu");
 }
 
@@ -567,15 +727,8 @@ int launch_oz_slice_generic(const double* src, int ld, int rows, int cols, const
 
 int launch_oz_gemm_tn(const uint8_t* A, const uint8_t* B, int M, int N, int K, const double* sa, const double* sb,
                       double* C, int ldc, int* dbg, cudaStream_t st) {
-    static bool done7 = false, done8 = false;
     const dim3 grid(N / OZ_TILE_N, M / NB);
-    if (g_oz_groups == 7) {
-        if (oz_smem_attr(k_oz_gemm_tn<7>, done7)) return 1;
-        k_oz_gemm_tn<7><<<grid, OZ_THREADS, OZ_SMEM_BYTES, st>>>(A, B, K / 32, sa, sb, C, ldc, dbg);
-    } else {
-        if (oz_smem_attr(k_oz_gemm_tn<8>, done8)) return 1;
-        k_oz_gemm_tn<8><<<grid, OZ_THREADS, OZ_SMEM_BYTES, st>>>(A, B, K / 32, sa, sb, C, ldc, dbg);
-    }
+    OZ_LAUNCH(k_oz_gemm_tn, grid, st, A, B, K / 32, sa, sb, C, ldc, dbg);
     return check_launch("k_oz_gemm_tn");
 }
 
