@@ -154,16 +154,19 @@ __device__ __forceinline__ void oz_issue_chunk(uint32_t tmem, uint64_t da, uint6
     }
 }
 
-// One 128 x 64 output tile per CTA.
-template <int EPI, int NG>
-__device__ __forceinline__ void oz_tile(const OzTile& t, uint8_t* smem) {
+// Persistent tile loop: CTA c computes the 128 x 64 tiles c, c + gridDim.x, ... ; f.make(tile, t) describes a tile
+// (false = nothing to do).  The operand ring runs across tile boundaries, so the next tile's first stages load while
+// the epilogue drains the accumulators (all 512 TMEM columns hold one tile: MMA and epilogue of one CTA alternate).
+template <int EPI, int NG, class F>
+__device__ __forceinline__ void oz_run(const F& f, int ntiles, uint8_t* smem) {
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
     uint8_t* ctrl = smem + (size_t)OZ_STAGES * OZ_STAGE;
     const uint32_t full0 = smem_u32(ctrl);                 // OZ_STAGES x 8 B
     const uint32_t empty0 = full0 + 8 * OZ_STAGES;         // OZ_STAGES x 8 B
-    const uint32_t accbar = empty0 + 8 * OZ_STAGES;        // 8 B
-    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(ctrl + 8 * (2 * OZ_STAGES + 1));
+    const uint32_t accbar = empty0 + 8 * OZ_STAGES;        // 8 B: accumulators complete (MMA -> epilogue)
+    const uint32_t freebar = accbar + 8;                   // 8 B: accumulators drained (epilogue -> MMA)
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(ctrl + 8 * (2 * OZ_STAGES + 2));
     const uint32_t stage0 = smem_u32(smem);
 
     if (tid == 0) {
@@ -172,6 +175,7 @@ __device__ __forceinline__ void oz_tile(const OzTile& t, uint8_t* smem) {
             mbar_init(empty0 + 8 * s, 1);
         }
         mbar_init(accbar, 1);
+        mbar_init(freebar, OZ_THREADS - 64);
         asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
     }
     if (warp == 2) {
@@ -188,9 +192,13 @@ __device__ __forceinline__ void oz_tile(const OzTile& t, uint8_t* smem) {
 
     if (warp == 0) {
         if (lane == 0) {
-            for (int k = 0; k < t.nk; ++k) {
-                const int s = k % OZ_STAGES;
-                const uint32_t ph = (uint32_t)(k / OZ_STAGES) & 1u;
+            OzTile t;
+            uint32_t kg = 0;                     // chunk counter across tiles = position in the ring
+            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+                if (!f.make(tile, t)) continue;
+            for (int k = 0; k < t.nk; ++k, ++kg) {
+                const uint32_t s = kg % OZ_STAGES;
+                const uint32_t ph = (kg / OZ_STAGES) & 1u;
                 mbar_wait(empty0 + 8 * s, ph ^ 1u);
                 mbar_expect_tx(full0 + 8 * s, OZ_STAGE);
                 const uint32_t dst = stage0 + s * OZ_STAGE;
@@ -200,12 +208,20 @@ __device__ __forceinline__ void oz_tile(const OzTile& t, uint8_t* smem) {
                     bulk_g2s(dst + OZ_CHUNK + d * OZ_DIGIT_HALF, t.b + (size_t)k * OZ_CHUNK + d * OZ_DIGIT, OZ_DIGIT_HALF,
                              full0 + 8 * s);
             }
+            }
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            for (int k = 0; k < t.nk; ++k) {
-                const int s = k % OZ_STAGES;
-                const uint32_t ph = (uint32_t)(k / OZ_STAGES) & 1u;
+            OzTile t;
+            uint32_t kg = 0, it = 0;
+            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+                if (!f.make(tile, t)) continue;
+                mbar_wait(freebar, (it & 1u) ^ 1u);      // the epilogue has drained the previous tile
+                tc_fence_after();
+                ++it;
+            for (int k = 0; k < t.nk; ++k, ++kg) {
+                const uint32_t s = kg % OZ_STAGES;
+                const uint32_t ph = (kg / OZ_STAGES) & 1u;
                 mbar_wait(full0 + 8 * s, ph);
                 tc_fence_after();
                 const uint64_t da = OZ_SDESC | (uint64_t)(((stage0 + s * OZ_STAGE) >> 4) & 0x3FFF);
@@ -214,12 +230,17 @@ __device__ __forceinline__ void oz_tile(const OzTile& t, uint8_t* smem) {
                 umma_commit(empty0 + 8 * s);     // frees the stage when these MMAs have read it
             }
             umma_commit(accbar);                 // accumulators complete
+            }
         }
     } else {
         // epilogue warps 2..9: TMEM lane quadrant = warp % 4, one output row and 32 of the 64 columns per thread
         const int q = warp & 3;
         const int ch = (warp - 2) >> 2;
         const int row = q * 32 + lane;
+        OzTile t;
+        uint32_t it = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        if (!f.make(tile, t)) continue;
         const double rs = (t.sa ? t.sa[row] : 1.0) * t.sa_const * 0x1p-14;
         double* crow = t.c + (size_t)row * t.ldc + ch * 32;
         const double* sbp = t.sb ? t.sb + ch * 32 : nullptr;
@@ -231,8 +252,9 @@ __device__ __forceinline__ void oz_tile(const OzTile& t, uint8_t* smem) {
 #pragma unroll
             for (int j = 0; j < 16; ++j) cold[j] = reinterpret_cast<const double2*>(crow)[j];
         }
-        mbar_wait(accbar, 0);
+        mbar_wait(accbar, it & 1u);
         tc_fence_after();
+        ++it;
         const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + ch * 32;
 #pragma unroll
         for (int cc = 0; cc < 32; cc += 8) {
@@ -297,6 +319,9 @@ __device__ __forceinline__ void oz_tile(const OzTile& t, uint8_t* smem) {
                 }
             }
         }
+        tc_fence_before();
+        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(freebar) : "memory");   // TMEM may be overwritten
+        }
     }
     tc_fence_before();
     __syncthreads();
@@ -306,89 +331,102 @@ __device__ __forceinline__ void oz_tile(const OzTile& t, uint8_t* smem) {
     }
 }
 
-// ---- kernels ----------------------------------------------------------------------------------------------
-// Left-looking Cholesky update of block column J: A_IJ -= sum_{K<J} L_IK L_JK^T from the digit slices of L.
-// blockIdx.x = 2 * (I - J) + half, blockIdx.y = particle.
-template <int NG>
-__global__ void __launch_bounds__(OZ_THREADS, 1)
-k_oz_syrk(double* __restrict__ mat, int Np, int J, const uint8_t* __restrict__ slices, size_t slice_stride,
-          const double* __restrict__ rowsig, const double* __restrict__ rowinv, uint8_t* __restrict__ sdig,
-          size_t sdig_stride, const unsigned char* __restrict__ active) {
+// ---- tile descriptions (functors) and the one persistent kernel ---------------------------------------------------
+template <int EPI, int NG, class F>
+__global__ void __launch_bounds__(OZ_THREADS, 1) k_oz(const F f, int ntiles) {
     extern __shared__ __align__(128) uint8_t oz_smem[];
-    const int p = blockIdx.y;
-    if (active && !active[p]) return;
-    const int I = J + (blockIdx.x >> 1), h = blockIdx.x & 1;
-    const int kch = Np / 32;
-    const uint8_t* S = slices + (size_t)p * slice_stride;
-    OzTile t;
-    t.a = S + (size_t)I * kch * OZ_CHUNK;
-    t.b = S + (size_t)J * kch * OZ_CHUNK + (size_t)h * OZ_DIGIT_HALF;
-    t.nk = 4 * J;
-    t.c = mat + (size_t)p * Np * Np + (size_t)I * NB * Np + (size_t)J * NB + h * OZ_TILE_N;
-    t.ldc = Np;
-    t.sa = rowsig + I * NB;
-    t.sa_const = 1.0;
-    t.sb = rowsig + J * NB + h * OZ_TILE_N;
-    t.dbg = nullptr;
-    t.dig = nullptr; t.dig_rs = nullptr; t.dig_rconst = 1.0; t.dig_cs = nullptr;
-    if (sdig && I > J) {                           // digits of S_IJ / (rowsig_i rowsig_j): A operand of the TRSM
-        t.dig = sdig + (size_t)p * sdig_stride + ((size_t)I * 4 + 2 * h) * OZ_CHUNK;
-        t.dig_rs = rowinv + I * NB;
-        t.dig_cs = rowinv + J * NB + h * OZ_TILE_N;
-    }
-    oz_tile<OZ_SUB, NG>(t, oz_smem);
+    oz_run<EPI, NG, F>(f, ntiles, oz_smem);
 }
 
-// Phase-2 update W_IJ = - sum_{k in [(J+1)NB, (I+1)NB)} (W gamma)[I-block][k] * (Mt / gamma)[:, k]^T.
-// blockIdx.x = 2 * (T - 1 - I) + half (deepest contraction first), blockIdx.y = particle.
-template <int NG>
-__global__ void __launch_bounds__(OZ_THREADS, 1)
-k_oz_invu(double* __restrict__ mat, int Np, int T, int J, uint8_t* slices, size_t slice_stride,
-          const uint8_t* __restrict__ mtslices, size_t mt_stride, const double* __restrict__ mtsig,
-          const double* __restrict__ gam, int emit, const unsigned char* __restrict__ active) {
-    extern __shared__ __align__(128) uint8_t oz_smem[];
-    const int p = blockIdx.y;
-    if (active && !active[p]) return;
-    const int I = T - 1 - (blockIdx.x >> 1), h = blockIdx.x & 1;
-    const int kch = Np / 32;
-    OzTile t;
-    t.a = slices + (size_t)p * slice_stride + ((size_t)I * kch + 4 * (J + 1)) * OZ_CHUNK;
-    t.b = mtslices + (size_t)p * mt_stride + (size_t)(4 * (J + 1)) * OZ_CHUNK + (size_t)h * OZ_DIGIT_HALF;
-    t.nk = 4 * (I - J);
-    t.c = mat + (size_t)p * Np * Np + (size_t)I * NB * Np + (size_t)J * NB + h * OZ_TILE_N;
-    t.ldc = Np;
-    t.sa = nullptr;
-    t.sa_const = 2.0;                              // W gamma is sliced with sigma = 2
-    t.sb = mtsig + (size_t)p * NB + h * OZ_TILE_N;
+__device__ __forceinline__ void oz_no_digits(OzTile& t) {
     t.dbg = nullptr;
-    t.dig = nullptr; t.dig_rs = nullptr; t.dig_rconst = 0.5; t.dig_cs = nullptr;
-    if (emit && J > 0) {                           // digits of W gamma / 2 for the later steps J' < J
-        t.dig = slices + (size_t)p * slice_stride + ((size_t)I * kch + 4 * J + 2 * h) * OZ_CHUNK;
-        t.dig_cs = gam + J * NB + h * OZ_TILE_N;
-    }
-    oz_tile<OZ_STORE_NEG, NG>(t, oz_smem);
+    t.dig = nullptr; t.dig_rs = nullptr; t.dig_rconst = 1.0; t.dig_cs = nullptr;
 }
 
-// Generic C = A B^T over sliced operands (test / library primitive): grid (N / 64, M / 128).
-template <int NG>
-__global__ void __launch_bounds__(OZ_THREADS, 1)
-k_oz_gemm_tn(const uint8_t* __restrict__ A, const uint8_t* __restrict__ B, int kch, const double* __restrict__ sa,
-             const double* __restrict__ sb, double* __restrict__ C, int ldc, int* dbg) {
-    extern __shared__ __align__(128) uint8_t oz_smem[];
-    const int nb = blockIdx.x, mb = blockIdx.y;
-    OzTile t;
-    t.a = A + (size_t)mb * kch * OZ_CHUNK;
-    t.b = B + (size_t)(nb >> 1) * kch * OZ_CHUNK + (size_t)(nb & 1) * OZ_DIGIT_HALF;
-    t.nk = kch;
-    t.c = C + (size_t)mb * NB * ldc + (size_t)nb * OZ_TILE_N;
-    t.ldc = ldc;
-    t.sa = sa ? sa + mb * NB : nullptr;
-    t.sa_const = 1.0;
-    t.sb = sb ? sb + nb * OZ_TILE_N : nullptr;
-    t.dbg = dbg ? dbg + ((size_t)mb * gridDim.x + nb) * (NG * 128 * OZ_TILE_N) : nullptr;
-    t.dig = nullptr; t.dig_rs = nullptr; t.dig_rconst = 1.0; t.dig_cs = nullptr;
-    oz_tile<OZ_STORE, NG>(t, oz_smem);
-}
+// Left-looking Cholesky update of block column J: A_IJ -= sum_{K<J} L_IK L_JK^T from the digits of L.
+// tile = p * nx + 2 * (I - J) + half.  sdig != nullptr: the epilogue also leaves the digits of
+// S_IJ / (rowsig_i rowsig_j), I > J, the A operand of the panel solve.
+struct OzSyrkTiles {
+    double* mat; int Np, J, nx;
+    const uint8_t* slices; size_t slice_stride;
+    const double* rowsig; const double* rowinv;
+    uint8_t* sdig; size_t sdig_stride;
+    const unsigned char* active;
+    __device__ __forceinline__ bool make(int tile, OzTile& t) const {
+        const int p = tile / nx, bx = tile - p * nx;
+        if (active && !active[p]) return false;
+        const int I = J + (bx >> 1), h = bx & 1;
+        const int kch = Np / 32;
+        const uint8_t* S = slices + (size_t)p * slice_stride;
+        t.a = S + (size_t)I * kch * OZ_CHUNK;
+        t.b = S + (size_t)J * kch * OZ_CHUNK + (size_t)h * OZ_DIGIT_HALF;
+        t.nk = 4 * J;
+        t.c = mat + (size_t)p * Np * Np + (size_t)I * NB * Np + (size_t)J * NB + h * OZ_TILE_N;
+        t.ldc = Np;
+        t.sa = rowsig + I * NB;
+        t.sa_const = 1.0;
+        t.sb = rowsig + J * NB + h * OZ_TILE_N;
+        oz_no_digits(t);
+        if (sdig && I > J) {
+            t.dig = sdig + (size_t)p * sdig_stride + ((size_t)I * 4 + 2 * h) * OZ_CHUNK;
+            t.dig_rs = rowinv + I * NB;
+            t.dig_cs = rowinv + J * NB + h * OZ_TILE_N;
+        }
+        return true;
+    }
+};
+
+// Phase-2 update W_IJ = - sum_{k in [(J+1)NB, (I+1)NB)} (W gamma)[I-block][k] * (Mt / gamma)[:, k]^T,
+// tile = p * nx + 2 * (T - 1 - I) + half (deepest contraction first).  emit: the epilogue also writes the digits of
+// W_IJ gamma / 2 for the later steps J' < J.
+struct OzInvuTiles {
+    double* mat; int Np, T, J, nx;
+    uint8_t* slices; size_t slice_stride;
+    const uint8_t* mtslices; size_t mt_stride;
+    const double* mtsig; const double* gam; int emit;
+    const unsigned char* active;
+    __device__ __forceinline__ bool make(int tile, OzTile& t) const {
+        const int p = tile / nx, bx = tile - p * nx;
+        if (active && !active[p]) return false;
+        const int I = T - 1 - (bx >> 1), h = bx & 1;
+        const int kch = Np / 32;
+        t.a = slices + (size_t)p * slice_stride + ((size_t)I * kch + 4 * (J + 1)) * OZ_CHUNK;
+        t.b = mtslices + (size_t)p * mt_stride + (size_t)(4 * (J + 1)) * OZ_CHUNK + (size_t)h * OZ_DIGIT_HALF;
+        t.nk = 4 * (I - J);
+        t.c = mat + (size_t)p * Np * Np + (size_t)I * NB * Np + (size_t)J * NB + h * OZ_TILE_N;
+        t.ldc = Np;
+        t.sa = nullptr;
+        t.sa_const = 2.0;                              // W gamma is sliced with sigma = 2
+        t.sb = mtsig + (size_t)p * NB + h * OZ_TILE_N;
+        oz_no_digits(t);
+        if (emit && J > 0) {
+            t.dig = slices + (size_t)p * slice_stride + ((size_t)I * kch + 4 * J + 2 * h) * OZ_CHUNK;
+            t.dig_rconst = 0.5;
+            t.dig_cs = gam + J * NB + h * OZ_TILE_N;
+        }
+        return true;
+    }
+};
+
+// Generic C = A B^T over sliced operands (test / library primitive): tile = mb * nx + nb, nx = N / 64.
+struct OzGemmTiles {
+    const uint8_t* A; const uint8_t* B; int kch, nx;
+    const double* sa; const double* sb; double* C; int ldc; int* dbg; int ng;
+    __device__ __forceinline__ bool make(int tile, OzTile& t) const {
+        const int mb = tile / nx, nb = tile - mb * nx;
+        t.a = A + (size_t)mb * kch * OZ_CHUNK;
+        t.b = B + (size_t)(nb >> 1) * kch * OZ_CHUNK + (size_t)(nb & 1) * OZ_DIGIT_HALF;
+        t.nk = kch;
+        t.c = C + (size_t)mb * NB * ldc + (size_t)nb * OZ_TILE_N;
+        t.ldc = ldc;
+        t.sa = sa ? sa + mb * NB : nullptr;
+        t.sa_const = 1.0;
+        t.sb = sb ? sb + nb * OZ_TILE_N : nullptr;
+        oz_no_digits(t);
+        t.dbg = dbg ? dbg + (size_t)tile * (ng * 128 * OZ_TILE_N) : nullptr;
+        return true;
+    }
+};
 
 // ---- slicers: FP64 128 x 128 tile -> 4 chunk records ----------------------------------------------------------
 
@@ -557,60 +595,61 @@ k_oz_slice_d(const double* __restrict__ dinv, const double* __restrict__ dinvT, 
     oz_slice_tile(src, NB, inv, 1.0, cs, dig + (((size_t)p * T + J) * 2 + which) * (4 * (size_t)OZ_CHUNK));
 }
 
-// Panel solve on the digit GEMM: L_IJ = S_IJ D_J^T, I = J + 1 + blockIdx.x / 2.  A = digits of S_IJ / (rowsig_i rowsig_j)
-// left by the SYRK epilogue, B = digits of D_J rowsig_j; the epilogue stores L_IJ and its digits (L / rowsig_i).
-template <int NG>
-__global__ void __launch_bounds__(OZ_THREADS, 1)
-k_oz_trsm(double* __restrict__ mat, int Np, int T, int J, const uint8_t* __restrict__ sdig, size_t sdig_stride,
-          const uint8_t* __restrict__ ddig, const double* __restrict__ dsc, const double* __restrict__ rowsig,
-          const double* __restrict__ rowinv, uint8_t* __restrict__ slices, size_t slice_stride,
-          const unsigned char* __restrict__ active) {
-    extern __shared__ __align__(128) uint8_t oz_smem[];
-    const int p = blockIdx.y;
-    if (active && !active[p]) return;
-    const int I = J + 1 + (blockIdx.x >> 1), h = blockIdx.x & 1;
-    const int kch = Np / 32;
-    OzTile t;
-    t.a = sdig + (size_t)p * sdig_stride + (size_t)I * 4 * OZ_CHUNK;
-    t.b = ddig + (((size_t)p * T + J) * 2 + 0) * (4 * (size_t)OZ_CHUNK) + (size_t)h * OZ_DIGIT_HALF;
-    t.nk = 4;
-    t.c = mat + (size_t)p * Np * Np + (size_t)I * NB * Np + (size_t)J * NB + h * OZ_TILE_N;
-    t.ldc = Np;
-    t.sa = rowsig + I * NB;
-    t.sa_const = 1.0;
-    t.sb = dsc + (((size_t)p * T + J) * 2 + 0) * NB + h * OZ_TILE_N;
-    t.dbg = nullptr;
-    t.dig = slices + (size_t)p * slice_stride + ((size_t)I * kch + 4 * J + 2 * h) * OZ_CHUNK;
-    t.dig_rs = rowinv + I * NB;
-    t.dig_rconst = 1.0;
-    t.dig_cs = nullptr;
-    oz_tile<OZ_STORE, NG>(t, oz_smem);
-}
+// Panel solve on the digit GEMM: L_IJ = S_IJ D_J^T, tile = p * nx + 2 * (I - J - 1) + half.  A = digits of
+// S_IJ / (rowsig_i rowsig_j) left by the SYRK epilogue, B = digits of D_J rowsig_j; the epilogue stores L_IJ and its
+// digits (L / rowsig_i).
+struct OzTrsmTiles {
+    double* mat; int Np, T, J, nx;
+    const uint8_t* sdig; size_t sdig_stride;
+    const uint8_t* ddig; const double* dsc;
+    const double* rowsig; const double* rowinv;
+    uint8_t* slices; size_t slice_stride;
+    const unsigned char* active;
+    __device__ __forceinline__ bool make(int tile, OzTile& t) const {
+        const int p = tile / nx, bx = tile - p * nx;
+        if (active && !active[p]) return false;
+        const int I = J + 1 + (bx >> 1), h = bx & 1;
+        const int kch = Np / 32;
+        t.a = sdig + (size_t)p * sdig_stride + (size_t)I * 4 * OZ_CHUNK;
+        t.b = ddig + (((size_t)p * T + J) * 2 + 0) * (4 * (size_t)OZ_CHUNK) + (size_t)h * OZ_DIGIT_HALF;
+        t.nk = 4;
+        t.c = mat + (size_t)p * Np * Np + (size_t)I * NB * Np + (size_t)J * NB + h * OZ_TILE_N;
+        t.ldc = Np;
+        t.sa = rowsig + I * NB;
+        t.sa_const = 1.0;
+        t.sb = dsc + (((size_t)p * T + J) * 2 + 0) * NB + h * OZ_TILE_N;
+        oz_no_digits(t);
+        t.dig = slices + (size_t)p * slice_stride + ((size_t)I * kch + 4 * J + 2 * h) * OZ_CHUNK;
+        t.dig_rs = rowinv + I * NB;
+        return true;
+    }
+};
 
-// Phase-2 panel on the digit GEMM: Mt[n][r] = sum_j D_J^T[n][j] L[r][J NB + j], r in block R = J + 1 + blockIdx.x / 2.
-template <int NG>
-__global__ void __launch_bounds__(OZ_THREADS, 1)
-k_oz_invp(double* __restrict__ mt, int Np, int T, int J, const uint8_t* __restrict__ ddig,
-          const double* __restrict__ dsc, const uint8_t* __restrict__ slices, size_t slice_stride,
-          const double* __restrict__ rowsig, const unsigned char* __restrict__ active) {
-    extern __shared__ __align__(128) uint8_t oz_smem[];
-    const int p = blockIdx.y;
-    if (active && !active[p]) return;
-    const int R = J + 1 + (blockIdx.x >> 1), h = blockIdx.x & 1;
-    const int kch = Np / 32;
-    OzTile t;
-    t.a = ddig + (((size_t)p * T + J) * 2 + 1) * (4 * (size_t)OZ_CHUNK);
-    t.b = slices + (size_t)p * slice_stride + ((size_t)R * kch + 4 * J) * OZ_CHUNK + (size_t)h * OZ_DIGIT_HALF;
-    t.nk = 4;
-    t.c = mt + (size_t)p * NB * Np + (size_t)R * NB + h * OZ_TILE_N;
-    t.ldc = Np;
-    t.sa = dsc + (((size_t)p * T + J) * 2 + 1) * NB;
-    t.sa_const = 1.0;
-    t.sb = rowsig + R * NB + h * OZ_TILE_N;
-    t.dbg = nullptr;
-    t.dig = nullptr; t.dig_rs = nullptr; t.dig_rconst = 1.0; t.dig_cs = nullptr;
-    oz_tile<OZ_STORE, NG>(t, oz_smem);
-}
+// Phase-2 panel on the digit GEMM: Mt[n][r] = sum_j D_J^T[n][j] L[r][J NB + j], r in block R,
+// tile = p * nx + 2 * (R - J - 1) + half.
+struct OzInvpTiles {
+    double* mt; int Np, T, J, nx;
+    const uint8_t* ddig; const double* dsc;
+    const uint8_t* slices; size_t slice_stride;
+    const double* rowsig;
+    const unsigned char* active;
+    __device__ __forceinline__ bool make(int tile, OzTile& t) const {
+        const int p = tile / nx, bx = tile - p * nx;
+        if (active && !active[p]) return false;
+        const int R = J + 1 + (bx >> 1), h = bx & 1;
+        const int kch = Np / 32;
+        t.a = ddig + (((size_t)p * T + J) * 2 + 1) * (4 * (size_t)OZ_CHUNK);
+        t.b = slices + (size_t)p * slice_stride + ((size_t)R * kch + 4 * J) * OZ_CHUNK + (size_t)h * OZ_DIGIT_HALF;
+        t.nk = 4;
+        t.c = mt + (size_t)p * NB * Np + (size_t)R * NB + h * OZ_TILE_N;
+        t.ldc = Np;
+        t.sa = dsc + (((size_t)p * T + J) * 2 + 1) * NB;
+        t.sa_const = 1.0;
+        t.sb = rowsig + R * NB + h * OZ_TILE_N;
+        oz_no_digits(t);
+        return true;
+    }
+};
 
 // ---- launchers ------------------------------------------------------------------------------------------------
 template <typename K>
@@ -636,18 +675,30 @@ static int g_oz_groups = 8;     // digit groups kept: 8 -> 34 digit products (de
 void oz_set_groups(int ng) { g_oz_groups = (ng == 7) ? 7 : 8; }
 int oz_get_groups() { return g_oz_groups; }
 
-// launches KERNEL<7> or KERNEL<8> according to the digit-group setting (one smem-attribute call per instantiation)
-#define OZ_LAUNCH(KERNEL, GRID, ST, ...)                                                         \
-    do {                                                                                         \
-        static bool done7_ = false, done8_ = false;                                              \
-        if (g_oz_groups == 7) {                                                                  \
-            if (oz_smem_attr(KERNEL<7>, done7_)) return 1;                                       \
-            KERNEL<7><<<GRID, OZ_THREADS, OZ_SMEM_BYTES, ST>>>(__VA_ARGS__);                     \
-        } else {                                                                                 \
-            if (oz_smem_attr(KERNEL<8>, done8_)) return 1;                                       \
-            KERNEL<8><<<GRID, OZ_THREADS, OZ_SMEM_BYTES, ST>>>(__VA_ARGS__);                     \
-        }                                                                                        \
-    } while (0)
+static int oz_grid(int ntiles) {
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
+    }
+    return ntiles < sms ? ntiles : sms;       // one persistent CTA per SM (215 KB of shared memory, all of TMEM)
+}
+
+// launches k_oz<EPI, 7 or 8, F> on one persistent CTA per SM (one smem-attribute call per instantiation)
+template <int EPI, class F>
+static int oz_launch(const F& f, int ntiles, cudaStream_t st) {
+    static bool done7 = false, done8 = false;
+    if (ntiles <= 0) return 0;
+    if (g_oz_groups == 7) {
+        if (oz_smem_attr(k_oz<EPI, 7, F>, done7)) return 1;
+        k_oz<EPI, 7, F><<<oz_grid(ntiles), OZ_THREADS, OZ_SMEM_BYTES, st>>>(f, ntiles);
+    } else {
+        if (oz_smem_attr(k_oz<EPI, 8, F>, done8)) return 1;
+        k_oz<EPI, 8, F><<<oz_grid(ntiles), OZ_THREADS, OZ_SMEM_BYTES, st>>>(f, ntiles);
+    }
+    return 0;
+}
 
 size_t oz_panel_bytes(int Np) { return (size_t)(Np / NB) * 4 * OZ_CHUNK; }      // [T][4 chunks]: S digits of one block column
 size_t oz_ddig_bytes(int Np) { return (size_t)(Np / NB) * 2 * 4 * OZ_CHUNK; }   // [T][2][4 chunks]: D_J and D_J^T digits
@@ -656,8 +707,8 @@ size_t oz_ddig_bytes(int Np) { return (size_t)(Np / NB) * 2 * 4 * OZ_CHUNK; }   
 int launch_oz_syrk(double* mat, int Np, int T, int J, int P, const uint8_t* slices, const double* rowsig,
                    const double* rowinv, uint8_t* sdig, const unsigned char* active, cudaStream_t st) {
     if (J == 0) return 0;
-    const dim3 grid(2 * (T - J), P);
-    OZ_LAUNCH(k_oz_syrk, grid, st, mat, Np, J, slices, oz_slice_bytes(Np), rowsig, rowinv, sdig, oz_panel_bytes(Np), active);
+    const OzSyrkTiles f{mat, Np, J, 2 * (T - J), slices, oz_slice_bytes(Np), rowsig, rowinv, sdig, oz_panel_bytes(Np), active};
+    if (oz_launch<OZ_SUB>(f, f.nx * P, st)) return 1;
     return check_launch("k_oz_syrk");
 }
 
@@ -671,17 +722,17 @@ int launch_oz_trsm(double* mat, int Np, int T, int J, int P, const uint8_t* sdig
                    const double* rowsig, const double* rowinv, uint8_t* slices, const unsigned char* active,
                    cudaStream_t st) {
     if (J >= T - 1) return 0;
-    const dim3 grid(2 * (T - 1 - J), P);
-    OZ_LAUNCH(k_oz_trsm, grid, st, mat, Np, T, J, sdig, oz_panel_bytes(Np), ddig, dsc, rowsig, rowinv, slices,
-              oz_slice_bytes(Np), active);
+    const OzTrsmTiles f{mat, Np, T, J, 2 * (T - 1 - J), sdig, oz_panel_bytes(Np), ddig, dsc, rowsig, rowinv, slices,
+                        oz_slice_bytes(Np), active};
+    if (oz_launch<OZ_STORE>(f, f.nx * P, st)) return 1;
     return check_launch("k_oz_trsm");
 }
 
 int launch_oz_invp(double* mt, int Np, int T, int J, int P, const uint8_t* ddig, const double* dsc, const uint8_t* slices,
                    const double* rowsig, const unsigned char* active, cudaStream_t st) {
     if (J >= T - 1) return 0;
-    const dim3 grid(2 * (T - 1 - J), P);
-    OZ_LAUNCH(k_oz_invp, grid, st, mt, Np, T, J, ddig, dsc, slices, oz_slice_bytes(Np), rowsig, active);
+    const OzInvpTiles f{mt, Np, T, J, 2 * (T - 1 - J), ddig, dsc, slices, oz_slice_bytes(Np), rowsig, active};
+    if (oz_launch<OZ_STORE>(f, f.nx * P, st)) return 1;
     return check_launch("k_oz_invp");
 }
 
@@ -713,9 +764,9 @@ int launch_oz_mt(const double* mt, int Np, int T, int J, int P, const double* ga
 int launch_oz_invu(double* mat, int Np, int T, int J, int P, uint8_t* slices, const uint8_t* mtslices,
                    const double* mtsig, const double* gam, int emit, const unsigned char* active, cudaStream_t st) {
     if (J >= T - 1) return 0;
-    const dim3 grid(2 * (T - 1 - J), P);
-    OZ_LAUNCH(k_oz_invu, grid, st, mat, Np, T, J, slices, oz_slice_bytes(Np), mtslices, oz_mt_bytes(Np), mtsig, gam, emit,
-              active);
+    const OzInvuTiles f{mat, Np, T, J, 2 * (T - 1 - J), slices, oz_slice_bytes(Np), mtslices, oz_mt_bytes(Np), mtsig, gam,
+                        emit, active};
+    if (oz_launch<OZ_STORE_NEG>(f, f.nx * P, st)) return 1;
     return check_launch("k_oz_invu");
 }
 
@@ -727,8 +778,8 @@ int launch_oz_slice_generic(const double* src, int ld, int rows, int cols, const
 
 int launch_oz_gemm_tn(const uint8_t* A, const uint8_t* B, int M, int N, int K, const double* sa, const double* sb,
                       double* C, int ldc, int* dbg, cudaStream_t st) {
-    const dim3 grid(N / OZ_TILE_N, M / NB);
-    OZ_LAUNCH(k_oz_gemm_tn, grid, st, A, B, K / 32, sa, sb, C, ldc, dbg);
+    const OzGemmTiles f{A, B, K / 32, N / OZ_TILE_N, sa, sb, C, ldc, dbg, g_oz_groups};
+    if (oz_launch<OZ_STORE>(f, f.nx * (M / NB), st)) return 1;
     return check_launch("k_oz_gemm_tn");
 }
 
