@@ -9,6 +9,10 @@ COLS = [
     ("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "dram%"),
     ("sm__inst_executed_pipe_tensor_op_dmma.avg.pct_of_peak_sustained_active", "dmma%act"),
     ("sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed", "tensor%el"),
+    ("TPC.TriageCompute.sm__pipe_tensor_cycles_active_realtime.avg.pct_of_peak_sustained_elapsed", "tc%el(realtime)"),
+    ("sm__mem_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed", "tc_mem%el"),
+    ("l1tex__m_xbar2l1tex_read_bytes.sum", "l2->sm"),
+    ("sm__cycles_elapsed.max", "cycles"),
     ("sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active", "fp64%act"),
     ("sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active", "fp64inst%"),
     ("sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm%"),

@@ -10,6 +10,9 @@ reps = int(sys.argv[2]) if len(sys.argv) > 2 else 2
 x, y, e = bench.make_problem(0)
 pos, lo, hi = bench.make_particles(x, P, 0)
 s, ex = pso.sigma_grid()
+if os.environ.get("GPK_GROUPS"):
+    from gaussian_process_b200 import _lib
+    _lib.check(_lib.load().gpk_set_groups(int(os.environ["GPK_GROUPS"])), "gpk_set_groups")
 ctx = engine.LossContext(x, y, e, s)
 dpos = engine.to_dev(pos); dact = torch.ones(P, dtype=torch.uint8, device="cuda")
 for _ in range(reps):
