@@ -90,7 +90,7 @@ BlockedLayout blocked_layout(int P, int N, int d, int emulated) {
     L.cn = take((size_t)P * Np * 8);
     L.z = take((size_t)P * Np * 8);
     L.alpha = take((size_t)P * Np * 8);
-    L.oz_slices = L.oz_mt = L.oz_rows = L.oz_mtsc = L.oz_sdig = L.oz_ddig = L.oz_dsc = 0;
+    L.oz_slices = L.oz_mt = L.oz_rows = L.oz_mtsc = L.oz_sdig = L.oz_ddig = L.oz_dsc = L.oz_cnt = 0;
     if (emulated) {
         L.oz_slices = take((size_t)P * oz_slice_bytes(L.Np));
         L.oz_mt = take((size_t)P * oz_mt_bytes(L.Np));
@@ -99,6 +99,7 @@ BlockedLayout blocked_layout(int P, int N, int d, int emulated) {
         L.oz_sdig = take((size_t)P * oz_panel_bytes(L.Np));
         L.oz_ddig = take((size_t)P * oz_ddig_bytes(L.Np));
         L.oz_dsc = take((size_t)P * T * 2 * NB * 8);
+        L.oz_cnt = take((4 * T + 8) * sizeof(int));
     }
     L.total = off;
     return L;
@@ -111,6 +112,9 @@ struct OzBuffers {
     uint8_t* sdig = nullptr;
     uint8_t* ddig = nullptr;
     double* dsc = nullptr;
+    int* cnt = nullptr;          // tile counters; next() hands out one per digit-GEMM launch
+    mutable int cnt_used = 0;
+    int* next() const { return cnt + cnt_used++; }
     double *rowsig = nullptr, *rowinv = nullptr, *gam = nullptr, *gaminv = nullptr, *mtsig = nullptr, *mtinv = nullptr;
 };
 
@@ -126,6 +130,7 @@ static OzBuffers oz_buffers(char* ws, const BlockedLayout& L) {
     o.sdig = (uint8_t*)(ws + L.oz_sdig);
     o.ddig = (uint8_t*)(ws + L.oz_ddig);
     o.dsc = (double*)(ws + L.oz_dsc);
+    o.cnt = (int*)(ws + L.oz_cnt);
     return o;
 }
 
@@ -142,7 +147,7 @@ static int factor_phase(double* mat, int Np, int T, int P, double* dinv, double*
         // emulated FP64: every contraction on the digit GEMM.  The SYRK epilogue leaves the digits of S_IJ, the
         // TRSM reads them with the digits of D_J and leaves L_IJ and its digits for the later SYRKs.
         if (J > 0) {
-            if (launch_oz_syrk(mat, Np, T, J, P, oz.slices, oz.rowsig, oz.rowinv, oz.sdig, active, st)) return 1;
+            if (launch_oz_syrk(mat, Np, T, J, P, oz.slices, oz.rowsig, oz.rowinv, oz.sdig, oz.next(), active, st)) return 1;
         }
         if (launch_diag_block(mat, Np, J, P, dinv, dinvT, T, info, active, mode, st)) return 1;
         if (launch_oz_slice_d(dinv, dinvT, T, J, P, oz.rowsig, oz.ddig, oz.dsc, active, st)) return 1;
@@ -150,7 +155,7 @@ static int factor_phase(double* mat, int Np, int T, int P, double* dinv, double*
             if (launch_trsm_panel(mat, Np, T, J, P, dinv, active, st)) return 1;
             if (launch_oz_slice_l(mat, Np, T, J, P, oz.rowinv, oz.slices, active, st)) return 1;
         } else {
-            if (launch_oz_trsm(mat, Np, T, J, P, oz.sdig, oz.ddig, oz.dsc, oz.rowsig, oz.rowinv, oz.slices, active, st)) return 1;
+            if (launch_oz_trsm(mat, Np, T, J, P, oz.sdig, oz.ddig, oz.dsc, oz.rowsig, oz.rowinv, oz.slices, oz.next(), active, st)) return 1;
         }
     }
     return 0;
@@ -162,9 +167,9 @@ static int inverse_phase(double* mat, int Np, int T, int P, const double* dinvT,
     if (oz.slices && launch_oz_slice_w(mat, Np, T, 0, 1, P, oz.gam, oz.slices, active, st)) return 1;
     for (int J = T - 2; J >= 0; --J) {
         if (oz.slices) {
-            if (launch_oz_invp(mt, Np, T, J, P, oz.ddig, oz.dsc, oz.slices, oz.rowsig, active, st)) return 1;
+            if (launch_oz_invp(mt, Np, T, J, P, oz.ddig, oz.dsc, oz.slices, oz.rowsig, oz.next(), active, st)) return 1;
             if (launch_oz_mt(mt, Np, T, J, P, oz.gaminv, oz.mtsig, oz.mtinv, oz.mtslices, active, st)) return 1;
-            if (launch_oz_invu(mat, Np, T, J, P, oz.slices, oz.mtslices, oz.mtsig, oz.gam, 1, active, st)) return 1;
+            if (launch_oz_invu(mat, Np, T, J, P, oz.slices, oz.mtslices, oz.mtsig, oz.gam, 1, oz.next(), active, st)) return 1;
         } else {
             if (launch_inv_panel(mat, Np, T, J, P, dinvT, mt, active, st)) return 1;
             if (launch_inv_update(mat, Np, T, J, P, mt, active, st)) return 1;
@@ -285,7 +290,10 @@ int gpk_loss_batched(const double* X, const double* y, const double* e, const do
             const BlockedLayout L = blocked_layout(Pc, N, d, emu);
             char* ws = (char*)workspace + (size_t)g * gbytes;
             const OzBuffers oz = oz_buffers(ws, L);
-            if (emu && launch_oz_prep(e, N, L.Np, oz.rowsig, oz.rowinv, oz.gam, oz.gaminv, gs)) return 1;
+            if (emu) {
+                if (cudaMemsetAsync(oz.cnt, 0, (4 * L.T + 8) * sizeof(int), gs) != cudaSuccess) { set_error("memset counters failed"); return 1; }
+                if (launch_oz_prep(e, N, L.Np, oz.rowsig, oz.rowinv, oz.gam, oz.gaminv, gs)) return 1;
+            }
             double* mat = (double*)(ws + L.mat);
             double* dinv = (double*)(ws + L.dinv);
             double* dinvT = (double*)(ws + L.dinvT);
@@ -321,7 +329,8 @@ size_t gpk_fit_workspace_bytes(int N, int d) {
     size_t b = 2 * align256(T * NB * NB * 8) + align256(NB * Np * 8) + 2 * align256(Np * 8);
     if (g_precision)
         b += align256(oz_slice_bytes((int)Np)) + align256(oz_mt_bytes((int)Np)) + align256(4 * Np * 8) + align256(2 * NB * 8) +
-             align256(oz_panel_bytes((int)Np)) + align256(oz_ddig_bytes((int)Np)) + align256(T * 2 * NB * 8);
+             align256(oz_panel_bytes((int)Np)) + align256(oz_ddig_bytes((int)Np)) + align256(T * 2 * NB * 8) +
+             align256((4 * T + 8) * sizeof(int));
     return b;
 }
 
@@ -349,7 +358,9 @@ int gpk_fit(const double* X, const double* y, const double* e, const double* ls,
         oz.mtsig = (double*)(ws + off); oz.mtinv = oz.mtsig + NB; off += align256((size_t)2 * NB * 8);
         oz.sdig = (uint8_t*)(ws + off); off += align256(oz_panel_bytes(Np));
         oz.ddig = (uint8_t*)(ws + off); off += align256(oz_ddig_bytes(Np));
-        oz.dsc = (double*)(ws + off);
+        oz.dsc = (double*)(ws + off); off += align256((size_t)T * 2 * NB * 8);
+        oz.cnt = (int*)(ws + off);
+        if (cudaMemsetAsync(oz.cnt, 0, (4 * T + 8) * sizeof(int), st) != cudaSuccess) { set_error("memset counters failed"); return 1; }
         if (launch_oz_prep(e, N, Np, oz.rowsig, oz.rowinv, oz.gam, oz.gaminv, st)) return 1;
     }
     if (cudaMemsetAsync(info, 0, sizeof(int), st) != cudaSuccess) { set_error("memset info failed"); return 1; }

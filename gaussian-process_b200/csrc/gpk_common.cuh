@@ -39,6 +39,7 @@ struct BlockedLayout {
     size_t oz_sdig;    // [P] digits of the Schur-complement block column (TRSM operand), oz_panel_bytes(Np) each
     size_t oz_ddig;    // [P] digits of D_J and D_J^T for every J, oz_ddig_bytes(Np) each
     size_t oz_dsc;     // [P][T][2][NB] their measured row scales
+    size_t oz_cnt;     // [4 T + 8] int tile counters, one per digit-GEMM launch (zeroed once per evaluation)
     size_t total;
 };
 BlockedLayout blocked_layout(int P, int N, int d, int emulated);
@@ -79,14 +80,14 @@ int launch_oz_prep(const double* e, int N, int Np, double* rowsig, double* rowin
 size_t oz_panel_bytes(int Np);
 size_t oz_ddig_bytes(int Np);
 int launch_oz_syrk(double* mat, int Np, int T, int J, int P, const uint8_t* slices, const double* rowsig,
-                   const double* rowinv, uint8_t* sdig, const unsigned char* active, cudaStream_t st);
+                   const double* rowinv, uint8_t* sdig, int* counter, const unsigned char* active, cudaStream_t st);
 int launch_oz_slice_d(const double* dinv, const double* dinvT, int T, int J, int P, const double* rowsig, uint8_t* ddig,
                       double* dsc, const unsigned char* active, cudaStream_t st);
 int launch_oz_trsm(double* mat, int Np, int T, int J, int P, const uint8_t* sdig, const uint8_t* ddig, const double* dsc,
-                   const double* rowsig, const double* rowinv, uint8_t* slices, const unsigned char* active,
+                   const double* rowsig, const double* rowinv, uint8_t* slices, int* counter, const unsigned char* active,
                    cudaStream_t st);
 int launch_oz_invp(double* mt, int Np, int T, int J, int P, const uint8_t* ddig, const double* dsc, const uint8_t* slices,
-                   const double* rowsig, const unsigned char* active, cudaStream_t st);
+                   const double* rowsig, int* counter, const unsigned char* active, cudaStream_t st);
 int launch_oz_slice_l(const double* mat, int Np, int T, int J, int P, const double* rowinv, uint8_t* slices,
                       const unsigned char* active, cudaStream_t st);
 int launch_oz_slice_w(const double* mat, int Np, int T, int J, int diag, int P, const double* gam, uint8_t* slices,
@@ -94,7 +95,8 @@ int launch_oz_slice_w(const double* mat, int Np, int T, int J, int diag, int P, 
 int launch_oz_mt(const double* mt, int Np, int T, int J, int P, const double* gaminv, double* mtsig, double* mtinv,
                  uint8_t* mtslices, const unsigned char* active, cudaStream_t st);
 int launch_oz_invu(double* mat, int Np, int T, int J, int P, uint8_t* slices, const uint8_t* mtslices,
-                   const double* mtsig, const double* gam, int emit, const unsigned char* active, cudaStream_t st);
+                   const double* mtsig, const double* gam, int emit, int* counter, const unsigned char* active,
+                   cudaStream_t st);
 int launch_oz_slice_generic(const double* src, int ld, int rows, int cols, const double* rowinv, uint8_t* dst,
                             cudaStream_t st);
 int launch_oz_gemm_tn(const uint8_t* A, const uint8_t* B, int M, int N, int K, const double* sa, const double* sb,

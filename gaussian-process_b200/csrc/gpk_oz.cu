@@ -40,7 +40,7 @@ constexpr int OZ_STAGES = 5;
 constexpr int OZ_THREADS = 320;                 // warp 0 producer, warp 1 MMA issuer, warps 2..9 epilogue
 constexpr int OZ_TMEM_COLS = 512;
 constexpr int OZ_TILE_N = 64;
-constexpr size_t OZ_SMEM_BYTES = (size_t)OZ_STAGES * OZ_STAGE + 128;
+constexpr size_t OZ_SMEM_BYTES = (size_t)OZ_STAGES * OZ_STAGE + 256;
 constexpr long long OZ_BIAS = 0x0000808080808080LL;
 // kind::i8, D = S32, A = B = signed 8 bit, both K-major, M = 128; the N field (bits 17..22, N >> 3) is added per MMA
 constexpr uint32_t OZ_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((128u >> 4) << 24);
@@ -55,6 +55,9 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 }
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
     uint32_t ok;
@@ -154,11 +157,15 @@ __device__ __forceinline__ void oz_issue_chunk(uint32_t tmem, uint64_t da, uint6
     }
 }
 
-// Persistent tile loop: CTA c computes the 128 x 64 tiles c, c + gridDim.x, ... ; f.make(tile, t) describes a tile
-// (false = nothing to do).  The operand ring runs across tile boundaries, so the next tile's first stages load while
-// the epilogue drains the accumulators (all 512 TMEM columns hold one tile: MMA and epilogue of one CTA alternate).
+// Persistent tile loop with a dynamic scheduler: the producer thread draws 128 x 64 tiles from a global counter and
+// hands the ids to the MMA thread and the epilogue warps through a small shared-memory queue, so CTAs that start late
+// (other streams' kernels still on their SM) or draw long tiles simply take fewer.  f.make(tile, t) describes a tile
+// (false = nothing to do).  The operand ring runs across tile boundaries: the next tile's first stages load while the
+// epilogue drains the accumulators (all 512 TMEM columns hold one tile: MMA and epilogue of one CTA alternate).
+constexpr int OZ_QDEPTH = 4;
+
 template <int EPI, int NG, class F>
-__device__ __forceinline__ void oz_run(const F& f, int ntiles, uint8_t* smem) {
+__device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uint8_t* smem) {
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
     uint8_t* ctrl = smem + (size_t)OZ_STAGES * OZ_STAGE;
@@ -166,7 +173,10 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, uint8_t* smem) {
     const uint32_t empty0 = full0 + 8 * OZ_STAGES;         // OZ_STAGES x 8 B
     const uint32_t accbar = empty0 + 8 * OZ_STAGES;        // 8 B: accumulators complete (MMA -> epilogue)
     const uint32_t freebar = accbar + 8;                   // 8 B: accumulators drained (epilogue -> MMA)
-    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(ctrl + 8 * (2 * OZ_STAGES + 2));
+    const uint32_t qfull0 = freebar + 8;                   // OZ_QDEPTH x 8 B: tile id written (producer -> consumers)
+    const uint32_t qempty0 = qfull0 + 8 * OZ_QDEPTH;       // OZ_QDEPTH x 8 B: tile id read by every consumer
+    volatile int* qtile = reinterpret_cast<volatile int*>(ctrl + 8 * (2 * OZ_STAGES + 2 + 2 * OZ_QDEPTH));
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(ctrl + 8 * (2 * OZ_STAGES + 2 + 2 * OZ_QDEPTH) + 4 * OZ_QDEPTH);
     const uint32_t stage0 = smem_u32(smem);
 
     if (tid == 0) {
@@ -176,6 +186,10 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, uint8_t* smem) {
         }
         mbar_init(accbar, 1);
         mbar_init(freebar, OZ_THREADS - 64);
+        for (int q = 0; q < OZ_QDEPTH; ++q) {
+            mbar_init(qfull0 + 8 * q, 1);
+            mbar_init(qempty0 + 8 * q, 1 + OZ_THREADS - 64);      // the MMA thread and every epilogue thread
+        }
         asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
     }
     if (warp == 2) {
@@ -194,7 +208,14 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, uint8_t* smem) {
         if (lane == 0) {
             OzTile t;
             uint32_t kg = 0;                     // chunk counter across tiles = position in the ring
-            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            for (uint32_t n = 0;; ++n) {
+                const uint32_t qs = n % OZ_QDEPTH;
+                mbar_wait(qempty0 + 8 * qs, ((n / OZ_QDEPTH) & 1u) ^ 1u);
+                int tile = atomicAdd(counter, 1);
+                if (tile >= ntiles) tile = -1;
+                qtile[qs] = tile;
+                mbar_arrive(qfull0 + 8 * qs);
+                if (tile < 0) break;
                 if (!f.make(tile, t)) continue;
             for (int k = 0; k < t.nk; ++k, ++kg) {
                 const uint32_t s = kg % OZ_STAGES;
@@ -214,7 +235,12 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, uint8_t* smem) {
         if (lane == 0) {
             OzTile t;
             uint32_t kg = 0, it = 0;
-            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            for (uint32_t n = 0;; ++n) {
+                const uint32_t qs = n % OZ_QDEPTH;
+                mbar_wait(qfull0 + 8 * qs, (n / OZ_QDEPTH) & 1u);
+                const int tile = qtile[qs];
+                mbar_arrive(qempty0 + 8 * qs);
+                if (tile < 0) break;
                 if (!f.make(tile, t)) continue;
                 mbar_wait(freebar, (it & 1u) ^ 1u);      // the epilogue has drained the previous tile
                 tc_fence_after();
@@ -239,7 +265,12 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, uint8_t* smem) {
         const int row = q * 32 + lane;
         OzTile t;
         uint32_t it = 0;
-        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        for (uint32_t n = 0;; ++n) {
+        const uint32_t qs = n % OZ_QDEPTH;
+        mbar_wait(qfull0 + 8 * qs, (n / OZ_QDEPTH) & 1u);
+        const int tile = qtile[qs];
+        mbar_arrive(qempty0 + 8 * qs);
+        if (tile < 0) break;
         if (!f.make(tile, t)) continue;
         const double rs = (t.sa ? t.sa[row] : 1.0) * t.sa_const * 0x1p-14;
         double* crow = t.c + (size_t)row * t.ldc + ch * 32;
@@ -320,7 +351,7 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, uint8_t* smem) {
             }
         }
         tc_fence_before();
-        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(freebar) : "memory");   // TMEM may be overwritten
+        mbar_arrive(freebar);                    // TMEM may be overwritten
         }
     }
     tc_fence_before();
@@ -333,9 +364,9 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, uint8_t* smem) {
 
 // ---- tile descriptions (functors) and the one persistent kernel ---------------------------------------------------
 template <int EPI, int NG, class F>
-__global__ void __launch_bounds__(OZ_THREADS, 1) k_oz(const F f, int ntiles) {
+__global__ void __launch_bounds__(OZ_THREADS, 1) k_oz(const F f, int ntiles, int* counter) {
     extern __shared__ __align__(128) uint8_t oz_smem[];
-    oz_run<EPI, NG, F>(f, ntiles, oz_smem);
+    oz_run<EPI, NG, F>(f, ntiles, counter, oz_smem);
 }
 
 __device__ __forceinline__ void oz_no_digits(OzTile& t) {
@@ -687,15 +718,15 @@ static int oz_grid(int ntiles) {
 
 // launches k_oz<EPI, 7 or 8, F> on one persistent CTA per SM (one smem-attribute call per instantiation)
 template <int EPI, class F>
-static int oz_launch(const F& f, int ntiles, cudaStream_t st) {
+static int oz_launch(const F& f, int ntiles, int* counter, cudaStream_t st) {
     static bool done7 = false, done8 = false;
     if (ntiles <= 0) return 0;
     if (g_oz_groups == 7) {
         if (oz_smem_attr(k_oz<EPI, 7, F>, done7)) return 1;
-        k_oz<EPI, 7, F><<<oz_grid(ntiles), OZ_THREADS, OZ_SMEM_BYTES, st>>>(f, ntiles);
+        k_oz<EPI, 7, F><<<oz_grid(ntiles), OZ_THREADS, OZ_SMEM_BYTES, st>>>(f, ntiles, counter);
     } else {
         if (oz_smem_attr(k_oz<EPI, 8, F>, done8)) return 1;
-        k_oz<EPI, 8, F><<<oz_grid(ntiles), OZ_THREADS, OZ_SMEM_BYTES, st>>>(f, ntiles);
+        k_oz<EPI, 8, F><<<oz_grid(ntiles), OZ_THREADS, OZ_SMEM_BYTES, st>>>(f, ntiles, counter);
     }
     return 0;
 }
@@ -705,10 +736,10 @@ size_t oz_ddig_bytes(int Np) { return (size_t)(Np / NB) * 2 * 4 * OZ_CHUNK; }   
 
 // sdig != nullptr: the epilogue also leaves the digits of S_IJ (I > J) for launch_oz_trsm
 int launch_oz_syrk(double* mat, int Np, int T, int J, int P, const uint8_t* slices, const double* rowsig,
-                   const double* rowinv, uint8_t* sdig, const unsigned char* active, cudaStream_t st) {
+                   const double* rowinv, uint8_t* sdig, int* counter, const unsigned char* active, cudaStream_t st) {
     if (J == 0) return 0;
     const OzSyrkTiles f{mat, Np, J, 2 * (T - J), slices, oz_slice_bytes(Np), rowsig, rowinv, sdig, oz_panel_bytes(Np), active};
-    if (oz_launch<OZ_SUB>(f, f.nx * P, st)) return 1;
+    if (oz_launch<OZ_SUB>(f, f.nx * P, counter, st)) return 1;
     return check_launch("k_oz_syrk");
 }
 
@@ -719,20 +750,20 @@ int launch_oz_slice_d(const double* dinv, const double* dinvT, int T, int J, int
 }
 
 int launch_oz_trsm(double* mat, int Np, int T, int J, int P, const uint8_t* sdig, const uint8_t* ddig, const double* dsc,
-                   const double* rowsig, const double* rowinv, uint8_t* slices, const unsigned char* active,
+                   const double* rowsig, const double* rowinv, uint8_t* slices, int* counter, const unsigned char* active,
                    cudaStream_t st) {
     if (J >= T - 1) return 0;
     const OzTrsmTiles f{mat, Np, T, J, 2 * (T - 1 - J), sdig, oz_panel_bytes(Np), ddig, dsc, rowsig, rowinv, slices,
                         oz_slice_bytes(Np), active};
-    if (oz_launch<OZ_STORE>(f, f.nx * P, st)) return 1;
+    if (oz_launch<OZ_STORE>(f, f.nx * P, counter, st)) return 1;
     return check_launch("k_oz_trsm");
 }
 
 int launch_oz_invp(double* mt, int Np, int T, int J, int P, const uint8_t* ddig, const double* dsc, const uint8_t* slices,
-                   const double* rowsig, const unsigned char* active, cudaStream_t st) {
+                   const double* rowsig, int* counter, const unsigned char* active, cudaStream_t st) {
     if (J >= T - 1) return 0;
     const OzInvpTiles f{mt, Np, T, J, 2 * (T - 1 - J), ddig, dsc, slices, oz_slice_bytes(Np), rowsig, active};
-    if (oz_launch<OZ_STORE>(f, f.nx * P, st)) return 1;
+    if (oz_launch<OZ_STORE>(f, f.nx * P, counter, st)) return 1;
     return check_launch("k_oz_invp");
 }
 
@@ -762,11 +793,12 @@ int launch_oz_mt(const double* mt, int Np, int T, int J, int P, const double* ga
 
 // emit != 0: the epilogue also writes the digits of W_IJ gamma / 2 (replaces launch_oz_slice_w for column J)
 int launch_oz_invu(double* mat, int Np, int T, int J, int P, uint8_t* slices, const uint8_t* mtslices,
-                   const double* mtsig, const double* gam, int emit, const unsigned char* active, cudaStream_t st) {
+                   const double* mtsig, const double* gam, int emit, int* counter, const unsigned char* active,
+                   cudaStream_t st) {
     if (J >= T - 1) return 0;
     const OzInvuTiles f{mat, Np, T, J, 2 * (T - 1 - J), slices, oz_slice_bytes(Np), mtslices, oz_mt_bytes(Np), mtsig, gam,
                         emit, active};
-    if (oz_launch<OZ_STORE_NEG>(f, f.nx * P, st)) return 1;
+    if (oz_launch<OZ_STORE_NEG>(f, f.nx * P, counter, st)) return 1;
     return check_launch("k_oz_invu");
 }
 
@@ -778,8 +810,11 @@ int launch_oz_slice_generic(const double* src, int ld, int rows, int cols, const
 
 int launch_oz_gemm_tn(const uint8_t* A, const uint8_t* B, int M, int N, int K, const double* sa, const double* sb,
                       double* C, int ldc, int* dbg, cudaStream_t st) {
+    static int* counter = nullptr;           // the library primitive owns one tile counter
+    if (!counter && cudaMalloc(&counter, sizeof(int)) != cudaSuccess) { set_error("oz counter alloc failed"); return 1; }
+    if (cudaMemsetAsync(counter, 0, sizeof(int), st) != cudaSuccess) { set_error("oz counter memset failed"); return 1; }
     const OzGemmTiles f{A, B, K / 32, N / OZ_TILE_N, sa, sb, C, ldc, dbg, g_oz_groups};
-    if (oz_launch<OZ_STORE>(f, f.nx * (M / NB), st)) return 1;
+    if (oz_launch<OZ_STORE>(f, f.nx * (M / NB), counter, st)) return 1;
     return check_launch("k_oz_gemm_tn");
 }
 
