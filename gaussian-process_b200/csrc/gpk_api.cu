@@ -400,6 +400,39 @@ int gpk_predict(const double* W, const double* alpha, const double* xs, const do
     return 0;
 }
 
+size_t gpk_predict_state_bytes(int N) { return oz_pred_state_bytes(round_up(N, NB)); }
+
+int gpk_predict_prepare(const double* W, const double* e, int N, void* state, size_t state_bytes, void* stream) {
+    if (N < 1) { set_error("gpk_predict_prepare: N=%d", N); return 2; }
+    if (state_bytes < gpk_predict_state_bytes(N)) { set_error("gpk_predict_prepare: state buffer too small"); return 3; }
+    set_stream((cudaStream_t)stream);
+    return launch_oz_pred_prepare(W, e, N, round_up(N, NB), (uint8_t*)state, (cudaStream_t)stream);
+}
+
+size_t gpk_predict_emu_workspace_bytes(int N, int chunk) {
+    return oz_pred_workspace_bytes(round_up(N, NB), round_up(chunk, NB));
+}
+
+int gpk_predict_emu(const void* state, const double* alpha, const double* xs, const double* sq, const double* ls, int N,
+                    int d, const double* Xfit, long long M, double* mu_out, double* sd_out, int chunk, void* workspace,
+                    size_t workspace_bytes, void* stream) {
+    if (bad_dims("gpk_predict_emu", N, d, 0) || chunk < 1) return 2;
+    if (M <= 0) return 0;
+    if (workspace_bytes < gpk_predict_emu_workspace_bytes(N, chunk)) { set_error("gpk_predict_emu: workspace too small"); return 3; }
+    cudaStream_t st = (cudaStream_t)stream;
+    set_stream(st);
+    const int Np = round_up(N, NB), T = Np / NB;
+    for (long long m0 = 0; m0 < M; m0 += chunk) {
+        const int B = (int)((M - m0 < chunk) ? (M - m0) : chunk);
+        const int Bp = round_up(B, NB);
+        double* partial = nullptr;
+        if (launch_oz_predict_chunk((const uint8_t*)state, xs, sq, ls, alpha, N, Np, d, Xfit, M, m0, B, Bp,
+                                    (uint8_t*)workspace, mu_out, &partial, st)) return 1;
+        if (launch_predict_finalize(partial, 4 * T, Bp, B, sd_out + m0, st)) return 1;
+    }
+    return 0;
+}
+
 int gpk_prob_surface(const double* table, long long R, int ncols, int npoints, double* y_out, double* p_out,
                      int* valid_out, void* stream) {
     if (npoints < 1) { set_error("gpk_prob_surface: npoints=%d", npoints); return 2; }

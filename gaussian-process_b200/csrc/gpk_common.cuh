@@ -101,6 +101,12 @@ int launch_oz_slice_generic(const double* src, int ld, int rows, int cols, const
                             cudaStream_t st);
 int launch_oz_gemm_tn(const uint8_t* A, const uint8_t* B, int M, int N, int K, const double* sa, const double* sb,
                       double* C, int ldc, int* dbg, cudaStream_t st);
+size_t oz_pred_state_bytes(int Np);
+size_t oz_pred_workspace_bytes(int Np, int Bp);
+int launch_oz_pred_prepare(const double* W, const double* e, int N, int Np, uint8_t* state, cudaStream_t st);
+int launch_oz_predict_chunk(const uint8_t* state, const double* xs, const double* sq, const double* ls, const double* alpha,
+                            int N, int Np, int d, const double* Xfit, long long M, long long m0, int B, int Bp,
+                            uint8_t* workspace, double* mu_out, double** partial_out, cudaStream_t st);
 void oz_set_groups(int ng);
 int oz_get_groups();
 

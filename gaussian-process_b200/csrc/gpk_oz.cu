@@ -117,7 +117,7 @@ __device__ __forceinline__ uint32_t pack_digit(const uint32_t* w, int b) {
     return __byte_perm(t0, t1, 0x5410);
 }
 
-enum OzEpi { OZ_SUB = 0, OZ_STORE = 1, OZ_STORE_NEG = 2 };
+enum OzEpi { OZ_SUB = 0, OZ_STORE = 1, OZ_STORE_NEG = 2, OZ_SUMSQ = 3 };
 
 struct OzTile {
     const uint8_t* a;     // first chunk of the A row block (128 rows), chunks are consecutive in K
@@ -134,6 +134,9 @@ struct OzTile {
     const double* dig_rs;  // 128 row multipliers or nullptr
     double dig_rconst;     // u = value * dig_rs[row] * dig_rconst * dig_cs[col], |u| <= 0.98
     const double* dig_cs;  // 64 column multipliers or nullptr
+    // OZ_SUMSQ only: column sums of squares over each 32-row quadrant, red[q * red_ld + col] (no FP64 tile is stored)
+    double* red;
+    size_t red_ld;
 };
 
 // The MMAs of one K chunk.  NG = number of digit groups kept (g = s + t < NG): 7 -> 28 digit products, 8 -> 34.
@@ -287,6 +290,7 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
         tc_fence_after();
         ++it;
         const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + ch * 32;
+        double sqv[EPI == OZ_SUMSQ ? 32 : 1];
 #pragma unroll
         for (int cc = 0; cc < 32; cc += 8) {
             uint32_t a[NG][8];
@@ -309,6 +313,11 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
                 double x = fma(ll2d_exact(mid), 0x1p-40, ll2d_exact(lo) * 0x1p-56);
                 x = fma(ll2d_exact(hi), 0x1p-16, x);
                 v[j] = x * (rs * (sbp ? sbp[cc + j] : 1.0));
+            }
+            if (EPI == OZ_SUMSQ) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) sqv[cc + j] = v[j] * v[j];
+                continue;
             }
             double2* cp = reinterpret_cast<double2*>(crow + cc);
 #pragma unroll
@@ -352,6 +361,20 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
         }
         tc_fence_before();
         mbar_arrive(freebar);                    // TMEM may be overwritten
+        if (EPI == OZ_SUMSQ) {
+            // butterfly: 32 columns x 32 rows (lanes) -> lane l holds the sum over the quadrant's rows of column l
+#pragma unroll
+            for (int step = 16; step >= 1; step >>= 1) {
+                const bool up = (lane & step) != 0;
+#pragma unroll
+                for (int i = 0; i < step; ++i) {
+                    const double send = up ? sqv[i] : sqv[i + step];
+                    const double keep = up ? sqv[i + step] : sqv[i];
+                    sqv[i] = keep + __shfl_xor_sync(0xffffffffu, send, step);
+                }
+            }
+            t.red[(size_t)q * t.red_ld + ch * 32 + lane] = sqv[0];
+        }
         }
     }
     tc_fence_before();
@@ -372,6 +395,7 @@ __global__ void __launch_bounds__(OZ_THREADS, 1) k_oz(const F f, int ntiles, int
 __device__ __forceinline__ void oz_no_digits(OzTile& t) {
     t.dbg = nullptr;
     t.dig = nullptr; t.dig_rs = nullptr; t.dig_rconst = 1.0; t.dig_cs = nullptr;
+    t.red = nullptr; t.red_ld = 0;
 }
 
 // Left-looking Cholesky update of block column J: A_IJ -= sum_{K<J} L_IK L_JK^T from the digits of L.
@@ -682,6 +706,140 @@ struct OzInvpTiles {
     }
 };
 
+// ---- prediction on the digit GEMM (GP_func.py:38-39 for a chunk of grid points) ---------------------------------------
+// sd^2 = 1 - |W k_*|^2: tile = I * nx + nb computes (W gamma / 2)[block I] x (k_* / gamma / sigma_B)[64 grid points]^T over
+// k < (I+1) NB and reduces the squares over each 32-row quadrant: partial[(4 I + q) * Bp + n].
+struct OzPredTiles {
+    const uint8_t* wdig; const uint8_t* kdig; int Np, nx;
+    const double* sigb; double* partial; size_t Bp;
+    __device__ __forceinline__ bool make(int tile, OzTile& t) const {
+        const int I = (Np / NB) - 1 - tile / nx, nb = tile % nx;          // deepest contraction first
+        const int kch = Np / 32;
+        t.a = wdig + (size_t)I * kch * OZ_CHUNK;
+        t.b = kdig + (size_t)(nb >> 1) * kch * OZ_CHUNK + (size_t)(nb & 1) * OZ_DIGIT_HALF;
+        t.nk = 4 * (I + 1);
+        t.c = nullptr;
+        t.ldc = 0;
+        t.sa = nullptr;
+        t.sa_const = 2.0 * sigb[0];
+        t.sb = nullptr;
+        oz_no_digits(t);
+        t.red = partial + (size_t)(4 * I) * Bp + (size_t)nb * OZ_TILE_N;
+        t.red_ld = Bp;
+        return true;
+    }
+};
+
+// gamma_k = 2^floor(log2 e_k), sigma_B = scale of max_k 1 / gamma_k, ginv_s[k] = 1 / (gamma_k sigma_B) (0 in the padding)
+__global__ void __launch_bounds__(256) k_oz_pred_scales(const double* __restrict__ e, int N, int Np, double* __restrict__ gam,
+                                                        double* __restrict__ ginv_s, double* __restrict__ sigb) {
+    __shared__ double red[8];
+    __shared__ double sig;
+    double m = 0.0;
+    for (int k = threadIdx.x; k < N; k += 256) {
+        const double ek = fabs(e[k]);
+        const double g = (ek > 1e-290 && ek < 1e290) ? scalbn(1.0, ilogb(ek)) : 1.0;
+        m = fmax(m, 1.0 / g);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w) m = fmax(m, red[w]);
+        sig = oz_scale_for(m);
+        sigb[0] = sig;
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < Np; k += 256) {
+        double g = 1.0, gi = 0.0;
+        if (k < N) {
+            const double ek = fabs(e[k]);
+            g = (ek > 1e-290 && ek < 1e290) ? scalbn(1.0, ilogb(ek)) : 1.0;
+            gi = 1.0 / (g * sig);
+        }
+        gam[k] = g;
+        ginv_s[k] = gi;
+    }
+}
+
+// digits of the whole lower block triangle of W (columns scaled by gamma, sigma = 2): grid (T, T), blocks J <= I
+__global__ void __launch_bounds__(256) k_oz_slice_wall(const double* __restrict__ W, int Np, const double* __restrict__ gam,
+                                                       uint8_t* __restrict__ wdig) {
+    const int J = blockIdx.x, I = blockIdx.y;
+    if (J > I) return;
+    oz_slice_tile(W + (size_t)I * NB * Np + (size_t)J * NB, Np, nullptr, 0.5, gam + J * NB,
+                  wdig + ((size_t)I * (Np / 32) + 4 * J) * OZ_CHUNK);
+}
+
+__device__ __forceinline__ double oz_rbf(double sq1, double sq2, double dot) {
+    // kernel_func, GP_func.py:59-65, same operation order as rbf_from_parts in gpk_cov.cu
+    double s = __dadd_rn(__dadd_rn(sq1, sq2), __dmul_rn(-2.0, dot));
+    s = fmax(s, 0.0);
+    return exp(__dmul_rn(-0.5, s));
+}
+
+// Cross covariance of a chunk of grid points straight into digit records (rows = grid points, K = training index),
+// with the predictive mean mu_b = sum_j k(x_j, x_b) alpha_j (GP_func.py:32,36) fused in.  One warp per grid point; a
+// lane owns 16 consecutive j (one 16-byte unit of every digit).
+__global__ void __launch_bounds__(256) k_oz_cross_cov(const double* __restrict__ xs, const double* __restrict__ sq,
+                                                      const double* __restrict__ ls, const double* __restrict__ alpha,
+                                                      const double* __restrict__ ginv_s, int N, int Np, int d,
+                                                      const double* __restrict__ Xfit, long long M, long long m0, int B,
+                                                      int Bp, uint8_t* __restrict__ kdig, double* __restrict__ mu_out) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int b = blockIdx.x * 8 + warp;
+    if (b >= Bp) return;
+    const int kch = Np / 32;
+    uint8_t* rec = kdig + (size_t)(b >> 7) * kch * OZ_CHUNK + ((b & 127) >> 3) * 256 + (b & 7) * 16;
+    double xb[MAX_D];
+    double sqb = 0.0;
+#pragma unroll
+    for (int dd = 0; dd < MAX_D; ++dd) {
+        xb[dd] = 0.0;
+        if (dd < d && b < B) {
+            xb[dd] = __ddiv_rn(Xfit[(size_t)dd * M + m0 + b], ls[dd]);
+            const double v2 = __dmul_rn(xb[dd], xb[dd]);
+            sqb = (dd == 0) ? v2 : __dadd_rn(sqb, v2);
+        }
+    }
+    double acc = 0.0;
+    for (int j0 = lane * 16; j0 < Np; j0 += 512) {
+        uint32_t lo[16], hi[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const int j = j0 + i;
+            double v = 0.0;
+            if (j < N && b < B) {
+                double dot = __dmul_rn(xs[j], xb[0]);
+#pragma unroll
+                for (int dd = 1; dd < MAX_D; ++dd)
+                    if (dd < d) dot = fma(xs[(size_t)dd * Np + j], xb[dd], dot);
+                v = oz_rbf(sq[j], sqb, dot);
+                acc = fma(v, alpha[j], acc);
+            }
+            const long long w = (__double2ll_rn(v * ginv_s[j] * 0x1p55) + OZ_BIAS) ^ OZ_BIAS;
+            lo[i] = (uint32_t)w;
+            hi[i] = (uint32_t)(w >> 32);
+        }
+        uint8_t* dd8 = rec + (size_t)(j0 >> 5) * OZ_CHUNK + ((j0 >> 4) & 1) * 128;
+#pragma unroll
+        for (int s = 0; s < OZ_NS; ++s) {
+            const int bytepos = 6 - s;
+            const uint32_t* w = (bytepos >= 4) ? hi : lo;
+            uint4 o;
+            o.x = pack_digit(w + 0, bytepos & 3);
+            o.y = pack_digit(w + 4, bytepos & 3);
+            o.z = pack_digit(w + 8, bytepos & 3);
+            o.w = pack_digit(w + 12, bytepos & 3);
+            *reinterpret_cast<uint4*>(dd8 + s * OZ_DIGIT) = o;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0 && b < B) mu_out[m0 + b] = acc;
+}
+
 // ---- launchers ------------------------------------------------------------------------------------------------
 template <typename K>
 static int oz_smem_attr(K kernel, bool& done) {
@@ -816,6 +974,43 @@ int launch_oz_gemm_tn(const uint8_t* A, const uint8_t* B, int M, int N, int K, c
     const OzGemmTiles f{A, B, K / 32, N / OZ_TILE_N, sa, sb, C, ldc, dbg, g_oz_groups};
     if (oz_launch<OZ_STORE>(f, f.nx * (M / NB), counter, st)) return 1;
     return check_launch("k_oz_gemm_tn");
+}
+
+// ---- prediction launchers -------------------------------------------------------------------------------------------
+static size_t oz_align256(size_t x) { return (x + 255) & ~(size_t)255; }
+// state of a fitted GP for the digit-GEMM prediction: [W digits][gamma Np][ginv_s Np][sigma_B]
+size_t oz_pred_state_bytes(int Np) { return oz_align256(oz_slice_bytes(Np)) + oz_align256((size_t)2 * Np * 8) + 256; }
+size_t oz_pred_workspace_bytes(int Np, int Bp) {
+    return oz_align256((size_t)(Bp / NB) * (Np / 32) * OZ_CHUNK) + oz_align256((size_t)4 * (Np / NB) * Bp * 8) + 256;
+}
+
+int launch_oz_pred_prepare(const double* W, const double* e, int N, int Np, uint8_t* state, cudaStream_t st) {
+    double* gam = (double*)(state + oz_align256(oz_slice_bytes(Np)));
+    double* ginv_s = gam + Np;
+    double* sigb = (double*)(state + oz_align256(oz_slice_bytes(Np)) + oz_align256((size_t)2 * Np * 8));
+    k_oz_pred_scales<<<1, 256, 0, st>>>(e, N, Np, gam, ginv_s, sigb);
+    if (check_launch("k_oz_pred_scales")) return 1;
+    const int T = Np / NB;
+    k_oz_slice_wall<<<dim3(T, T), 256, 0, st>>>(W, Np, gam, state);
+    return check_launch("k_oz_slice_wall");
+}
+
+// one chunk of B grid points (Bp = B rounded up to 128): digits of K_*, mean, |W k_*|^2 partial sums
+int launch_oz_predict_chunk(const uint8_t* state, const double* xs, const double* sq, const double* ls, const double* alpha,
+                            int N, int Np, int d, const double* Xfit, long long M, long long m0, int B, int Bp,
+                            uint8_t* workspace, double* mu_out, double** partial_out, cudaStream_t st) {
+    const double* ginv_s = (const double*)(state + oz_align256(oz_slice_bytes(Np))) + Np;
+    const double* sigb = (const double*)(state + oz_align256(oz_slice_bytes(Np)) + oz_align256((size_t)2 * Np * 8));
+    uint8_t* kdig = workspace;
+    double* partial = (double*)(workspace + oz_align256((size_t)(Bp / NB) * (Np / 32) * OZ_CHUNK));
+    int* counter = (int*)((uint8_t*)partial + oz_align256((size_t)4 * (Np / NB) * Bp * 8));
+    if (cudaMemsetAsync(counter, 0, sizeof(int), st) != cudaSuccess) { set_error("oz counter memset failed"); return 1; }
+    k_oz_cross_cov<<<(Bp + 7) / 8, 256, 0, st>>>(xs, sq, ls, alpha, ginv_s, N, Np, d, Xfit, M, m0, B, Bp, kdig, mu_out);
+    if (check_launch("k_oz_cross_cov")) return 1;
+    const OzPredTiles f{state, kdig, Np, Bp / OZ_TILE_N, sigb, partial, (size_t)Bp};
+    if (oz_launch<OZ_SUMSQ>(f, f.nx * (Np / NB), counter, st)) return 1;
+    *partial_out = partial;
+    return check_launch("k_oz_predict");
 }
 
 }  // namespace gpk

@@ -230,12 +230,26 @@ class GPFit:
         if int(info.item()) != 0:
             # numpy.linalg.cholesky's behaviour at GP_func.py:22
             raise np.linalg.LinAlgError("Matrix is not positive definite")
+        self.state = None
+        if self.mode != 0 and self.n > NB:
+            # digits of W for the int8 tensor-core prediction GEMM (emulated FP64), sliced once per fit
+            self.state = torch.empty(lib.gpk_predict_state_bytes(self.n), dtype=torch.uint8, device=dev)
+            st = lib.gpk_predict_prepare(self.W.data_ptr(), de.data_ptr(), self.n, self.state.data_ptr(),
+                                         self.state.numel(), _stream())
+            _lib.check(st, "gpk_predict_prepare")
 
     def predict_device(self, xfit_dev, m, chunk=DEFAULT_CHUNK):
         dev = device()
         mu = torch.empty(m, dtype=torch.float64, device=dev)
         sd = torch.empty(m, dtype=torch.float64, device=dev)
         chunk = int(max(NB, min(chunk, -(-m // NB) * NB)))
+        if self.state is not None:
+            ws = workspace(self.lib.gpk_predict_emu_workspace_bytes(self.n, chunk), "predict")
+            st = self.lib.gpk_predict_emu(self.state.data_ptr(), self.alpha.data_ptr(), self.xs.data_ptr(),
+                                          self.sq.data_ptr(), self.ls.data_ptr(), self.n, self.d, xfit_dev.data_ptr(), m,
+                                          mu.data_ptr(), sd.data_ptr(), chunk, ws.data_ptr(), ws.numel(), _stream())
+            _lib.check(st, "gpk_predict_emu")
+            return mu, sd
         ws = workspace(self.lib.gpk_predict_workspace_bytes(self.n, chunk), "predict")
         st = self.lib.gpk_predict(self.W.data_ptr(), self.alpha.data_ptr(), self.xs.data_ptr(), self.sq.data_ptr(),
                                   self.ls.data_ptr(), self.n, self.d, xfit_dev.data_ptr(), m, mu.data_ptr(),

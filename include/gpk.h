@@ -74,6 +74,17 @@ GPK_API int gpk_predict(const double* W, const double* alpha, const double* xs, 
                 int N, int d, const double* Xfit, long long M, double* mu_out, double* sd_out, int chunk,
                 void* workspace, size_t workspace_bytes, void* stream);
 
+/* (c) the same prediction with |W k_*|^2 on the int8 tcgen05 digit GEMM (emulated FP64, see gpk_set_precision):
+ *     gpk_predict_prepare slices the fitted W once into a caller-owned state buffer (needs e > 0), gpk_predict_emu then
+ *     builds the digits of each K_* chunk on the fly (no FP64 K_* in HBM) and reduces the squares in the epilogue.
+ *     Results do not depend on `chunk`. */
+GPK_API size_t gpk_predict_state_bytes(int N);
+GPK_API int gpk_predict_prepare(const double* W, const double* e, int N, void* state, size_t state_bytes, void* stream);
+GPK_API size_t gpk_predict_emu_workspace_bytes(int N, int chunk);
+GPK_API int gpk_predict_emu(const void* state, const double* alpha, const double* xs, const double* sq, const double* ls,
+                    int N, int d, const double* Xfit, long long M, double* mu_out, double* sd_out, int chunk,
+                    void* workspace, size_t workspace_bytes, void* stream);
+
 /* (d) generate_prob_surf row loop, calc_prob_surf.py:67-81 + sum_gaussians :15-30.
  *     table: [R][ncols] payload columns of the merged frame (interleaved mean, std; non-finite = gap).
  *     valid[r] = 1 if the row emits output; y_out/p_out [R][npoints] are written for valid rows only. */

@@ -44,7 +44,7 @@ def predict(n, d, m, label):
     grid = engine.to_dev(np.random.default_rng(0).random((d, m)))
     ms = timed(lambda: fit.predict_device(grid, m), reps=2, warm=1)
     fl = float(n) * n * m
-    print(json.dumps({"kernel": "gpk_predict (k_cross_cov + k_predict_gemm + finalize)", "config": label, "shape": f"N={n} d={d} M={m}",
+    print(json.dumps({"kernel": "gpk_predict", "precision": engine.get_precision(), "config": label, "shape": f"N={n} d={d} M={m}",
                       "ms": ms, "grid_pts_per_s": m / ms * 1e3, "algorithmic_TFLOPs": fl / ms * 1e3 / 1e12,
                       "frac_of_fp64_dmma_peak": fl / ms * 1e3 / 1e12 / FP64, "out_GBps": 16.0 * m / ms * 1e3 / 1e9,
                       "fit_ms_single_matrix": ms_fit}), flush=True)
@@ -71,7 +71,10 @@ if __name__ == "__main__":
     which = sys.argv[1:] or ["cov", "predict", "surface"]
     if "cov" in which: cov()
     if "predict" in which:
-        predict(1024, 2, 40000, "C2")
-        predict(4096, 3, 1000000, "C3")
+        for mode in ("fp64", "emu"):
+            engine.set_precision(mode)
+            predict(1024, 2, 40000, "C2")
+            predict(4096, 3, 1000000, "C3")
+        engine.set_precision("auto")
     if "surface" in which:
         surface(1 << 22, 16)
