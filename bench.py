@@ -279,6 +279,25 @@ def run_ours(args):
     dev_ms = e0.elapsed_time(e1)
     assert int(info.abs().sum().item()) == 0, "covariance not positive definite in the bench workload"
 
+    # ---- the same region with the native FP64 (DMMA) contractions, for reference next to the emulated default ----
+    native = None
+    if args.precision != "fp64" and not args.no_native:
+        engine.set_precision("fp64")
+        for _ in range(2):
+            ctx.counts_device(dpos, dact, P)
+        torch.cuda.synchronize()
+        n0, n1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n0.record(st)
+        for _ in range(2):
+            c_nat, _i = ctx.counts_device(dpos, dact, P)
+        n1.record(st)
+        torch.cuda.synchronize()
+        native = {"value": P * 2 / (n0.elapsed_time(n1) * 1e-3), "unit": UNIT, "per": "GPU", "steps": 2,
+                  "counts_identical_to_default": bool(torch.equal(c_nat, counts))}
+        engine.set_precision(args.precision)
+        ctx.counts_device(dpos, dact, P)
+        torch.cuda.synchronize()
+
     # ---- per-kernel-class device time: one extra, separately instrumented step (single stream, events after
     #      every launch); the timed region above runs uninstrumented with concurrent particle groups ----
     _lib.timing_begin(st.cuda_stream)
@@ -328,6 +347,9 @@ def run_ours(args):
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": "C3 loss evaluation: N=4096 points, d=3, swarm of 256 particles per GPU, S=1000 sigma scales",
                        **WORKLOAD, "particles_per_gpu": P, "algorithm": "Cholesky + triangular inverse (2/3 N^3 flop/eval)", "precision": args.precision,
+                       "arithmetic": ("FP64 emulated on the int8 tcgen05 tensor cores: error-free 7 x 8-bit digit split, "
+                                      "34 digit products, exact int32 accumulation; same rounding level as FP64 (DESIGN.md 3.1)")
+                       if args.precision != "fp64" else "native FP64 (DMMA)",
                        "l2_policy": "working set 34 GB per step >> 126 MB L2 (inputs larger than L2)"},
             "e2e": {"value": evals / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches),
@@ -344,6 +366,7 @@ def run_ours(args):
                          "whole_step_tflops": algorithmic_flops_per_eval(N) * P * args.steps / (dev_ms * 1e-3) / 1e12,
                          "kernel_share_of_step": {k: round(v[0] / total_cls_ms, 4) for k, v in sorted(classes.items(), key=lambda kv: -kv[1][0])}},
             "cpu_baseline": cpu_base,
+            "native_fp64": native,
             "loss_checksum": float(np.sum(losses[:P])),
         }
         print(json.dumps(line), flush=True)
@@ -359,6 +382,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--particles", type=int, default=WORKLOAD["particles_per_gpu"], help="particles per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-native", action="store_true", help="skip the short native-FP64 (DMMA) comparison run")
     ap.add_argument("--precision", default="emu", choices=["fp64", "emu", "emu28"],
                     help="fp64: native DMMA contractions; emu: FP64 emulated on the int8 tcgen05 tensor cores "
                          "(34 digit products); emu28: 28 digit products")
