@@ -44,8 +44,10 @@ def to_dev(a, dtype=None):
 #   "emu"    FP64 emulated on the int8 tcgen05 tensor cores (7-digit Ozaki split, 34 digit products): same rounding
 #            level as an FP64 dot product, 1.7x the loss-evaluation throughput at N = 4096; needs e > 0
 #   "emu28"  28 digit products (~2^8 larger truncation error)
-#   "auto"   "emu" whenever every e_i is finite and > 0, else "fp64"            (default; env GPK_PRECISION)
+#   "auto"   "emu" when every e_i is finite and > 0 and N >= 1024 (below that the native kernels are faster:
+#            profiles/r01_mode_crossover.log), else "fp64"                        (default; env GPK_PRECISION)
 _MODES = {"fp64": 0, "emu": 1, "emu28": 2}
+EMU_MIN_N = 1024
 _precision_pref = os.environ.get("GPK_PRECISION", "auto")
 
 
@@ -61,12 +63,12 @@ def get_precision():
     return _precision_pref
 
 
-def _resolve_precision(e_host):
-    """Mode number for a problem with uncertainties e_host (host array)."""
+def _resolve_precision(e_host, n=None):
+    """Mode number for a problem with uncertainties e_host (host array) and n known points."""
     pref = _precision_pref
     ok = bool(np.all(np.isfinite(e_host)) and np.all(np.abs(e_host) > 1e-150)) if e_host.size else False
     if pref == "auto":
-        return 1 if ok else 0
+        return 1 if ok and (n is None or n >= EMU_MIN_N) else 0
     if pref != "fp64" and not ok:
         raise ValueError("emulated-FP64 mode needs finite, non-zero e_known (use GPK_PRECISION=fp64)")
     return _MODES[pref]
@@ -150,7 +152,7 @@ class LossContext:
         self._pin_counts = None
 
     def _ws(self, p):
-        self.mode = _resolve_precision(self._e_ok)       # also sizes the workspace
+        self.mode = _resolve_precision(self._e_ok, self.n)       # also sizes the workspace
         _apply_precision(self.mode)
         need = self.lib.gpk_loss_workspace_bytes(p, self.n, self.d)
         have = _ws_cache.get((torch.cuda.current_device(), "loss"))
@@ -220,7 +222,7 @@ class GPFit:
         self.xs = torch.empty((self.d, self.np_), dtype=torch.float64, device=dev)
         self.sq = torch.empty(self.np_, dtype=torch.float64, device=dev)
         info = torch.zeros(1, dtype=torch.int32, device=dev)
-        self.mode = _resolve_precision(e)
+        self.mode = _resolve_precision(e, self.n)
         _apply_precision(self.mode)
         ws = workspace(lib.gpk_fit_workspace_bytes(self.n, self.d), "fit")
         st = lib.gpk_fit(dx.data_ptr(), dy.data_ptr(), de.data_ptr(), self.ls.data_ptr(), self.n, self.d,
