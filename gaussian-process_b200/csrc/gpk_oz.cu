@@ -780,64 +780,96 @@ __device__ __forceinline__ double oz_rbf(double sq1, double sq2, double dot) {
 }
 
 // Cross covariance of a chunk of grid points straight into digit records (rows = grid points, K = training index),
-// with the predictive mean mu_b = sum_j k(x_j, x_b) alpha_j (GP_func.py:32,36) fused in.  One warp per grid point; a
-// lane owns 16 consecutive j (one 16-byte unit of every digit).
+// with the predictive mean mu_b = sum_j k(x_j, x_b) alpha_j (GP_func.py:32,36) fused in.  A CTA owns XC_PTS grid points
+// (8 warps x XC_WPTS); a lane owns 16 consecutive j (one 16-byte unit of every digit).  The training-side arrays
+// (scaled points, |x|^2, alpha, 1 / (gamma sigma_B)) are staged through shared memory in blocks of 512 j, transposed to
+// [i = j % 16][lane = j / 16] with a row pitch of 33 so that both the coalesced fill and the per-lane reads are free of
+// bank conflicts (a lane reading its 16 consecutive doubles straight from global memory touches 32 lines per request and
+// is bound by the L1 tag rate: profiles/r01_ncu_predict_emu.md).
+constexpr int XC_WPTS = 2;
+constexpr int XC_PTS = 8 * XC_WPTS;
+constexpr int XC_PITCH = 33;
+constexpr int XC_ARR = 16 * XC_PITCH;       // doubles per staged array
 __global__ void __launch_bounds__(256) k_oz_cross_cov(const double* __restrict__ xs, const double* __restrict__ sq,
                                                       const double* __restrict__ ls, const double* __restrict__ alpha,
                                                       const double* __restrict__ ginv_s, int N, int Np, int d,
                                                       const double* __restrict__ Xfit, long long M, long long m0, int B,
                                                       int Bp, uint8_t* __restrict__ kdig, double* __restrict__ mu_out) {
+    extern __shared__ __align__(16) double xc_sm[];      // [d + 3][16][33]: xs rows, sq, alpha, ginv_s
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int b = blockIdx.x * 8 + warp;
-    if (b >= Bp) return;
+    const int b0 = blockIdx.x * XC_PTS + warp * XC_WPTS;
     const int kch = Np / 32;
-    uint8_t* rec = kdig + (size_t)(b >> 7) * kch * OZ_CHUNK + ((b & 127) >> 3) * 256 + (b & 7) * 16;
-    double xb[MAX_D];
-    double sqb = 0.0;
+    double xb[XC_WPTS][MAX_D], sqb[XC_WPTS], acc[XC_WPTS];
 #pragma unroll
-    for (int dd = 0; dd < MAX_D; ++dd) {
-        xb[dd] = 0.0;
-        if (dd < d && b < B) {
-            xb[dd] = __ddiv_rn(Xfit[(size_t)dd * M + m0 + b], ls[dd]);
-            const double v2 = __dmul_rn(xb[dd], xb[dd]);
-            sqb = (dd == 0) ? v2 : __dadd_rn(sqb, v2);
-        }
-    }
-    double acc = 0.0;
-    for (int j0 = lane * 16; j0 < Np; j0 += 512) {
-        uint32_t lo[16], hi[16];
+    for (int q = 0; q < XC_WPTS; ++q) {
+        const int b = b0 + q;
+        sqb[q] = 0.0;
+        acc[q] = 0.0;
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            const int j = j0 + i;
-            double v = 0.0;
-            if (j < N && b < B) {
-                double dot = __dmul_rn(xs[j], xb[0]);
-#pragma unroll
-                for (int dd = 1; dd < MAX_D; ++dd)
-                    if (dd < d) dot = fma(xs[(size_t)dd * Np + j], xb[dd], dot);
-                v = oz_rbf(sq[j], sqb, dot);
-                acc = fma(v, alpha[j], acc);
+        for (int dd = 0; dd < MAX_D; ++dd) {
+            xb[q][dd] = 0.0;
+            if (dd < d && b < B) {
+                xb[q][dd] = __ddiv_rn(Xfit[(size_t)dd * M + m0 + b], ls[dd]);
+                const double v2 = __dmul_rn(xb[q][dd], xb[q][dd]);
+                sqb[q] = (dd == 0) ? v2 : __dadd_rn(sqb[q], v2);
             }
-            const long long w = (__double2ll_rn(v * ginv_s[j] * 0x1p55) + OZ_BIAS) ^ OZ_BIAS;
-            lo[i] = (uint32_t)w;
-            hi[i] = (uint32_t)(w >> 32);
         }
-        uint8_t* dd8 = rec + (size_t)(j0 >> 5) * OZ_CHUNK + ((j0 >> 4) & 1) * 128;
+    }
+    const int narr = d + 3;
+    for (int jb = 0; jb < Np; jb += 512) {
+        __syncthreads();
+        for (int t = threadIdx.x; t < narr * 512; t += 256) {
+            const int a = t >> 9, jl = t & 511, j = jb + jl;
+            double v = 0.0;
+            if (j < N) v = (a < d) ? xs[(size_t)a * Np + j] : (a == d) ? sq[j] : (a == d + 1) ? alpha[j] : ginv_s[j];
+            xc_sm[a * XC_ARR + (jl & 15) * XC_PITCH + (jl >> 4)] = v;
+        }
+        __syncthreads();
+        const int j0 = jb + lane * 16;
+        if (j0 >= Np) continue;
 #pragma unroll
-        for (int s = 0; s < OZ_NS; ++s) {
-            const int bytepos = 6 - s;
-            const uint32_t* w = (bytepos >= 4) ? hi : lo;
-            uint4 o;
-            o.x = pack_digit(w + 0, bytepos & 3);
-            o.y = pack_digit(w + 4, bytepos & 3);
-            o.z = pack_digit(w + 8, bytepos & 3);
-            o.w = pack_digit(w + 12, bytepos & 3);
-            *reinterpret_cast<uint4*>(dd8 + s * OZ_DIGIT) = o;
+        for (int q = 0; q < XC_WPTS; ++q) {
+            const int b = b0 + q;
+            if (b >= Bp) continue;
+            uint32_t lo[16], hi[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const double* col = xc_sm + i * XC_PITCH + lane;
+                double v = 0.0;
+                if (j0 + i < N && b < B) {
+                    double dot = __dmul_rn(col[0], xb[q][0]);
+#pragma unroll
+                    for (int dd = 1; dd < MAX_D; ++dd)
+                        if (dd < d) dot = fma(col[dd * XC_ARR], xb[q][dd], dot);
+                    v = oz_rbf(col[d * XC_ARR], sqb[q], dot);
+                    acc[q] = fma(v, col[(d + 1) * XC_ARR], acc[q]);
+                }
+                const long long w = (__double2ll_rn(v * col[(d + 2) * XC_ARR] * 0x1p55) + OZ_BIAS) ^ OZ_BIAS;
+                lo[i] = (uint32_t)w;
+                hi[i] = (uint32_t)(w >> 32);
+            }
+            uint8_t* dd8 = kdig + (size_t)(b >> 7) * kch * OZ_CHUNK + ((b & 127) >> 3) * 256 + (b & 7) * 16 +
+                           (size_t)(j0 >> 5) * OZ_CHUNK + ((j0 >> 4) & 1) * 128;
+#pragma unroll
+            for (int s = 0; s < OZ_NS; ++s) {
+                const int bytepos = 6 - s;
+                const uint32_t* w = (bytepos >= 4) ? hi : lo;
+                uint4 o;
+                o.x = pack_digit(w + 0, bytepos & 3);
+                o.y = pack_digit(w + 4, bytepos & 3);
+                o.z = pack_digit(w + 8, bytepos & 3);
+                o.w = pack_digit(w + 12, bytepos & 3);
+                *reinterpret_cast<uint4*>(dd8 + s * OZ_DIGIT) = o;
+            }
         }
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    if (lane == 0 && b < B) mu_out[m0 + b] = acc;
+    for (int q = 0; q < XC_WPTS; ++q) {
+        double a = acc[q];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+        if (lane == 0 && b0 + q < B) mu_out[m0 + b0 + q] = a;
+    }
 }
 
 // ---- launchers ------------------------------------------------------------------------------------------------
@@ -1005,7 +1037,8 @@ int launch_oz_predict_chunk(const uint8_t* state, const double* xs, const double
     double* partial = (double*)(workspace + oz_align256((size_t)(Bp / NB) * (Np / 32) * OZ_CHUNK));
     int* counter = (int*)((uint8_t*)partial + oz_align256((size_t)4 * (Np / NB) * Bp * 8));
     if (cudaMemsetAsync(counter, 0, sizeof(int), st) != cudaSuccess) { set_error("oz counter memset failed"); return 1; }
-    k_oz_cross_cov<<<(Bp + 7) / 8, 256, 0, st>>>(xs, sq, ls, alpha, ginv_s, N, Np, d, Xfit, M, m0, B, Bp, kdig, mu_out);
+    k_oz_cross_cov<<<(Bp + XC_PTS - 1) / XC_PTS, 256, (size_t)(d + 3) * XC_ARR * sizeof(double), st>>>(
+        xs, sq, ls, alpha, ginv_s, N, Np, d, Xfit, M, m0, B, Bp, kdig, mu_out);
     if (check_launch("k_oz_cross_cov")) return 1;
     const OzPredTiles f{state, kdig, Np, Bp / OZ_TILE_N, sigb, partial, (size_t)Bp};
     if (oz_launch<OZ_SUMSQ>(f, f.nx * (Np / NB), counter, st)) return 1;
