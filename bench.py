@@ -224,6 +224,28 @@ def measure_fp64_peak(torch, dev):
     return 2.0 * n ** 3 / (best * 1e-3) / 1e12
 
 
+# DRAM bytes per launch of the digit-GEMM roles, from the ncu launch list of this command (dram__bytes_read.sum +
+# dram__bytes_write.sum, mean over the launches of one role; 64-particle groups): profiles/r01_launch_summary_v8.csv
+NCU_TRAFFIC_PER_LAUNCH = {"k_oz_invu": 1410.89e6 + 220.57e6, "k_oz_syrk": 1922.79e6 + 305.89e6}
+
+
+def dram_traffic(kernel, N, P, launches):
+    """roofline.traffic for the top kernel (measured by ncu earlier, same command) next to its algorithmic bytes."""
+    if kernel not in NCU_TRAFFIC_PER_LAUNCH or N != 4096 or P != 256:
+        return {"traffic": None}
+    T = N // 128
+    pairs = sum(n * (n + 1) // 2 for n in range(T))            # 128 x 128 operand blocks read per matrix per phase
+    per_matrix = pairs * 128 * 128 * 7                          # A digits: 7 bytes per element, each block read once
+    per_matrix += sum(range(T)) * 128 * 128 * 7                 # B digits (panel / block row) per block column
+    per_matrix += sum(range(T)) * 128 * 128 * (8 + 7)           # FP64 output tile + its digits for the next contraction
+    if kernel == "k_oz_syrk":
+        per_matrix += sum(range(T)) * 128 * 128 * 8             # the covariance tile it is subtracted from
+    return {"traffic": NCU_TRAFFIC_PER_LAUNCH[kernel],
+            "traffic_unit": "DRAM bytes per launch (64-particle group)",
+            "traffic_source": "ncu launch list of this command, profiles/r01_launch_summary_v8.csv",
+            "algorithmic_bytes_per_launch": per_matrix * 64 / (T - 1)}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -356,7 +378,8 @@ def run_ours(args):
             "clocks": clocks,
             "roofline": {"bound": "tensor", "kernel": top[0], "achieved": achieved,
                          "peak": INT8_PEAK_TOPS if emulated else fp64_peak, "unit": "TOP/s (int8)" if emulated else "TFLOP/s",
-                         "frac": (achieved / (INT8_PEAK_TOPS if emulated else fp64_peak)) if achieved else None, "traffic": None,
+                         "frac": (achieved / (INT8_PEAK_TOPS if emulated else fp64_peak)) if achieved else None,
+                         **dram_traffic(top[0], N, P, top[1][1]),
                          "peak_source": INT8_PEAK_SOURCE if emulated else
                                         "FP64 cuBLAS DGEMM 8192^3 measured in this run (MEASURED_PEAKS.json has no FP64 figure; "
                                         "DMMA issue-rate probe: 37.1 TFLOP/s, profiles/r01_fp64_peak_probe.txt)",

@@ -28,6 +28,8 @@
 // N <= 256 per K chunk instead of 28-34 of N = 64.
 #include "gpk_common.cuh"
 
+#include <cstdlib>
+
 namespace gpk {
 
 constexpr int OZ_NS = 7;                        // int8 digits per FP64 value
@@ -902,6 +904,8 @@ static int oz_grid(int ntiles) {
         int dev = 0;
         cudaGetDevice(&dev);
         if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
+        // experiment knob: leave some SMs to the panel kernels of the other particle groups (streams)
+        if (const char* v = getenv("GPK_OZ_SMS")) { const int n = atoi(v); if (n > 0 && n < sms) sms = n; }
     }
     return ntiles < sms ? ntiles : sms;       // one persistent CTA per SM (215 KB of shared memory, all of TMEM)
 }

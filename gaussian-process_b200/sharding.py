@@ -10,10 +10,46 @@ import torch
 import torch.distributed as dist
 
 
-def world():
+_local_depth = 0
+
+
+def dist_world():
+    """(rank, size) of the process group, whatever the sharding mode."""
     if dist.is_available() and dist.is_initialized():
         return dist.get_rank(), dist.get_world_size()
     return 0, 1
+
+
+def world():
+    """(rank, size) the swarm shards over: the process group, or (0, 1) inside `local_swarm()`."""
+    if _local_depth > 0:
+        return 0, 1
+    return dist_world()
+
+
+class local_swarm:
+    """Context in which swarm evaluations stay on this rank (no collective): used when whole experiments are the
+    sharded unit (GP_fit.create_GP with at least as many experiments as ranks)."""
+
+    def __enter__(self):
+        global _local_depth
+        _local_depth += 1
+        return self
+
+    def __exit__(self, *exc):
+        global _local_depth
+        _local_depth -= 1
+        return False
+
+
+def gather_objects(local, group=None):
+    """List of every rank's picklable `local`, in rank order, on every rank."""
+    rank, size = dist_world()
+    if size == 1:
+        return [local]
+    out = [None] * size
+    dist.all_gather_object(out, local, group=group)
+    return out
 
 
 def shard_slice(n, rank, size):
