@@ -6,7 +6,8 @@ GP_fit.py:20-164), SURVEY 8f row N1.  What changes underneath:
   experiments r, r + G, ... with its swarm kept local (no collective on the data path), the per-experiment tables are
   gathered once, and rank 0 alone writes files.  With fewer experiments than ranks every rank walks all experiments and
   the swarm shards inside `len_scale_opt` as before;
-* the chains of pandas outer merges (GP_fit.py:79,103,160) are one key sort (`tables.merge_outer`, identical result).
+* the chains of pandas outer merges (GP_fit.py:79,103,160) are one key sort (`tables.merge_outer`, identical result);
+* files are written by `tables.write_csv` (row N3: libgpk's threaded formatter, the same bytes as `to_csv`).
 
 `read_in.read_yaml` and `convex_hull.fill_convex_hull` are the reference's own modules, found further down sys.path."""
 import _bootstrap  # noqa: F401
@@ -20,7 +21,7 @@ from GP_func import GP
 from read_in import read_yaml
 
 from gaussian_process_b200 import sharding
-from gaussian_process_b200.tables import merge_outer
+from gaussian_process_b200.tables import merge_outer, write_csv
 
 
 def process_experiment(x_known, y_known, e_known, resolution, dim_labels, filename, exp_idx, total_exps, PSO_progress):
@@ -54,7 +55,7 @@ def write_individual_file(df, filename, out_path, total_exps, exp_idx):
         output_path = folder / f"{filename}_GP_results.txt"
     else:
         output_path = folder / f"{filename}_exp{exp_idx}_GP_results.txt"
-    df.to_csv(output_path, index=False)
+    write_csv(df, output_path)
     print(f"Written individual output file: {output_path}")
     return
 
@@ -64,7 +65,7 @@ def write_grouped_file(file_dfs, filename, out_path, dim_labels):
     folder = _output_folder(out_path)
     merged_df = merge_outer(file_dfs, dim_labels)
     output_path = folder / f"{filename}_GP_results.txt"
-    merged_df.to_csv(output_path, index=False)
+    write_csv(merged_df, output_path)
     print(f"Written grouped output file: {output_path}")
     return
 
@@ -79,7 +80,7 @@ def write_combined_file(experiment_dfs, out_path, dim_labels):
         combined_output_file = out_path
         combined_output_file.parent.mkdir(parents=True, exist_ok=True)
     merged_df = merge_outer(experiment_dfs, dim_labels)
-    merged_df.to_csv(combined_output_file, index=False)
+    write_csv(merged_df, combined_output_file)
     print(f"Combined results written to {combined_output_file}")
     return merged_df
 

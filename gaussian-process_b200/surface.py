@@ -1,15 +1,15 @@
 """Probability-surface step: host side of calc_prob_surf.py on top of the fused GPU reduction.
 
 The row loop of generate_prob_surf (calc_prob_surf.py:67-81: finite mask, linspace y-axis,
-sum_gaussians) is one `gpk_prob_surface` launch over the whole merged table; the frame assembly
-and `to_csv` (:83-84, frozen text format) stay in pandas."""
+sum_gaussians) is one `gpk_prob_surface` launch over the whole merged table; the frame assembly (:83) stays in
+pandas and the frozen text format of `to_csv` (:84) is written by libgpk's threaded formatter (tables.write_csv)."""
 import os
 
 import numpy as np
 import pandas as pd
 import yaml
 
-from . import engine
+from . import engine, tables
 
 POINTS = 100                      # calc_prob_surf.py:45
 DEFAULT_FILENAME = "prob_surf.txt"
@@ -52,6 +52,6 @@ def generate_prob_surf(df, ndims, options_path="options.yaml"):
     print("Calculating Probability")
     output_file = resolve_output_path(options_path)
     output_df = surface_frame(df, ndims)
-    output_df.to_csv(output_file, index=False)
+    tables.write_csv(output_df, output_file)               # the bytes of to_csv(index=False), :84
     print(f"Probability results written to {output_file}")
     return

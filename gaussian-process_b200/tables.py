@@ -8,7 +8,11 @@ lattice of fill_convex_hull is de-duplicated, convex_hull.py:34) the result is s
 lexicographic order, each experiment's columns scattered into place, +inf elsewhere -- one sort of all keys.
 `merge_outer` does that and returns exactly the DataFrame the pandas expression returns (same rows, row order, column
 order, dtypes, index); anything it does not cover (duplicate keys, non-float columns, NaN keys, overlapping value column
-names) goes through the pandas expression itself."""
+names) goes through the pandas expression itself.
+
+Row N3: `write_csv(df, path)` writes what `df.to_csv(path, index=False)` writes (GP_fit.py:63,81,104;
+calc_prob_surf.py:84), byte for byte, with the float formatting done by libgpk's threaded formatter
+(`gpk_csv_format_f64`) instead of pandas' per-value Python objects."""
 from functools import reduce
 
 import numpy as np
@@ -100,3 +104,39 @@ def merge_outer(dfs, dim_labels):
             out[c] = col
         off += len(df)
     return pd.DataFrame(out)
+
+
+_CSV_BLOCK_ROWS = 1 << 20
+
+
+def _plain_header(columns):
+    """Header line if no column name needs CSV quoting, else None."""
+    names = []
+    for c in columns:
+        if not isinstance(c, str) or c == "" or any(ch in c for ch in ',"\r\n'):
+            return None
+        names.append(c)
+    return ",".join(names) + "\n"
+
+
+def write_csv(df, path, threads=0):
+    """df.to_csv(path, index=False) for an all-float64 table; anything else is handed to pandas."""
+    header = _plain_header(df.columns)
+    if header is None or len(df.columns) == 0 or any(dt != np.float64 for dt in df.dtypes):
+        df.to_csv(path, index=False)
+        return
+    import ctypes as C
+    from . import _lib
+    lib = _lib.load()
+    ncol = len(df.columns)
+    with open(path, "wb") as f:
+        f.write(header.encode("utf-8"))
+        for r0 in range(0, len(df), _CSV_BLOCK_ROWS):
+            block = np.ascontiguousarray(df.iloc[r0:r0 + _CSV_BLOCK_ROWS].to_numpy(dtype=np.float64))
+            cap = lib.gpk_csv_bound(block.shape[0], ncol)
+            out = np.empty(cap, dtype=np.uint8)
+            n = lib.gpk_csv_format_f64(block.ctypes.data_as(C.c_void_p), block.shape[0], ncol, ncol,
+                                       out.ctypes.data_as(C.c_void_p), cap, threads)
+            if n < 0:
+                raise _lib.GpkError("gpk_csv_format_f64 rejected its arguments")
+            f.write(memoryview(out)[:n])

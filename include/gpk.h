@@ -124,6 +124,15 @@ GPK_API int gpk_oz_slice(const double* src, int ld, int rows, int cols, const do
 GPK_API int gpk_oz_gemm_tn(const void* A, const void* B, int M, int N, int K, const double* sa, const double* sb,
                    double* C, int ldc, int* dbg, int groups, void* stream);
 
+/* Result tables as text (host code, no device work): rows x cols float64 (row stride ld) -> CSV bytes exactly as the
+ * reference writes them with pandas.DataFrame.to_csv(index=False) (GP_fit.py:63,81,104; calc_prob_surf.py:84):
+ * shortest round-trip digits, positional for 1e-4 <= |x| < 1e16, "1e-05"-style exponents otherwise, "inf"/"-inf",
+ * NaN as an empty field, '\n' line ends; no header line.  `out` must hold gpk_csv_bound(rows, cols) bytes; rows are
+ * formatted by `threads` host threads (0 = all); returns the number of bytes written, or -1 on bad arguments. */
+GPK_API size_t gpk_csv_bound(long long rows, int cols);
+GPK_API long long gpk_csv_format_f64(const double* table, long long rows, int cols, long long ld, char* out,
+                                     size_t out_cap, int threads);
+
 /* Measurement aid (bench.py roofline): per-kernel-class device time by events recorded after every launch
  * on `stream` between begin and end.  Not thread-safe; name_out is a HOST buffer. */
 GPK_API int gpk_timing_begin(void* stream);
