@@ -246,6 +246,47 @@ def dram_traffic(kernel, N, P, launches):
             "algorithmic_bytes_per_launch": per_matrix * 64 / (T - 1)}
 
 
+def aux_measurements(torch, engine):
+    """The other two quantities BASELINE.json's metric names, on one GPU: grid points/s of the predictive mean/sd
+    (C3: N=4096, d=3, 100^3 grid) and rows/s of the probability surface (16 experiments with gaps), each device-resident
+    and end to end through the public call with host arrays."""
+    from oracle import gp_oracle as orc               # synthetic data generators only
+    out = {}
+    N, d, M = WORKLOAD["n_points"], WORKLOAD["dims"], 100 ** 3
+    x, y, e = orc.synthetic_problem(N, d, 1)
+    ls = np.full(d, 0.25)
+    xfit = np.random.default_rng(0).random((d, M))
+    engine.gp(x, y, e, xfit[:, :20000], ls)                                   # warm-up (workspaces, module load)
+    t0 = time.perf_counter()
+    mu, sd = engine.gp(x, y, e, xfit, ls)
+    e2e_s = time.perf_counter() - t0
+    fit = engine.GPFit(x, y, e, ls)
+    grid = engine.to_dev(xfit)
+    fit.predict_device(grid, M)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    fit.predict_device(grid, M)
+    e1.record()
+    torch.cuda.synchronize()
+    out["grid_predict"] = {"workload": f"C3 prediction: N={N}, d={d}, {M} grid points", "value": M / (e0.elapsed_time(e1) * 1e-3),
+                           "unit": "grid_pts/s", "e2e": {"value": M / e2e_s, "unit": "grid_pts/s", "includes": "fit + H2D of the grid + predict + D2H of mean and sd",
+                                                         "h2d_bytes": int(xfit.nbytes), "d2h_bytes": int(mu.nbytes + sd.nbytes)},
+                           "precision": {0: "fp64", 1: "emu", 2: "emu28"}[fit.mode], "sd_checksum": float(sd.sum())}
+    del grid, fit
+    R, E = 1 << 22, 16
+    t = orc.synthetic_surface_table(1 << 18, E, seed=3)
+    table = np.tile(t, (R // t.shape[0], 1))
+    engine.prob_surface(table[:1 << 16])
+    t0 = time.perf_counter()
+    idx, yy, pp = engine.prob_surface(table)
+    s_e2e = time.perf_counter() - t0
+    out["prob_surface"] = {"workload": f"surface reduction: {R} merged rows, {E} experiments, 25% gaps, 100 points per row",
+                           "e2e": {"value": R / s_e2e, "unit": "rows/s", "h2d_bytes": int(table.nbytes), "d2h_bytes": int(yy.nbytes + pp.nbytes + idx.nbytes)},
+                           "valid_rows": int(len(idx))}
+    return out
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -343,6 +384,12 @@ def run_ours(args):
     h2d = (d * N + 2 * N + S + P * d) * 8 + P
     d2h = P * S * 4 + P * 4
 
+    aux = None
+    if rank == 0 and world == 1 and not args.no_aux:
+        del ctx
+        engine.release_workspaces()
+        aux = aux_measurements(torch, engine)
+
     if world > 1:
         t = torch.tensor([dev_ms, e2e_s], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -390,6 +437,7 @@ def run_ours(args):
                          "kernel_share_of_step": {k: round(v[0] / total_cls_ms, 4) for k, v in sorted(classes.items(), key=lambda kv: -kv[1][0])}},
             "cpu_baseline": cpu_base,
             "native_fp64": native,
+            "aux": aux,
             "loss_checksum": float(np.sum(losses[:P])),
         }
         print(json.dumps(line), flush=True)
@@ -405,6 +453,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--particles", type=int, default=WORKLOAD["particles_per_gpu"], help="particles per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-aux", action="store_true", help="skip the grid-prediction and surface measurements")
     ap.add_argument("--no-native", action="store_true", help="skip the short native-FP64 (DMMA) comparison run")
     ap.add_argument("--precision", default="emu", choices=["fp64", "emu", "emu28"],
                     help="fp64: native DMMA contractions; emu: FP64 emulated on the int8 tcgen05 tensor cores "

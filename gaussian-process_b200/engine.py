@@ -278,31 +278,95 @@ def gp(x_known, y_known, e_known, x_fit, lengths, batch_size=10000):
 
 
 # ------------------------------------------------------------------------------------ (d)
+_pinned = {}
+
+
+def _pinned_buffer(tag, nbytes):
+    """Grow-only page-locked staging buffer (uint8) per tag."""
+    buf = _pinned.get(tag)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(int(nbytes), dtype=torch.uint8).pin_memory()
+        _pinned[tag] = buf
+    return buf
+
+
 def prob_surface(table, points=100, rows_per_pass=None):
-    """table (R, 2E) host payload -> (row_index[Rv], y[Rv,points], p[Rv,points]) of the emitting rows."""
+    """table (R, 2E) host payload -> (row_index[Rv], y[Rv,points], p[Rv,points]) of the emitting rows.
+    Passes of `rows_per_pass` rows are pipelined over two streams: while pass k's compacted result drains to the host
+    through page-locked staging buffers (the output is 1600 B per row, so this path is PCIe bound), pass k+1 uploads and
+    computes."""
     lib = _lib.load()
     table = _f64(table)
     r, ncols = table.shape
     if r == 0 or ncols == 0:
         return np.zeros(0, dtype=np.int64), np.zeros((0, points)), np.zeros((0, points))
     if rows_per_pass is None:
-        rows_per_pass = max(1, min(r, (1 << 28) // (points * 16)))
-    idx_parts, y_parts, p_parts = [], [], []
+        rows_per_pass = max(1, min(r, (1 << 27) // (points * 8)))        # 128 MB of y (and of p) per pass
     dev = device()
-    for r0 in range(0, r, rows_per_pass):
+    y_out = np.empty((r, points))
+    p_out = np.empty((r, points))
+    idx_out = np.empty(r, dtype=np.int64)
+    y_t, p_t, idx_t = torch.from_numpy(y_out), torch.from_numpy(p_out), torch.from_numpy(idx_out)
+    streams = [torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)]
+    main = torch.cuda.current_stream()
+    for st_ in streams:
+        st_.wait_stream(main)
+    slot_bytes = rows_per_pass * points * 8
+    pending = [None, None]              # per slot: (rows kept, staging views, first row, done event)
+    n_out = 0
+
+    def drain(slot):
+        nonlocal n_out
+        item = pending[slot]
+        if item is None:
+            return
+        k, ys, ps, ids, r0, done = item
+        done.synchronize()
+        y_t[n_out:n_out + k].copy_(ys[:k])                                # threaded host copy out of the staging buffer
+        p_t[n_out:n_out + k].copy_(ps[:k])
+        idx_t[n_out:n_out + k].copy_(ids[:k])
+        idx_out[n_out:n_out + k] += r0
+        n_out += k
+        pending[slot] = None
+
+    for i, r0 in enumerate(range(0, r, rows_per_pass)):
+        slot = i & 1
+        drain(slot)                                                       # its staging buffers are about to be reused
         rc = min(rows_per_pass, r - r0)
-        dt = to_dev(table[r0:r0 + rc])
-        y = torch.empty((rc, points), dtype=torch.float64, device=dev)
-        p = torch.empty((rc, points), dtype=torch.float64, device=dev)
-        valid = torch.empty(rc, dtype=torch.int32, device=dev)
-        st = lib.gpk_prob_surface(dt.data_ptr(), rc, ncols, points, y.data_ptr(), p.data_ptr(), valid.data_ptr(),
-                                  _stream())
-        _lib.check(st, "gpk_prob_surface")
-        keep = torch.nonzero(valid, as_tuple=False).reshape(-1)
-        idx_parts.append(keep.cpu().numpy() + r0)
-        y_parts.append(y.index_select(0, keep).cpu().numpy())
-        p_parts.append(p.index_select(0, keep).cpu().numpy())
-    return np.concatenate(idx_parts), np.concatenate(y_parts), np.concatenate(p_parts)
+        stage_in = _pinned_buffer(("surf_in", slot), rows_per_pass * ncols * 8)[:rc * ncols * 8].view(torch.float64).view(rc, ncols)
+        stage_in.copy_(torch.from_numpy(table[r0:r0 + rc]))
+        ys = _pinned_buffer(("surf_y", slot), slot_bytes).view(torch.float64)[:rc * points].view(rc, points)
+        ps = _pinned_buffer(("surf_p", slot), slot_bytes).view(torch.float64)[:rc * points].view(rc, points)
+        ids = _pinned_buffer(("surf_i", slot), rows_per_pass * 8).view(torch.int64)[:rc]
+        with torch.cuda.stream(streams[slot]):
+            dt = stage_in.to(dev, non_blocking=True)
+            y = torch.empty((rc, points), dtype=torch.float64, device=dev)
+            p = torch.empty((rc, points), dtype=torch.float64, device=dev)
+            valid = torch.empty(rc, dtype=torch.int32, device=dev)
+            st = lib.gpk_prob_surface(dt.data_ptr(), rc, ncols, points, y.data_ptr(), p.data_ptr(), valid.data_ptr(),
+                                      streams[slot].cuda_stream)
+            _lib.check(st, "gpk_prob_surface")
+            # rows that do not emit are rare: ship everything when all rows are valid, else compact on the device first
+            keep = torch.nonzero(valid, as_tuple=False).reshape(-1)
+            k = keep.numel()                                              # (synchronises this stream only)
+            if k == rc:
+                ys.copy_(y, non_blocking=True)
+                ps.copy_(p, non_blocking=True)
+            else:
+                ys[:k].copy_(y.index_select(0, keep), non_blocking=True)
+                ps[:k].copy_(p.index_select(0, keep), non_blocking=True)
+            ids[:k].copy_(keep, non_blocking=True)
+            done = torch.cuda.Event()
+            done.record(streams[slot])
+        pending[slot] = (k, ys, ps, ids, r0, done)
+    drain(0 if pending[0] is not None and (pending[1] is None or pending[0][4] < pending[1][4]) else 1)
+    drain(0)
+    drain(1)
+    main.wait_stream(streams[0])
+    main.wait_stream(streams[1])
+    if n_out == r:
+        return idx_out, y_out, p_out
+    return idx_out[:n_out].copy(), y_out[:n_out].copy(), p_out[:n_out].copy()
 
 
 def sum_gaussians(y, gaus, half_dy):

@@ -187,6 +187,21 @@ def test_surface_golden(mods):
         np.testing.assert_allclose(p.reshape(-1), c["out_yp"][:, 1], rtol=1e-9, atol=1e-15, err_msg=str(name))
 
 
+@pytest.mark.parametrize("rows_per_pass", [257, 1000, None])
+def test_surface_passes_and_silent_rows(mods, rows_per_pass):
+    """Several pipelined passes (two streams, staged copies) with rows that emit nothing (all pairs masked, or an odd
+    number of finite entries, calc_prob_surf.py:71) in between: same rows, same order, same values as the row loop."""
+    t = orc.synthetic_surface_table(3000, 3, seed=9, p_gap=0.55)
+    t[5::97, 1] = np.inf                              # odd number of finite entries in those rows
+    t[:40] = np.inf                                   # a whole leading block without data
+    idx, y, p = mods["engine"].prob_surface(t, rows_per_pass=rows_per_pass)
+    i_r, y_r, p_r = orc.prob_surface_rows(t)
+    assert 0 < len(i_r) < len(t)
+    np.testing.assert_array_equal(idx, i_r)
+    np.testing.assert_array_equal(y, y_r)
+    np.testing.assert_allclose(p, p_r, rtol=1e-9, atol=1e-15)
+
+
 def test_generate_prob_surf_csv(mods, tmp_path, monkeypatch):
     import pandas as pd
     g = load_golden("surface_cases.npz")
