@@ -301,7 +301,12 @@ def run_ours(args):
 
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    json_fd = None
     if world > 1:
+        # NCCL writes its version banner to stdout at communicator creation: keep stdout for the one JSON line
+        sys.stdout.flush()
+        json_fd = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
     _lib.load()
     engine.set_precision(args.precision)
@@ -440,7 +445,10 @@ def run_ours(args):
             "aux": aux,
             "loss_checksum": float(np.sum(losses[:P])),
         }
-        print(json.dumps(line), flush=True)
+        if json_fd is not None:
+            os.write(json_fd, (json.dumps(line) + "\n").encode())
+        else:
+            print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
