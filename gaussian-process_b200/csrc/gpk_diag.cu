@@ -10,17 +10,15 @@ k_diag_block(double* __restrict__ mat, int Np, int J, double* __restrict__ dinv,
              int T, int* __restrict__ info, const unsigned char* __restrict__ active, int mode) {
     extern __shared__ double smem[];
     double* Lm = smem;
-    double* col = smem + NB * CI_LD;
-    double* xr = col + NB;
+    double* work = smem + NB * CI_LD;
+    double* xr = work + CI_WORK;
     const int p = blockIdx.x;
     if (active && !active[p]) return;
     const int tid = threadIdx.x;
     double* blk = mat + (size_t)p * Np * Np + (size_t)J * NB * Np + (size_t)J * NB;
 
     // each thread loads its 8x8 register tile of the lower triangle (the X part starts at zero)
-    double* v = col;
     double* xd = xr;
-    double* piv = xr + NB;
     double E[8][8];
     {
         const int R0 = (tid >> 4) * 8, C0 = (tid & 15) * 8;
@@ -32,7 +30,7 @@ k_diag_block(double* __restrict__ mat, int Np, int J, double* __restrict__ dinv,
                 E[rr][cc] = (c <= r) ? blk[(size_t)r * Np + c] : 0.0;
             }
     }
-    const int bad = chol_inv_regs(E, NB, v, xd, piv);
+    const int bad = chol_inv_regs(E, NB, work, xd);
     if (bad && tid == 0) atomicCAS(&info[p], 0, J * NB + bad);
     chol_inv_dump(E, xd, Lm);
     __syncthreads();

@@ -58,7 +58,7 @@ __device__ __forceinline__ void resid_sigma(double d, double alpha, double cn, d
 struct SmallSmem {
     static constexpr size_t lm = 0;
     static constexpr size_t col = lm + (size_t)NB * CI_LD * 8;
-    static constexpr size_t xr = col + NB * 8;
+    static constexpr size_t xr = col + (size_t)CI_WORK * 8;
     static constexpr size_t xs = xr + NB * 8;
     static constexpr size_t sq = xs + (size_t)MAX_D * NB * 8;
     static constexpr size_t y = sq + NB * 8;
@@ -132,8 +132,7 @@ k_small_loss(const double* __restrict__ X, const double* __restrict__ y, const d
                 E[rr][cc] = val;
             }
     }
-    double* piv = reinterpret_cast<double*>(raw + SmallSmem::piv);
-    const int bad = chol_inv_regs(E, N, col, xr, piv);
+    const int bad = chol_inv_regs(E, N, col, xr);
     if (bad && tid == 0) info[p] = bad;
     chol_inv_dump(E, xr, Lm);
     __syncthreads();
