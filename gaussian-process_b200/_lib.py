@@ -77,13 +77,24 @@ def launch_count():
     return int(load().gpk_launch_count())
 
 
+_timing = False
+
+
+def timing_active():
+    return _timing
+
+
 def timing_begin(stream):
+    global _timing
     check(load().gpk_timing_begin(stream), "gpk_timing_begin")
+    _timing = True
 
 
 def timing_end():
     """-> {kernel class: (total ms, launches)} since timing_begin."""
+    global _timing
     lib = load()
+    _timing = False
     check(lib.gpk_timing_end(), "gpk_timing_end")
     out, i = {}, 0
     name = C.create_string_buffer(128)

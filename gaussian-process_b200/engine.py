@@ -78,6 +78,14 @@ def _apply_precision(mode):
     _lib.check(_lib.load().gpk_set_precision(int(mode)), "gpk_set_precision")
 
 
+# CUDA-graph replay of the blocked loss evaluation where launch latency shows (128 < N <= 2048); GPK_GRAPH=0 disables
+GRAPH_MIN_N, GRAPH_MAX_N = 128, 2048
+
+
+def _graphs_enabled():
+    return os.environ.get("GPK_GRAPH", "1") != "0" and not _lib.timing_active()
+
+
 _ws_cache = {}
 
 
@@ -150,11 +158,15 @@ class LossContext:
         self._e_ok = e
         self._pin_pos = None
         self._pin_counts = None
+        self._mode_key = None
+        self._graphs = {}
 
     def _ws(self, p):
-        self.mode = _resolve_precision(self._e_ok, self.n)       # also sizes the workspace
-        _apply_precision(self.mode)
-        need = self.lib.gpk_loss_workspace_bytes(p, self.n, self.d)
+        if self._mode_key != _precision_pref:                 # the e-scan is O(N): once per policy, not per call
+            self.mode = _resolve_precision(self._e_ok, self.n)
+            self._mode_key = _precision_pref
+        _apply_precision(self.mode)                            # process-wide switch: other contexts may have moved it
+        need = self.lib.gpk_loss_workspace_bytes(p, self.n, self.d)     # sized for the mode just applied
         have = _ws_cache.get((torch.cuda.current_device(), "loss"))
         if have is not None and have.numel() >= need:
             return have
@@ -164,21 +176,61 @@ class LossContext:
             need = max(one, budget // one * one)
         return workspace(need, "loss")
 
+    def _launch(self, positions_dev, active_dev, p, counts, info, resid, sd, ws):
+        st = self.lib.gpk_loss_batched(
+            self.x.data_ptr(), self.y.data_ptr(), self.e.data_ptr(), positions_dev.data_ptr(),
+            active_dev.data_ptr() if active_dev is not None else None, self.sig.data_ptr(), p, self.n, self.d,
+            self.s, counts.data_ptr(), info.data_ptr(), resid.data_ptr() if resid is not None else None,
+            sd.data_ptr() if sd is not None else None, ws.data_ptr(), ws.numel(), _stream())
+        _lib.check(st, "gpk_loss_batched")
+
     def counts_device(self, positions_dev, active_dev, p, want_detail=False):
-        """All inputs already on the device; returns device tensors (counts, info[, resid, sd])."""
+        """All inputs already on the device; returns device tensors (counts, info[, resid, sd]).  In the launch-bound
+        range of the blocked path the evaluation is replayed from a CUDA graph; the tensors returned then belong to the
+        context and are overwritten by its next evaluation."""
         dev = device()
+        ws = self._ws(p)
+        if not want_detail and GRAPH_MIN_N < self.n <= GRAPH_MAX_N and _graphs_enabled():
+            return self._counts_graphed(positions_dev, active_dev, p, ws)
         counts = torch.empty((p, self.s), dtype=torch.int32, device=dev)
         info = torch.empty(p, dtype=torch.int32, device=dev)
         resid = torch.empty((p, self.n), dtype=torch.float64, device=dev) if want_detail else None
         sd = torch.empty((p, self.n), dtype=torch.float64, device=dev) if want_detail else None
-        ws = self._ws(p)
-        st = self.lib.gpk_loss_batched(
-            self.x.data_ptr(), self.y.data_ptr(), self.e.data_ptr(), positions_dev.data_ptr(),
-            active_dev.data_ptr() if active_dev is not None else None, self.sig.data_ptr(), p, self.n, self.d,
-            self.s, counts.data_ptr(), info.data_ptr(), resid.data_ptr() if want_detail else None,
-            sd.data_ptr() if want_detail else None, ws.data_ptr(), ws.numel(), _stream())
-        _lib.check(st, "gpk_loss_batched")
+        self._launch(positions_dev, active_dev, p, counts, info, resid, sd, ws)
         return (counts, info, resid, sd) if want_detail else (counts, info)
+
+    def _counts_graphed(self, positions_dev, active_dev, p, ws):
+        """One swarm evaluation of the blocked path is ~16 launches per block column on up to four streams; for
+        N <= 2048 their launch latency is a visible share of the step.  Captured once per (swarm size, mode,
+        workspace) into a CUDA graph with static input / output tensors, replayed afterwards."""
+        key = (p, self.mode, ws.data_ptr(), ws.numel())
+        g = self._graphs.get(key)
+        if g is None:
+            dev = device()
+            st = {"pos": torch.empty((p, self.d), dtype=torch.float64, device=dev),
+                  "act": torch.ones(p, dtype=torch.uint8, device=dev),
+                  "counts": torch.empty((p, self.s), dtype=torch.int32, device=dev),
+                  "info": torch.empty(p, dtype=torch.int32, device=dev)}
+            st["pos"].copy_(positions_dev)
+            cur = torch.cuda.current_stream()
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):                  # warm-up outside the capture (attribute calls, streams)
+                self._launch(st["pos"], st["act"], p, st["counts"], st["info"], None, None, ws)
+            cur.wait_stream(side)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                self._launch(st["pos"], st["act"], p, st["counts"], st["info"], None, None, ws)
+            self._graphs.clear()                           # one live graph per context (its workspace is shared)
+            g = self._graphs[key] = (graph, st)
+        graph, st = g
+        st["pos"].copy_(positions_dev)
+        if active_dev is not None:
+            st["act"].copy_(active_dev)
+        else:
+            st["act"].fill_(1)
+        graph.replay()
+        return st["counts"], st["info"]
 
     def counts(self, positions, active=None, want_detail=False):
         """positions (P,d) host -> counts (P,S) int32 host (+ info, optional resid/sd)."""
