@@ -8,7 +8,8 @@
 //
 // Step j (right-looking): the threads owning column j scale it by 1/sqrt(E(j,j)) and publish it three times:
 //   v[r]   = the scaled column (L part for r > j, X part for r < j, 1/L_jj at r = j),
-//   vcm[c] = v[c] for c > j, else 0      (columns <= j are final),
+//   vcm[c] = v[c] for c > j, else 0      (columns <= j are final; stored as [c % 8][c / 8] so that the 16 tile
+//                                         columns of a warp read 16 consecutive doubles: no bank conflicts),
 //   vup[r] = v[r] for r <= j, else 0     (rows of the X part that have not started yet must stay zero).
 // Every element with column c > j that is either in the lower triangle (c <= r) or in the X part with r <= j then
 // receives E(r,c) -= v[r] * v[c]: with the masks folded into the published vectors this is 64 unconditional FMAs per
@@ -68,7 +69,7 @@ __device__ __forceinline__ int chol_inv_regs(double (&E)[8][8], int n, double* w
                             E[rr][jj] = t;
                         }
                         v[r] = t;
-                        vcm[r] = (r > j) ? t : 0.0;
+                        vcm[rr * 16 + tr] = (r > j) ? t : 0.0;      // [r % 8][r / 8]: see the load below
                         vup[r] = (r <= j) ? t : 0.0;
                     }
                 }
@@ -77,7 +78,7 @@ __device__ __forceinline__ int chol_inv_regs(double (&E)[8][8], int n, double* w
                 if (C0 + 7 > j && !(tc > tr && R0 > j)) {
                     double lo[8], up[8], vc[8];
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) { lo[k] = row_lo[R0 + k]; up[k] = row_up[R0 + k]; vc[k] = vcm[C0 + k]; }
+                    for (int k = 0; k < 8; ++k) { lo[k] = row_lo[R0 + k]; up[k] = row_up[R0 + k]; vc[k] = vcm[k * 16 + tc]; }
                     // the owner of the next pivot updates that element first and publishes it with its square root and
                     // reciprocal, so that the serial chain of the factorisation does not wait for its other 63 products
                     const int jn = j + 1;
