@@ -127,3 +127,31 @@ def test_emulated_mode_rejects_zero_uncertainty(env):
     finally:
         engine.set_precision("auto")
     assert engine._resolve_precision(e) == 0          # auto falls back to the native FP64 kernels
+
+
+@pytest.mark.parametrize("mode", ["fp64", "emu"])
+def test_graph_replay_equals_direct_launches(env, mode, monkeypatch):
+    """128 < N <= 2048 replays the evaluation from a CUDA graph: same counts as direct launches, for changing
+    positions, active masks and swarm sizes on one context."""
+    torch, lib, _lib, engine = env
+    from oracle import gp_oracle as orc
+    x, y, e = orc.synthetic_problem(300, 2, 5)
+    s, ex = orc.sigma_grid()
+    engine.set_precision(mode)
+    try:
+        ctx_g = engine.LossContext(x, y, e, s)
+        ctx_d = engine.LossContext(x, y, e, s)
+        for seed, p in ((1, 6), (2, 6), (3, 9), (4, 6)):
+            pos, lo, hi = orc.synthetic_particles(x, p, seed)
+            act = (np.arange(p) % 3 != seed % 3).astype(np.uint8)
+            monkeypatch.setenv("GPK_GRAPH", "1")
+            cg, ig = ctx_g.counts(pos, active=act)
+            assert len(ctx_g._graphs) == 1
+            monkeypatch.setenv("GPK_GRAPH", "0")
+            cd, idd = ctx_d.counts(pos, active=act)
+            live = act.astype(bool)
+            np.testing.assert_array_equal(cg[live], cd[live])
+            np.testing.assert_array_equal(ig[live], idd[live])
+        assert len(ctx_d._graphs) == 0
+    finally:
+        engine.set_precision("auto")
