@@ -10,6 +10,8 @@
 #include "../../include/gpk.h"
 #include "gpk_common.cuh"
 
+#include <cstdlib>
+
 namespace gpk {
 
 static std::mutex g_err_mu;

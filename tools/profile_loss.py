@@ -15,7 +15,12 @@ if os.environ.get("GPK_GROUPS"):
     _lib.check(_lib.load().gpk_set_groups(int(os.environ["GPK_GROUPS"])), "gpk_set_groups")
 ctx = engine.LossContext(x, y, e, s)
 dpos = engine.to_dev(pos); dact = torch.ones(P, dtype=torch.uint8, device="cuda")
+counts, info = ctx.counts_device(dpos, dact, P)
+torch.cuda.synchronize()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record()
 for _ in range(reps):
     counts, info = ctx.counts_device(dpos, dact, P)
+e1.record()
 torch.cuda.synchronize()
-print("ok", int(counts.sum().item()), int(info.abs().sum().item()))
+print("ok", int(counts.sum().item()), int(info.abs().sum().item()), f"{e0.elapsed_time(e1) / reps:.2f} ms per swarm evaluation")
