@@ -42,14 +42,13 @@ def algorithmic_flops_per_eval(n):
 
 
 def make_problem(seed=0):
-    from oracle import gp_oracle as orc          # synthetic-data generator only
-    x, y, e = orc.synthetic_problem(WORKLOAD["n_points"], WORKLOAD["dims"], seed)
-    return x, y, e
+    from gaussian_process_b200 import synthetic            # the measured arm never imports oracle/
+    return synthetic.problem(WORKLOAD["n_points"], WORKLOAD["dims"], seed)
 
 
 def make_particles(x, p, seed):
-    from oracle import gp_oracle as orc
-    return orc.synthetic_particles(x, p, seed)
+    from gaussian_process_b200 import synthetic
+    return synthetic.particles(x, p, seed)
 
 
 # --------------------------------------------------------------------------------------- clocks
@@ -250,10 +249,10 @@ def aux_measurements(torch, engine):
     """The other two quantities BASELINE.json's metric names, on one GPU: grid points/s of the predictive mean/sd
     (C3: N=4096, d=3, 100^3 grid) and rows/s of the probability surface (16 experiments with gaps), each device-resident
     and end to end through the public call with host arrays."""
-    from oracle import gp_oracle as orc               # synthetic data generators only
+    from gaussian_process_b200 import synthetic
     out = {}
     N, d, M = WORKLOAD["n_points"], WORKLOAD["dims"], 100 ** 3
-    x, y, e = orc.synthetic_problem(N, d, 1)
+    x, y, e = synthetic.problem(N, d, 1)
     ls = np.full(d, 0.25)
     xfit = np.random.default_rng(0).random((d, M))
     engine.gp(x, y, e, xfit[:, :20000], ls)                                   # warm-up (workspaces, module load)
@@ -275,7 +274,7 @@ def aux_measurements(torch, engine):
                            "precision": {0: "fp64", 1: "emu", 2: "emu28"}[fit.mode], "sd_checksum": float(sd.sum())}
     del grid, fit
     R, E = 1 << 22, 16
-    t = orc.synthetic_surface_table(1 << 18, E, seed=3)
+    t = synthetic.surface_table(1 << 18, E, seed=3)
     table = np.tile(t, (R // t.shape[0], 1))
     engine.prob_surface(table[:1 << 16])
     t0 = time.perf_counter()

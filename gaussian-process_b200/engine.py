@@ -297,6 +297,7 @@ class GPFit:
         mu = torch.empty(m, dtype=torch.float64, device=dev)
         sd = torch.empty(m, dtype=torch.float64, device=dev)
         chunk = int(max(NB, min(chunk, -(-m // NB) * NB)))
+        _apply_precision(self.mode)                 # process-wide switch: predict in the mode this fit was made in
         if self.state is not None:
             ws = workspace(self.lib.gpk_predict_emu_workspace_bytes(self.n, chunk), "predict")
             st = self.lib.gpk_predict_emu(self.state.data_ptr(), self.alpha.data_ptr(), self.xs.data_ptr(),

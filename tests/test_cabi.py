@@ -41,6 +41,6 @@ def test_no_oracle_import_in_product():
     pkg = os.path.join(ROOT, "gaussian-process_b200")
     for dirpath, _dirs, files in os.walk(pkg):
         for f in files:
-            if f.endswith((".py", ".cu", ".cuh", ".h")):
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in src.replace("no CPU fallback", ""), f

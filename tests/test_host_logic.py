@@ -77,3 +77,16 @@ def test_pso_host_loop_reproduces_reference_trace(name, capsys):
     np.testing.assert_allclose(pos, g["positions"], rtol=1e-9, atol=1e-12)
     np.testing.assert_allclose(best, g["best"], rtol=1e-9)
     assert out == str(g["stdout"])
+
+
+def test_synthetic_generators_equal_the_oracles():
+    """bench.py's measured arm generates its workload without importing oracle/: same data, value for value."""
+    from oracle import gp_oracle as orc
+    from gaussian_process_b200 import synthetic
+    for n, d, seed in ((40, 2, 0), (300, 3, 1), (64, 1, 5)):
+        for a, b in zip(synthetic.problem(n, d, seed), orc.synthetic_problem(n, d, seed)):
+            np.testing.assert_array_equal(a, b)
+        x = orc.synthetic_problem(n, d, seed)[0]
+        for a, b in zip(synthetic.particles(x, 7, seed), orc.synthetic_particles(x, 7, seed)):
+            np.testing.assert_array_equal(a, b)
+    np.testing.assert_array_equal(synthetic.surface_table(500, 4, seed=3), orc.synthetic_surface_table(500, 4, seed=3))

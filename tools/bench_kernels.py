@@ -3,7 +3,7 @@
 import json, os, sys, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
 import numpy as np, torch
-from oracle import gp_oracle as orc               # synthetic data generators only
+from gaussian_process_b200 import synthetic
 from gaussian_process_b200 import engine, _lib
 
 HBM = 6533.2   # GB/s, MEASURED_PEAKS.json
@@ -23,8 +23,8 @@ def timed(fn, reps=3, warm=1):
 def cov():
     lib = _lib.load()
     n, d, p = 4096, 3, 64
-    x, y, e = orc.synthetic_problem(n, d, 0)
-    pos, lo, hi = orc.synthetic_particles(x, p, 0)
+    x, y, e = synthetic.problem(n, d, 0)
+    pos, lo, hi = synthetic.particles(x, p, 0)
     dx, de, dls = engine.to_dev(x), engine.to_dev(e), engine.to_dev(pos)
     out = torch.empty((p, n, n), dtype=torch.float64, device="cuda")
     st = torch.cuda.current_stream().cuda_stream
@@ -37,7 +37,7 @@ def cov():
 
 
 def predict(n, d, m, label):
-    x, y, e = orc.synthetic_problem(n, d, 1)
+    x, y, e = synthetic.problem(n, d, 1)
     ls = np.full(d, 0.25)
     t0 = time.perf_counter(); fit = engine.GPFit(x, y, e, ls); torch.cuda.synchronize(); fit_s = time.perf_counter() - t0
     ms_fit = timed(lambda: engine.GPFit(x, y, e, ls), reps=2, warm=0)
@@ -52,7 +52,7 @@ def predict(n, d, m, label):
 
 def surface(r, e_):
     lib = _lib.load()
-    t = orc.synthetic_surface_table(min(r, 1 << 18), e_, seed=3)
+    t = synthetic.surface_table(min(r, 1 << 18), e_, seed=3)
     reps_ = -(-r // t.shape[0])
     dt = engine.to_dev(t).repeat(reps_, 1)[:r].contiguous()
     y = torch.empty((r, 100), dtype=torch.float64, device="cuda"); p = torch.empty_like(y)

@@ -2,16 +2,16 @@
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
 import numpy as np, torch
-from oracle import gp_oracle as orc
+from gaussian_process_b200 import synthetic
 from gaussian_process_b200 import engine, pso
 
 s, ex = pso.sigma_grid()
 for n, d in ((256, 2), (512, 2), (1024, 2), (2048, 3), (4096, 3), (8192, 2)):
-    x, y, e = orc.synthetic_problem(n, d, 0)
+    x, y, e = synthetic.problem(n, d, 0)
     for p in (40, 64, 256):
         if n >= 8192 and p > 64:
             continue
-        pos, lo, hi = orc.synthetic_particles(x, p, 0)
+        pos, lo, hi = synthetic.particles(x, p, 0)
         row = []
         for mode in ("fp64", "emu"):
             engine.set_precision(mode)

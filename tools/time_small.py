@@ -1,10 +1,10 @@
 import sys, time, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
-from oracle import gp_oracle as orc
+from gaussian_process_b200 import synthetic
 from gaussian_process_b200 import engine, pso
 for n, d in ((21, 2), (100, 2), (128, 3)):
-    x, y, e = orc.synthetic_problem(n, d, 0); pos, lo, hi = orc.synthetic_particles(x, 40, 0); s, ex = pso.sigma_grid()
+    x, y, e = synthetic.problem(n, d, 0); pos, lo, hi = synthetic.particles(x, 40, 0); s, ex = pso.sigma_grid()
     sw = pso.SwarmLoss(x, y, e, s, ex, lo, hi)
     for _ in range(5): sw(pos)
     t = time.perf_counter()
