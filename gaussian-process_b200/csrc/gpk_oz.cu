@@ -283,16 +283,21 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
         const double drs = (t.dig_rs ? t.dig_rs[row] : 1.0) * t.dig_rconst * 0x1p55;
         const double* dcs = t.dig_cs ? t.dig_cs + ch * 32 : nullptr;
         uint8_t* drow = t.dig ? t.dig + (size_t)ch * OZ_CHUNK + (row >> 3) * 256 + (row & 7) * 16 : nullptr;
-        double2 cold[16];
+        // phase A (TMEM busy): accumulators -> FP64 output values in registers; phase B (after the accumulators are
+        // released to the MMA thread): global stores and digit emission, overlapping the next tile's MMAs
+        double val[32];
         if (EPI == OZ_SUB) {                     // the tile is final input data: fetch it while the MMAs run
 #pragma unroll
-            for (int j = 0; j < 16; ++j) cold[j] = reinterpret_cast<const double2*>(crow)[j];
+            for (int j = 0; j < 16; ++j) {
+                const double2 c2 = reinterpret_cast<const double2*>(crow)[j];
+                val[2 * j] = c2.x;
+                val[2 * j + 1] = c2.y;
+            }
         }
         mbar_wait(accbar, it & 1u);
         tc_fence_after();
         ++it;
         const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + ch * 32;
-        double sqv[EPI == OZ_SUMSQ ? 32 : 1];
 #pragma unroll
         for (int cc = 0; cc < 32; cc += 8) {
             uint32_t a[NG][8];
@@ -305,7 +310,6 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
 #pragma unroll
                     for (int j = 0; j < 8; ++j) t.dbg[(g * 128 + row) * OZ_TILE_N + ch * 32 + cc + j] = (int)a[g][j];
             }
-            double v[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
                 const long long hi = ((long long)(int)a[0][j] << 16) + ((long long)(int)a[1][j] << 8) + (long long)(int)a[2][j];
@@ -314,55 +318,42 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
                 if (NG == 8) lo += (long long)(int)a[NG - 1][j];
                 double x = fma(ll2d_exact(mid), 0x1p-40, ll2d_exact(lo) * 0x1p-56);
                 x = fma(ll2d_exact(hi), 0x1p-16, x);
-                v[j] = x * (rs * (sbp ? sbp[cc + j] : 1.0));
-            }
-            if (EPI == OZ_SUMSQ) {
-#pragma unroll
-                for (int j = 0; j < 8; ++j) sqv[cc + j] = v[j] * v[j];
-                continue;
-            }
-            double2* cp = reinterpret_cast<double2*>(crow + cc);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                double2 o;
-                if (EPI == OZ_SUB) {
-                    o = cold[cc / 2 + j];
-                    o.x -= v[2 * j];
-                    o.y -= v[2 * j + 1];
-                } else if (EPI == OZ_STORE) {
-                    o.x = v[2 * j];
-                    o.y = v[2 * j + 1];
-                } else {
-                    o.x = -v[2 * j];
-                    o.y = -v[2 * j + 1];
-                }
-                cp[j] = o;
-                v[2 * j] = o.x;
-                v[2 * j + 1] = o.y;
-            }
-            if (drow) {                          // digits of the stored values, 8 consecutive k of one record row
-                uint32_t lo[8], hi[8];
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const double u = v[j] * (drs * (dcs ? dcs[cc + j] : 1.0));
-                    const long long w = (__double2ll_rn(u) + OZ_BIAS) ^ OZ_BIAS;
-                    lo[j] = (uint32_t)w;
-                    hi[j] = (uint32_t)(w >> 32);
-                }
-                uint8_t* d = drow + (cc >> 4) * 128 + (cc & 15);
-#pragma unroll
-                for (int s = 0; s < OZ_NS; ++s) {
-                    const int bytepos = 6 - s;
-                    const uint32_t* w = (bytepos >= 4) ? hi : lo;
-                    uint2 o2;
-                    o2.x = pack_digit(w, bytepos & 3);
-                    o2.y = pack_digit(w + 4, bytepos & 3);
-                    *reinterpret_cast<uint2*>(d + s * OZ_DIGIT) = o2;
-                }
+                const double v = x * (rs * (sbp ? sbp[cc + j] : 1.0));
+                if (EPI == OZ_SUB) val[cc + j] -= v;
+                else if (EPI == OZ_STORE) val[cc + j] = v;
+                else if (EPI == OZ_STORE_NEG) val[cc + j] = -v;
+                else val[cc + j] = v * v;
             }
         }
         tc_fence_before();
         mbar_arrive(freebar);                    // TMEM may be overwritten
+        if (EPI != OZ_SUMSQ) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) reinterpret_cast<double2*>(crow)[j] = make_double2(val[2 * j], val[2 * j + 1]);
+            if (drow) {                          // digits of the stored values, 8 consecutive k of one record row at a time
+#pragma unroll
+                for (int cc = 0; cc < 32; cc += 8) {
+                    uint32_t lo[8], hi[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const double u = val[cc + j] * (drs * (dcs ? dcs[cc + j] : 1.0));
+                        const long long w = (__double2ll_rn(u) + OZ_BIAS) ^ OZ_BIAS;
+                        lo[j] = (uint32_t)w;
+                        hi[j] = (uint32_t)(w >> 32);
+                    }
+                    uint8_t* d = drow + (cc >> 4) * 128 + (cc & 15);
+#pragma unroll
+                    for (int s = 0; s < OZ_NS; ++s) {
+                        const int bytepos = 6 - s;
+                        const uint32_t* w = (bytepos >= 4) ? hi : lo;
+                        uint2 o2;
+                        o2.x = pack_digit(w, bytepos & 3);
+                        o2.y = pack_digit(w + 4, bytepos & 3);
+                        *reinterpret_cast<uint2*>(d + s * OZ_DIGIT) = o2;
+                    }
+                }
+            }
+        }
         if (EPI == OZ_SUMSQ) {
             // butterfly: 32 columns x 32 rows (lanes) -> lane l holds the sum over the quadrant's rows of column l
 #pragma unroll
@@ -370,12 +361,12 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
                 const bool up = (lane & step) != 0;
 #pragma unroll
                 for (int i = 0; i < step; ++i) {
-                    const double send = up ? sqv[i] : sqv[i + step];
-                    const double keep = up ? sqv[i + step] : sqv[i];
-                    sqv[i] = keep + __shfl_xor_sync(0xffffffffu, send, step);
+                    const double send = up ? val[i] : val[i + step];
+                    const double keep = up ? val[i + step] : val[i];
+                    val[i] = keep + __shfl_xor_sync(0xffffffffu, send, step);
                 }
             }
-            t.red[(size_t)q * t.red_ld + ch * 32 + lane] = sqv[0];
+            t.red[(size_t)q * t.red_ld + ch * 32 + lane] = val[0];
         }
         }
     }
