@@ -97,7 +97,7 @@ BlockedLayout blocked_layout(int P, int N, int d, int emulated) {
         L.oz_slices = take((size_t)P * oz_slice_bytes(L.Np));
         L.oz_mt = take((size_t)P * oz_mt_bytes(L.Np));
         L.oz_rows = take((size_t)4 * Np * 8);
-        L.oz_mtsc = take((size_t)2 * P * NB * 8);
+        L.oz_mtsc = take((size_t)3 * P * NB * 8);
         L.oz_sdig = take((size_t)P * oz_panel_bytes(L.Np));
         L.oz_ddig = take((size_t)P * oz_ddig_bytes(L.Np));
         L.oz_dsc = take((size_t)P * T * 2 * NB * 8);
@@ -118,6 +118,8 @@ struct OzBuffers {
     mutable int cnt_used = 0;
     int* next() const { return cnt + cnt_used++; }
     double *rowsig = nullptr, *rowinv = nullptr, *gam = nullptr, *gaminv = nullptr, *mtsig = nullptr, *mtinv = nullptr;
+    unsigned long long* mtmax = nullptr;      // row maxima of the phase-2 panel (bit patterns of non-negative doubles)
+    size_t mtmax_bytes = 0;
 };
 
 static OzBuffers oz_buffers(char* ws, const BlockedLayout& L) {
@@ -129,6 +131,8 @@ static OzBuffers oz_buffers(char* ws, const BlockedLayout& L) {
     o.rowsig = r; o.rowinv = r + L.Np; o.gam = r + 2 * (size_t)L.Np; o.gaminv = r + 3 * (size_t)L.Np;
     double* m = (double*)(ws + L.oz_mtsc);
     o.mtsig = m; o.mtinv = m + (size_t)L.P * NB;
+    o.mtmax = (unsigned long long*)(m + 2 * (size_t)L.P * NB);
+    o.mtmax_bytes = (size_t)L.P * NB * 8;
     o.sdig = (uint8_t*)(ws + L.oz_sdig);
     o.ddig = (uint8_t*)(ws + L.oz_ddig);
     o.dsc = (double*)(ws + L.oz_dsc);
@@ -166,11 +170,14 @@ static int factor_phase(double* mat, int Np, int T, int P, double* dinv, double*
 // Blocked triangular inverse (phase 2), in place: L (with D_I already in the diagonal blocks) -> W = L^-1.
 static int inverse_phase(double* mat, int Np, int T, int P, const double* dinvT, double* mt,
                          const unsigned char* active, const OzBuffers& oz, cudaStream_t st) {
-    if (oz.slices && launch_oz_slice_w(mat, Np, T, 0, 1, P, oz.gam, oz.slices, active, st)) return 1;
+    if (oz.slices) {
+        if (cudaMemsetAsync(oz.mtmax, 0, oz.mtmax_bytes, st) != cudaSuccess) { set_error("memset of the panel maxima failed"); return 1; }
+        if (launch_oz_slice_w(mat, Np, T, 0, 1, P, oz.gam, oz.slices, active, st)) return 1;
+    }
     for (int J = T - 2; J >= 0; --J) {
         if (oz.slices) {
-            if (launch_oz_invp(mt, Np, T, J, P, oz.ddig, oz.dsc, oz.slices, oz.rowsig, oz.next(), active, st)) return 1;
-            if (launch_oz_mt(mt, Np, T, J, P, oz.gaminv, oz.mtsig, oz.mtinv, oz.mtslices, active, st)) return 1;
+            if (launch_oz_invp(mt, Np, T, J, P, oz.ddig, oz.dsc, oz.slices, oz.rowsig, oz.mtmax, oz.gaminv, oz.next(), active, st)) return 1;
+            if (launch_oz_mt(mt, Np, T, J, P, oz.gaminv, oz.mtmax, oz.mtsig, oz.mtinv, oz.mtslices, active, st)) return 1;
             if (launch_oz_invu(mat, Np, T, J, P, oz.slices, oz.mtslices, oz.mtsig, oz.gam, 1, oz.next(), active, st)) return 1;
         } else {
             if (launch_inv_panel(mat, Np, T, J, P, dinvT, mt, active, st)) return 1;
@@ -330,7 +337,7 @@ size_t gpk_fit_workspace_bytes(int N, int d) {
     const size_t Np = round_up(N, NB), T = Np / NB;
     size_t b = 2 * align256(T * NB * NB * 8) + align256(NB * Np * 8) + 2 * align256(Np * 8);
     if (g_precision)
-        b += align256(oz_slice_bytes((int)Np)) + align256(oz_mt_bytes((int)Np)) + align256(4 * Np * 8) + align256(2 * NB * 8) +
+        b += align256(oz_slice_bytes((int)Np)) + align256(oz_mt_bytes((int)Np)) + align256(4 * Np * 8) + align256(3 * NB * 8) +
              align256(oz_panel_bytes((int)Np)) + align256(oz_ddig_bytes((int)Np)) + align256(T * 2 * NB * 8) +
              align256((4 * T + 8) * sizeof(int));
     return b;
@@ -357,7 +364,8 @@ int gpk_fit(const double* X, const double* y, const double* e, const double* ls,
         oz.mtslices = (uint8_t*)(ws + off); off += align256(oz_mt_bytes(Np));
         double* r = (double*)(ws + off); off += align256((size_t)4 * Np * 8);
         oz.rowsig = r; oz.rowinv = r + Np; oz.gam = r + 2 * (size_t)Np; oz.gaminv = r + 3 * (size_t)Np;
-        oz.mtsig = (double*)(ws + off); oz.mtinv = oz.mtsig + NB; off += align256((size_t)2 * NB * 8);
+        oz.mtsig = (double*)(ws + off); oz.mtinv = oz.mtsig + NB; oz.mtmax = (unsigned long long*)(oz.mtsig + 2 * NB);
+        oz.mtmax_bytes = (size_t)NB * 8; off += align256((size_t)3 * NB * 8);
         oz.sdig = (uint8_t*)(ws + off); off += align256(oz_panel_bytes(Np));
         oz.ddig = (uint8_t*)(ws + off); off += align256(oz_ddig_bytes(Np));
         oz.dsc = (double*)(ws + off); off += align256((size_t)T * 2 * NB * 8);

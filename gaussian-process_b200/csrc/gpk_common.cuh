@@ -35,7 +35,7 @@ struct BlockedLayout {
     size_t oz_slices;  // [P] digit records of L (phase 1) then W gamma (phase 2), oz_slice_bytes(Np) each
     size_t oz_mt;      // [P] digit records of the phase-2 panel, oz_mt_bytes(Np) each
     size_t oz_rows;    // [4][Np]   rowsig, rowinv, gamma, 1/gamma (particle independent)
-    size_t oz_mtsc;    // [2][P][NB] row scales of the phase-2 panel and their inverses
+    size_t oz_mtsc;    // [3][P][NB] row scales of the phase-2 panel, their inverses, and the row maxima they come from
     size_t oz_sdig;    // [P] digits of the Schur-complement block column (TRSM operand), oz_panel_bytes(Np) each
     size_t oz_ddig;    // [P] digits of D_J and D_J^T for every J, oz_ddig_bytes(Np) each
     size_t oz_dsc;     // [P][T][2][NB] their measured row scales
@@ -87,13 +87,14 @@ int launch_oz_trsm(double* mat, int Np, int T, int J, int P, const uint8_t* sdig
                    const double* rowsig, const double* rowinv, uint8_t* slices, int* counter, const unsigned char* active,
                    cudaStream_t st);
 int launch_oz_invp(double* mt, int Np, int T, int J, int P, const uint8_t* ddig, const double* dsc, const uint8_t* slices,
-                   const double* rowsig, int* counter, const unsigned char* active, cudaStream_t st);
+                   const double* rowsig, unsigned long long* mtmax, const double* gaminv, int* counter,
+                   const unsigned char* active, cudaStream_t st);
 int launch_oz_slice_l(const double* mat, int Np, int T, int J, int P, const double* rowinv, uint8_t* slices,
                       const unsigned char* active, cudaStream_t st);
 int launch_oz_slice_w(const double* mat, int Np, int T, int J, int diag, int P, const double* gam, uint8_t* slices,
                       const unsigned char* active, cudaStream_t st);
-int launch_oz_mt(const double* mt, int Np, int T, int J, int P, const double* gaminv, double* mtsig, double* mtinv,
-                 uint8_t* mtslices, const unsigned char* active, cudaStream_t st);
+int launch_oz_mt(const double* mt, int Np, int T, int J, int P, const double* gaminv, unsigned long long* mtmax,
+                 double* mtsig, double* mtinv, uint8_t* mtslices, const unsigned char* active, cudaStream_t st);
 int launch_oz_invu(double* mat, int Np, int T, int J, int P, uint8_t* slices, const uint8_t* mtslices,
                    const double* mtsig, const double* gam, int emit, int* counter, const unsigned char* active,
                    cudaStream_t st);

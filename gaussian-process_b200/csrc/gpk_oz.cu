@@ -136,6 +136,10 @@ struct OzTile {
     const double* dig_rs;  // 128 row multipliers or nullptr
     double dig_rconst;     // u = value * dig_rs[row] * dig_rconst * dig_cs[col], |u| <= 0.98
     const double* dig_cs;  // 64 column multipliers or nullptr
+    // optional row maxima of |output * amax_cs[col]| (the row scale of the next slicing pass): atomicMax on the bit
+    // pattern of the non-negative double, amax[row]
+    unsigned long long* amax;
+    const double* amax_cs;
     // OZ_SUMSQ only: column sums of squares over each 32-row quadrant, red[q * red_ld + col] (no FP64 tile is stored)
     double* red;
     size_t red_ld;
@@ -330,6 +334,12 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
         if (EPI != OZ_SUMSQ) {
 #pragma unroll
             for (int j = 0; j < 16; ++j) reinterpret_cast<double2*>(crow)[j] = make_double2(val[2 * j], val[2 * j + 1]);
+            if (t.amax) {
+                double m = 0.0;
+#pragma unroll
+                for (int j = 0; j < 32; ++j) m = fmax(m, fabs(val[j] * t.amax_cs[ch * 32 + j]));
+                atomicMax(t.amax + row, (unsigned long long)__double_as_longlong(m));
+            }
             if (drow) {                          // digits of the stored values, 8 consecutive k of one record row at a time
 #pragma unroll
                 for (int cc = 0; cc < 32; cc += 8) {
@@ -388,6 +398,7 @@ __global__ void __launch_bounds__(OZ_THREADS, 1) k_oz(const F f, int ntiles, int
 __device__ __forceinline__ void oz_no_digits(OzTile& t) {
     t.dbg = nullptr;
     t.dig = nullptr; t.dig_rs = nullptr; t.dig_rconst = 1.0; t.dig_cs = nullptr;
+    t.amax = nullptr; t.amax_cs = nullptr;
     t.red = nullptr; t.red_ld = 0;
 }
 
@@ -569,24 +580,18 @@ k_oz_slice_w(const double* __restrict__ mat, int Np, int J, int diag, const doub
                   slices + (size_t)p * slice_stride + ((size_t)I * kch + 4 * Jc) * OZ_CHUNK);
 }
 
-// row scales of the phase-2 panel: sigma_n = 2^(ilogb(max_k |Mt[n][k] / gamma_k|) + 2), k >= (J+1) NB
-__global__ void __launch_bounds__(256)
-k_oz_mt_scale(const double* __restrict__ mt, int Np, int J, const double* __restrict__ gaminv,
-              double* __restrict__ mtsig, double* __restrict__ mtinv, const unsigned char* __restrict__ active) {
-    const int p = blockIdx.y;
+// row scales of the phase-2 panel from the row maxima max_k |Mt[n][k] / gamma_k| the panel GEMM's epilogue collected;
+// the maxima are reset for the next block column
+__global__ void __launch_bounds__(NB)
+k_oz_mt_scale(unsigned long long* __restrict__ mtmax, double* __restrict__ mtsig, double* __restrict__ mtinv,
+              const unsigned char* __restrict__ active) {
+    const int p = blockIdx.x;
     if (active && !active[p]) return;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n = blockIdx.x * 8 + warp;
-    const double* row = mt + (size_t)p * NB * Np + (size_t)n * Np;
-    double m = 0.0;
-    for (int k = (J + 1) * NB + lane; k < Np; k += 32) m = fmax(m, fabs(row[k] * gaminv[k]));
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
-    if (lane == 0) {
-        const double sig = oz_scale_for(m);
-        mtsig[(size_t)p * NB + n] = sig;
-        mtinv[(size_t)p * NB + n] = 1.0 / sig;
-    }
+    const size_t i = (size_t)p * NB + threadIdx.x;
+    const double sig = oz_scale_for(__longlong_as_double((long long)mtmax[i]));
+    mtmax[i] = 0ull;
+    mtsig[i] = sig;
+    mtinv[i] = 1.0 / sig;
 }
 
 // digits of Mt / gamma: blockIdx.x -> R = J + 1 + bx (128 columns of the panel)
@@ -680,6 +685,7 @@ struct OzInvpTiles {
     const uint8_t* ddig; const double* dsc;
     const uint8_t* slices; size_t slice_stride;
     const double* rowsig;
+    unsigned long long* mtmax; const double* gaminv;      // row maxima of Mt / gamma for the panel's row scales
     const unsigned char* active;
     __device__ __forceinline__ bool make(int tile, OzTile& t) const {
         const int p = tile / nx, bx = tile - p * nx;
@@ -695,6 +701,8 @@ struct OzInvpTiles {
         t.sa_const = 1.0;
         t.sb = rowsig + R * NB + h * OZ_TILE_N;
         oz_no_digits(t);
+        t.amax = mtmax + (size_t)p * NB;
+        t.amax_cs = gaminv + R * NB + h * OZ_TILE_N;
         return true;
     }
 };
@@ -945,9 +953,10 @@ int launch_oz_trsm(double* mat, int Np, int T, int J, int P, const uint8_t* sdig
 }
 
 int launch_oz_invp(double* mt, int Np, int T, int J, int P, const uint8_t* ddig, const double* dsc, const uint8_t* slices,
-                   const double* rowsig, int* counter, const unsigned char* active, cudaStream_t st) {
+                   const double* rowsig, unsigned long long* mtmax, const double* gaminv, int* counter,
+                   const unsigned char* active, cudaStream_t st) {
     if (J >= T - 1) return 0;
-    const OzInvpTiles f{mt, Np, T, J, 2 * (T - 1 - J), ddig, dsc, slices, oz_slice_bytes(Np), rowsig, active};
+    const OzInvpTiles f{mt, Np, T, J, 2 * (T - 1 - J), ddig, dsc, slices, oz_slice_bytes(Np), rowsig, mtmax, gaminv, active};
     if (oz_launch<OZ_STORE>(f, f.nx * P, counter, st)) return 1;
     return check_launch("k_oz_invp");
 }
@@ -967,10 +976,10 @@ int launch_oz_slice_w(const double* mat, int Np, int T, int J, int diag, int P, 
     return check_launch("k_oz_slice_w");
 }
 
-int launch_oz_mt(const double* mt, int Np, int T, int J, int P, const double* gaminv, double* mtsig, double* mtinv,
-                 uint8_t* mtslices, const unsigned char* active, cudaStream_t st) {
+int launch_oz_mt(const double* mt, int Np, int T, int J, int P, const double* gaminv, unsigned long long* mtmax,
+                 double* mtsig, double* mtinv, uint8_t* mtslices, const unsigned char* active, cudaStream_t st) {
     if (J >= T - 1) return 0;
-    k_oz_mt_scale<<<dim3(NB / 8, P), 256, 0, st>>>(mt, Np, J, gaminv, mtsig, mtinv, active);
+    k_oz_mt_scale<<<P, NB, 0, st>>>(mtmax, mtsig, mtinv, active);
     if (check_launch("k_oz_mt_scale")) return 1;
     k_oz_slice_mt<<<dim3(T - 1 - J, P), 256, 0, st>>>(mt, Np, J, gaminv, mtinv, mtslices, oz_mt_bytes(Np), active);
     return check_launch("k_oz_slice_mt");
