@@ -106,6 +106,14 @@ __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory"); }
 
+// 256-bit global accesses (32-byte aligned): one full sector per lane
+__device__ __forceinline__ void stg_f64x4(double* p, double a, double b, double c, double d) {
+    asm volatile("st.global.v4.f64 [%0], {%1, %2, %3, %4};\n" ::"l"(p), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
+}
+__device__ __forceinline__ void ldg_f64x4(const double* p, double& a, double& b, double& c, double& d) {
+    asm volatile("ld.global.v4.f64 {%0, %1, %2, %3}, [%4];\n" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p) : "memory");
+}
+
 // exact int64 -> double for |v| < 2^51 without the slow I2F path
 __device__ __forceinline__ double ll2d_exact(long long v) {
     return __longlong_as_double(0x4338000000000000LL + v) - 6755399441055744.0;
@@ -292,11 +300,7 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
         double val[32];
         if (EPI == OZ_SUB) {                     // the tile is final input data: fetch it while the MMAs run
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                const double2 c2 = reinterpret_cast<const double2*>(crow)[j];
-                val[2 * j] = c2.x;
-                val[2 * j + 1] = c2.y;
-            }
+            for (int j = 0; j < 8; ++j) ldg_f64x4(crow + 4 * j, val[4 * j], val[4 * j + 1], val[4 * j + 2], val[4 * j + 3]);
         }
         mbar_wait(accbar, it & 1u);
         tc_fence_after();
@@ -333,33 +337,35 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
         mbar_arrive(freebar);                    // TMEM may be overwritten
         if (EPI != OZ_SUMSQ) {
 #pragma unroll
-            for (int j = 0; j < 16; ++j) reinterpret_cast<double2*>(crow)[j] = make_double2(val[2 * j], val[2 * j + 1]);
+            for (int j = 0; j < 8; ++j) stg_f64x4(crow + 4 * j, val[4 * j], val[4 * j + 1], val[4 * j + 2], val[4 * j + 3]);
             if (t.amax) {
                 double m = 0.0;
 #pragma unroll
                 for (int j = 0; j < 32; ++j) m = fmax(m, fabs(val[j] * t.amax_cs[ch * 32 + j]));
                 atomicMax(t.amax + row, (unsigned long long)__double_as_longlong(m));
             }
-            if (drow) {                          // digits of the stored values, 8 consecutive k of one record row at a time
+            if (drow) {                          // digits of the stored values: one 16-byte unit (16 consecutive k) per store
 #pragma unroll
-                for (int cc = 0; cc < 32; cc += 8) {
-                    uint32_t lo[8], hi[8];
+                for (int cc = 0; cc < 32; cc += 16) {
+                    uint32_t lo[16], hi[16];
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
+                    for (int j = 0; j < 16; ++j) {
                         const double u = val[cc + j] * (drs * (dcs ? dcs[cc + j] : 1.0));
                         const long long w = (__double2ll_rn(u) + OZ_BIAS) ^ OZ_BIAS;
                         lo[j] = (uint32_t)w;
                         hi[j] = (uint32_t)(w >> 32);
                     }
-                    uint8_t* d = drow + (cc >> 4) * 128 + (cc & 15);
+                    uint8_t* d = drow + (cc >> 4) * 128;
 #pragma unroll
                     for (int s = 0; s < OZ_NS; ++s) {
                         const int bytepos = 6 - s;
                         const uint32_t* w = (bytepos >= 4) ? hi : lo;
-                        uint2 o2;
-                        o2.x = pack_digit(w, bytepos & 3);
-                        o2.y = pack_digit(w + 4, bytepos & 3);
-                        *reinterpret_cast<uint2*>(d + s * OZ_DIGIT) = o2;
+                        uint4 o4;
+                        o4.x = pack_digit(w, bytepos & 3);
+                        o4.y = pack_digit(w + 4, bytepos & 3);
+                        o4.z = pack_digit(w + 8, bytepos & 3);
+                        o4.w = pack_digit(w + 12, bytepos & 3);
+                        *reinterpret_cast<uint4*>(d + s * OZ_DIGIT) = o4;
                     }
                 }
             }
