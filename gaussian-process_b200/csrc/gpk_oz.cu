@@ -501,23 +501,21 @@ __device__ __forceinline__ void oz_slice_tile(const double* __restrict__ src, in
     for (int unit = threadIdx.x; unit < 1024; unit += blockDim.x) {
         const int kcl = unit >> 8, rg = (unit >> 4) & 15, kg = (unit >> 3) & 1, r8 = unit & 7;
         const int row = rg * 8 + r8, col0 = kcl * 32 + kg * 16;
-        const double2* s2 = reinterpret_cast<const double2*>(src + (size_t)row * ld + col0);
+        const double* sp = src + (size_t)row * ld + col0;
         const double rsv = (rs ? rs[row] : 1.0) * rconst * 0x1p55;
         uint32_t lo[16], hi[16];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const double2 x = s2[j];
-            double u0 = x.x * rsv, u1 = x.y * rsv;
-            if (cs) {
-                u0 *= cs[col0 + 2 * j];
-                u1 *= cs[col0 + 2 * j + 1];
+        for (int j = 0; j < 4; ++j) {
+            double x[4];
+            ldg_f64x4(sp + 4 * j, x[0], x[1], x[2], x[3]);          // one full 32-byte sector per lane
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                double u = x[i] * rsv;
+                if (cs) u *= cs[col0 + 4 * j + i];
+                const long long v = (__double2ll_rn(u) + OZ_BIAS) ^ OZ_BIAS;
+                lo[4 * j + i] = (uint32_t)v;
+                hi[4 * j + i] = (uint32_t)(v >> 32);
             }
-            const long long v0 = (__double2ll_rn(u0) + OZ_BIAS) ^ OZ_BIAS;
-            const long long v1 = (__double2ll_rn(u1) + OZ_BIAS) ^ OZ_BIAS;
-            lo[2 * j] = (uint32_t)v0;
-            hi[2 * j] = (uint32_t)(v0 >> 32);
-            lo[2 * j + 1] = (uint32_t)v1;
-            hi[2 * j + 1] = (uint32_t)(v1 >> 32);
         }
         uint8_t* d = dst + (size_t)kcl * OZ_CHUNK + rg * 256 + kg * 128 + r8 * 16;
 #pragma unroll
