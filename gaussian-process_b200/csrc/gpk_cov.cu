@@ -42,6 +42,31 @@ int launch_scale_points(const double* X, const double* ls, int P, int N, int Np,
     return check_launch("k_scale_points");
 }
 
+// rows r = (threadIdx.x >> 7), +2, ... of tile (I, .) for column j: K_ij + delta_ij e_i^2, identity in the padding
+template <int D>
+__device__ __forceinline__ void cov_lower_rows(const double* __restrict__ xsp, const double* __restrict__ sqp,
+                                               const double* __restrict__ e, int N, int Np, int I, int j,
+                                               const double (*s_xi)[NB], const double* s_sqi, double* __restrict__ out) {
+    double xj[D];
+#pragma unroll
+    for (int dd = 0; dd < D; ++dd) xj[dd] = xsp[(size_t)dd * Np + j];
+    const double sqj = sqp[j];
+    for (int r = threadIdx.x >> 7; r < NB; r += 2) {
+        const int i = I * NB + r;
+        double v;
+        if (i < N && j < N) {
+            double dot = __dmul_rn(s_xi[0][r], xj[0]);
+#pragma unroll
+            for (int dd = 1; dd < D; ++dd) dot = fma(s_xi[dd][r], xj[dd], dot);
+            v = rbf_from_parts(s_sqi[r], sqj, dot);
+            if (i == j) { const double ee = e[i]; v = __dadd_rn(v, __dmul_rn(ee, ee)); }
+        } else {
+            v = (i == j) ? 1.0 : 0.0;
+        }
+        out[(size_t)i * Np + j] = v;
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Lower block triangle of K + diag(e^2) for every particle, written straight into the factorisation
 // buffer.  One CTA per 128x128 tile (I >= J); padding rows/cols become the identity.
@@ -71,25 +96,18 @@ __global__ void __launch_bounds__(256) k_cov_lower(const double* __restrict__ xs
 
     const int c = threadIdx.x & (NB - 1);
     const int j = J * NB + c;
-    double xj[MAX_D];
-#pragma unroll
-    for (int dd = 0; dd < MAX_D; ++dd) xj[dd] = (dd < d) ? xsp[(size_t)dd * Np + j] : 0.0;
-    const double sqj = sqp[j];
     double* out = mat + (size_t)p * Np * Np;
-    for (int r = threadIdx.x >> 7; r < NB; r += 2) {
-        const int i = I * NB + r;
-        double v;
-        if (i < N && j < N) {
-            double dot = __dmul_rn(s_xi[0][r], xj[0]);
-#pragma unroll
-            for (int dd = 1; dd < MAX_D; ++dd)
-                if (dd < d) dot = fma(s_xi[dd][r], xj[dd], dot);
-            v = rbf_from_parts(s_sqi[r], sqj, dot);
-            if (i == j) { const double ee = e[i]; v = __dadd_rn(v, __dmul_rn(ee, ee)); }
-        } else {
-            v = (i == j) ? 1.0 : 0.0;
-        }
-        out[(size_t)i * Np + j] = v;
+    // the dimension loop is unrolled for the actual d (a run-time bound costs MAX_D predicated load / FMA pairs per
+    // element in issue slots); same operations in the same order for every D
+    switch (d) {
+        case 1: cov_lower_rows<1>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out); break;
+        case 2: cov_lower_rows<2>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out); break;
+        case 3: cov_lower_rows<3>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out); break;
+        case 4: cov_lower_rows<4>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out); break;
+        case 5: cov_lower_rows<5>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out); break;
+        case 6: cov_lower_rows<6>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out); break;
+        case 7: cov_lower_rows<7>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out); break;
+        default: cov_lower_rows<8>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out); break;
     }
 }
 

@@ -795,25 +795,27 @@ constexpr int XC_WPTS = 2;
 constexpr int XC_PTS = 8 * XC_WPTS;
 constexpr int XC_PITCH = 33;
 constexpr int XC_ARR = 16 * XC_PITCH;       // doubles per staged array
+template <int D>       // D = number of dimensions, compile time: a run-time bound costs MAX_D predicated pairs per element
 __global__ void __launch_bounds__(256) k_oz_cross_cov(const double* __restrict__ xs, const double* __restrict__ sq,
                                                       const double* __restrict__ ls, const double* __restrict__ alpha,
-                                                      const double* __restrict__ ginv_s, int N, int Np, int d,
+                                                      const double* __restrict__ ginv_s, int N, int Np,
                                                       const double* __restrict__ Xfit, long long M, long long m0, int B,
                                                       int Bp, uint8_t* __restrict__ kdig, double* __restrict__ mu_out) {
+    constexpr int d = D;
     extern __shared__ __align__(16) double xc_sm[];      // [d + 3][16][33]: xs rows, sq, alpha, ginv_s
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int b0 = blockIdx.x * XC_PTS + warp * XC_WPTS;
     const int kch = Np / 32;
-    double xb[XC_WPTS][MAX_D], sqb[XC_WPTS], acc[XC_WPTS];
+    double xb[XC_WPTS][D], sqb[XC_WPTS], acc[XC_WPTS];
 #pragma unroll
     for (int q = 0; q < XC_WPTS; ++q) {
         const int b = b0 + q;
         sqb[q] = 0.0;
         acc[q] = 0.0;
 #pragma unroll
-        for (int dd = 0; dd < MAX_D; ++dd) {
+        for (int dd = 0; dd < D; ++dd) {
             xb[q][dd] = 0.0;
-            if (dd < d && b < B) {
+            if (b < B) {
                 xb[q][dd] = __ddiv_rn(Xfit[(size_t)dd * M + m0 + b], ls[dd]);
                 const double v2 = __dmul_rn(xb[q][dd], xb[q][dd]);
                 sqb[q] = (dd == 0) ? v2 : __dadd_rn(sqb[q], v2);
@@ -844,8 +846,7 @@ __global__ void __launch_bounds__(256) k_oz_cross_cov(const double* __restrict__
                 if (j0 + i < N && b < B) {
                     double dot = __dmul_rn(col[0], xb[q][0]);
 #pragma unroll
-                    for (int dd = 1; dd < MAX_D; ++dd)
-                        if (dd < d) dot = fma(col[dd * XC_ARR], xb[q][dd], dot);
+                    for (int dd = 1; dd < D; ++dd) dot = fma(col[dd * XC_ARR], xb[q][dd], dot);
                     v = oz_rbf(col[d * XC_ARR], sqb[q], dot);
                     acc[q] = fma(v, col[(d + 1) * XC_ARR], acc[q]);
                 }
@@ -1045,8 +1046,20 @@ int launch_oz_predict_chunk(const uint8_t* state, const double* xs, const double
     double* partial = (double*)(workspace + oz_align256((size_t)(Bp / NB) * (Np / 32) * OZ_CHUNK));
     int* counter = (int*)((uint8_t*)partial + oz_align256((size_t)4 * (Np / NB) * Bp * 8));
     if (cudaMemsetAsync(counter, 0, sizeof(int), st) != cudaSuccess) { set_error("oz counter memset failed"); return 1; }
-    k_oz_cross_cov<<<(Bp + XC_PTS - 1) / XC_PTS, 256, (size_t)(d + 3) * XC_ARR * sizeof(double), st>>>(
-        xs, sq, ls, alpha, ginv_s, N, Np, d, Xfit, M, m0, B, Bp, kdig, mu_out);
+    const dim3 xgrid((Bp + XC_PTS - 1) / XC_PTS);
+    const size_t xsmem = (size_t)(d + 3) * XC_ARR * sizeof(double);
+#define GPK_XCOV(D) k_oz_cross_cov<D><<<xgrid, 256, xsmem, st>>>(xs, sq, ls, alpha, ginv_s, N, Np, Xfit, M, m0, B, Bp, kdig, mu_out)
+    switch (d) {
+        case 1: GPK_XCOV(1); break;
+        case 2: GPK_XCOV(2); break;
+        case 3: GPK_XCOV(3); break;
+        case 4: GPK_XCOV(4); break;
+        case 5: GPK_XCOV(5); break;
+        case 6: GPK_XCOV(6); break;
+        case 7: GPK_XCOV(7); break;
+        default: GPK_XCOV(8); break;
+    }
+#undef GPK_XCOV
     if (check_launch("k_oz_cross_cov")) return 1;
     const OzPredTiles f{state, kdig, Np, Bp / OZ_TILE_N, sigb, partial, (size_t)Bp};
     if (oz_launch<OZ_SUMSQ>(f, f.nx * (Np / NB), counter, st)) return 1;
