@@ -135,6 +135,7 @@ struct OzTile {
     int nk;               // number of 32-wide K chunks
     double* c;            // &C[row0][col0] of the 128 x 64 FP64 tile
     int ldc;
+    int store;            // 0: the FP64 result is not written (only its digits / maxima are wanted downstream)
     const double* sa;     // row scales sigma of the 128 A rows, or nullptr
     double sa_const;      // multiplies every row scale (use it alone when sa == nullptr)
     const double* sb;     // scales of the 64 B rows, or nullptr (= 1)
@@ -336,8 +337,10 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
         tc_fence_before();
         mbar_arrive(freebar);                    // TMEM may be overwritten
         if (EPI != OZ_SUMSQ) {
+            if (t.store) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) stg_f64x4(crow + 4 * j, val[4 * j], val[4 * j + 1], val[4 * j + 2], val[4 * j + 3]);
+                for (int j = 0; j < 8; ++j) stg_f64x4(crow + 4 * j, val[4 * j], val[4 * j + 1], val[4 * j + 2], val[4 * j + 3]);
+            }
             if (t.amax) {
                 double m = 0.0;
 #pragma unroll
@@ -405,6 +408,7 @@ __device__ __forceinline__ void oz_no_digits(OzTile& t) {
     t.dbg = nullptr;
     t.dig = nullptr; t.dig_rs = nullptr; t.dig_rconst = 1.0; t.dig_cs = nullptr;
     t.amax = nullptr; t.amax_cs = nullptr;
+    t.store = 1;
     t.red = nullptr; t.red_ld = 0;
 }
 
@@ -436,6 +440,7 @@ struct OzSyrkTiles {
             t.dig = sdig + (size_t)p * sdig_stride + ((size_t)I * 4 + 2 * h) * OZ_CHUNK;
             t.dig_rs = rowinv + I * NB;
             t.dig_cs = rowinv + J * NB + h * OZ_TILE_N;
+            t.store = 0;       // S_IJ (I > J) is read again only as digits (by the TRSM); S_JJ goes to the diagonal kernel in FP64
         }
         return true;
     }
@@ -678,6 +683,7 @@ struct OzTrsmTiles {
         oz_no_digits(t);
         t.dig = slices + (size_t)p * slice_stride + ((size_t)I * kch + 4 * J + 2 * h) * OZ_CHUNK;
         t.dig_rs = rowinv + I * NB;
+        t.store = 0;           // L_IJ is consumed as digits only (later SYRKs, phase-2 panel); the inverse overwrites the block
         return true;
     }
 };
