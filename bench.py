@@ -224,8 +224,8 @@ def measure_fp64_peak(torch, dev):
 
 
 # DRAM bytes per launch of the digit-GEMM roles, from the ncu launch list of this command (dram__bytes_read.sum +
-# dram__bytes_write.sum, mean over the launches of one role; 64-particle groups): profiles/r01_launch_summary_v8.csv
-NCU_TRAFFIC_PER_LAUNCH = {"k_oz_invu": 1410.89e6 + 220.57e6, "k_oz_syrk": 1922.79e6 + 305.89e6}
+# dram__bytes_write.sum, mean over the launches of one role; 64-particle groups): profiles/r01_launch_summary_v12.csv
+NCU_TRAFFIC_PER_LAUNCH = {"k_oz_invu": 1409.57e6 + 219.37e6, "k_oz_syrk": 1929.11e6 + 147.49e6}
 
 
 def dram_traffic(kernel, N, P, launches):
@@ -236,12 +236,14 @@ def dram_traffic(kernel, N, P, launches):
     pairs = sum(n * (n + 1) // 2 for n in range(T))            # 128 x 128 operand blocks read per matrix per phase
     per_matrix = pairs * 128 * 128 * 7                          # A digits: 7 bytes per element, each block read once
     per_matrix += sum(range(T)) * 128 * 128 * 7                 # B digits (panel / block row) per block column
-    per_matrix += sum(range(T)) * 128 * 128 * (8 + 7)           # FP64 output tile + its digits for the next contraction
     if kernel == "k_oz_syrk":
-        per_matrix += sum(range(T)) * 128 * 128 * 8             # the covariance tile it is subtracted from
+        per_matrix += sum(range(T)) * 128 * 128 * (8 + 7)       # covariance tile read, digits of the Schur block written
+        per_matrix += T * 128 * 128 * 8                         # FP64 copy of the diagonal Schur blocks only
+    else:
+        per_matrix += sum(range(T)) * 128 * 128 * (8 + 7)       # FP64 output tile + its digits for the next contraction
     return {"traffic": NCU_TRAFFIC_PER_LAUNCH[kernel],
             "traffic_unit": "DRAM bytes per launch (64-particle group)",
-            "traffic_source": "ncu launch list of this command, profiles/r01_launch_summary_v8.csv",
+            "traffic_source": "ncu launch list of this command, profiles/r01_launch_summary_v12.csv",
             "algorithmic_bytes_per_launch": per_matrix * 64 / (T - 1)}
 
 
