@@ -225,7 +225,7 @@ def measure_fp64_peak(torch, dev):
 
 # DRAM bytes per launch of the digit-GEMM roles, from the ncu launch list of this command (dram__bytes_read.sum +
 # dram__bytes_write.sum, mean over the launches of one role; 64-particle groups): profiles/r01_launch_summary_v12.csv
-NCU_TRAFFIC_PER_LAUNCH = {"k_oz_invu": 1409.57e6 + 219.37e6, "k_oz_syrk": 1929.11e6 + 147.49e6}
+NCU_TRAFFIC_PER_LAUNCH = {"k_oz_invu": 1409.57e6 + 219.37e6, "k_oz_syrk": 1445.11e6 + 107.60e6}
 
 
 def dram_traffic(kernel, N, P, launches):
@@ -235,7 +235,8 @@ def dram_traffic(kernel, N, P, launches):
     T = N // 128
     pairs = sum(n * (n + 1) // 2 for n in range(T))            # 128 x 128 operand blocks read per matrix per phase
     per_matrix = pairs * 128 * 128 * 7                          # A digits: 7 bytes per element, each block read once
-    per_matrix += sum(range(T)) * 128 * 128 * 7                 # B digits (panel / block row) per block column
+    if kernel == "k_oz_invu":
+        per_matrix += sum(range(T)) * 128 * 128 * 7             # B digits: the phase-2 panel (SYRK's B is one of its A row blocks)
     if kernel == "k_oz_syrk":
         per_matrix += sum(range(T)) * 128 * 128 * (8 + 7)       # covariance tile read, digits of the Schur block written
         per_matrix += T * 128 * 128 * 8                         # FP64 copy of the diagonal Schur blocks only

@@ -20,6 +20,7 @@ def main(path):
     for r in rows:
         per[int(r["ID"])]["name"] = r["Kernel Name"]
         per[int(r["ID"])]["stream"] = r["Stream"]
+        per[int(r["ID"])]["grid"] = r["Grid Size"]
         v = float(r["Metric Value"].replace(",", ""))
         unit = r["Metric Unit"]
         scale = {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3, "byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(unit, 1.0)
@@ -31,7 +32,11 @@ def main(path):
         if not per[i]["cls"].startswith("other:"):
             streams[per[i]["stream"]].append(i)
     for ids in streams.values():
+        particles = "?"
         for j, i in enumerate(ids):
+            if per[i]["cls"] == "k_cov_lower":          # grid (tiles, P): the particle group every following launch works on
+                particles = per[i]["grid"].strip("()").split(",")[1].strip()
+            per[i]["P"] = particles
             if per[i]["cls"] != "k_oz":
                 continue
             prev = per[ids[j - 1]]["cls"] if j else ""
@@ -41,7 +46,9 @@ def main(path):
             per[i]["cls"] = f"k_oz[{role}]"
     agg = defaultdict(lambda: [0, 0.0, 0.0, 0.0])
     for k in per.values():
-        a = agg[k["cls"]]
+        if k["cls"].startswith("other:"):
+            continue
+        a = agg[f'{k["cls"]} P={k.get("P", "?")}']
         a[0] += 1
         a[1] += k.get("gpu__time_duration.sum", 0.0)
         a[2] += k.get("dram__bytes_read.sum", 0.0)
