@@ -29,6 +29,9 @@ if ROOT not in sys.path:
 
 WORKLOAD = dict(n_points=4096, dims=3, particles_per_gpu=256, n_sigma=1000)
 INT8_PEAK_TOPS = 4497.0
+# the same instruction stream with uniformly random signed digits as operands and no memory traffic at all: the board
+# reaches its 1000 W cap and holds 3780 TOP/s (tools/umma_power.cu, profiles/r01_umma_power.log)
+INT8_SUSTAINED_RANDOM_TOPS = 3780.0
 INT8_PEAK_SOURCE = ("int8 tcgen05.mma issue-rate probe on this pool's B200 (tools/umma_probe.cu, 148 CTAs, N=256: 4497 TOP/s, "
                     "profiles/r01_umma_probe.log; nominal 4500).  MEASURED_PEAKS.json has only bf16 (1645 burst / 1379 "
                     "sustained TFLOP/s, cuBLAS); twice that, 3291 / 2757, is the library-GEMM-equivalent int8 figure")
@@ -438,6 +441,8 @@ def run_ours(args):
                                         "FP64 cuBLAS DGEMM 8192^3 measured in this run (MEASURED_PEAKS.json has no FP64 figure; "
                                         "DMMA issue-rate probe: 37.1 TFLOP/s, profiles/r01_fp64_peak_probe.txt)",
                          "fp64_dgemm_tflops_measured": fp64_peak,
+                         "peak_sustained_random_operands": INT8_SUSTAINED_RANDOM_TOPS if emulated else None,
+                         "frac_of_sustained": (achieved / INT8_SUSTAINED_RANDOM_TOPS) if (emulated and achieved) else None,
                          "algorithmic_flops_per_launch": flops_top / top[1][1] if flops_top else None,
                          "avg_launch_ms": top[1][0] / top[1][1],
                          "whole_step_tflops": algorithmic_flops_per_eval(N) * P * args.steps / (dev_ms * 1e-3) / 1e12,
