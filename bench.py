@@ -164,6 +164,39 @@ def cpu_baseline_sample():
                       f"{np.mean([o[1] for o in out]):.1f} s per evaluation"}
 
 
+def cpu_aux_baselines():
+    """SURVEY 8(d) CPU legs for the other quantities of the metric, bounded samples, one process (the reference runs
+    these parts single-process): (iii) GP() fit + predict on a 10 000-point slice of the C3 grid, (iv) the surface
+    reduction on 2 000 merged rows, and the default-workflow loss evaluation (N=100 after the KMeans subsample)."""
+    from oracle import gp_oracle as orc
+    out = {}
+    N, d = WORKLOAD["n_points"], WORKLOAD["dims"]
+    x, y, e = orc.synthetic_problem(N, d, 1)
+    xfit = np.random.default_rng(0).random((d, 10000))
+    t0 = time.perf_counter()
+    orc.gp(x, y, e, xfit, np.full(d, 0.25))
+    dt = time.perf_counter() - t0
+    out["grid_predict"] = {"value": 10000 / dt, "unit": "grid_pts/s", "cores": os.cpu_count(), "kind": "port",
+                           "sample": f"GP() fit + predict of one 10 000-point batch at N={N}, d={d}: {dt:.1f} s (NumPy/LAPACK threads as configured)"}
+    t = orc.synthetic_surface_table(2000, 16, seed=3)
+    t0 = time.perf_counter()
+    orc.prob_surface_rows(t)
+    dt = time.perf_counter() - t0
+    out["prob_surface"] = {"value": 2000 / dt, "unit": "rows/s", "cores": 1, "kind": "port",
+                           "sample": f"2 000 merged rows x 16 experiments, row loop of generate_prob_surf: {dt:.2f} s"}
+    x, y, e = orc.synthetic_problem(100, 2, 0)
+    pos, lo, hi = orc.synthetic_particles(x, 40, 0)
+    sv, ex = orc.sigma_grid()
+    t0 = time.perf_counter()
+    for k in range(200):
+        orc.evaluate_loss(pos[k % 40], x, y, e, sv, ex, lo, hi)
+    dt = time.perf_counter() - t0
+    out["len_scale_opt_default"] = {"value": 200 / dt, "unit": "loss_evals/s", "cores": 1, "kind": "port",
+                                    "sample": f"200 evaluate_loss calls at N=100, d=2 in one process: {dt:.2f} s; the reference maps "
+                                              f"them over max(1, cpu_count // 4) pool workers"}
+    return out
+
+
 def run_reference(args):
     """--impl reference: the CPU implementation of the path (NumPy oracle port) on all host cores."""
     rank = int(os.environ.get("RANK", "0"))
@@ -289,6 +322,42 @@ def aux_measurements(torch, engine):
     out["prob_surface"] = {"workload": f"surface reduction: {R} merged rows, {E} experiments, 25% gaps, 100 points per row",
                            "e2e": {"value": R / s_e2e, "unit": "rows/s", "h2d_bytes": int(table.nbytes), "d2h_bytes": int(yy.nbytes + pp.nbytes + idx.nbytes)},
                            "valid_rows": int(len(idx))}
+    del idx, yy, pp
+    # the same reduction as the workflow uses it: generate_prob_surf streaming into the CSV text of the output file
+    import pandas as pd
+    import tempfile
+    from gaussian_process_b200 import surface
+    Rc = 1 << 16
+    df = pd.DataFrame(np.hstack([np.random.default_rng(1).random((Rc, 4)), table[:Rc]]),
+                      columns=["d0", "d1", "d2", "d3"] + [f"c{i}" for i in range(2 * E)])
+    with tempfile.TemporaryDirectory() as tmp:
+        path = os.path.join(tmp, "prob_surf.txt")
+        t0 = time.perf_counter()
+        n_out = surface.write_surface_csv(df, 4, path)
+        s_csv = time.perf_counter() - t0
+        nbytes = os.path.getsize(path)
+    out["prob_surface"]["csv_e2e"] = {"value": Rc / s_csv, "unit": "rows/s", "merged_rows": Rc, "output_rows": int(n_out),
+                                      "csv_bytes": int(nbytes), "host_threads": os.cpu_count(),
+                                      "includes": "H2D, reduction, D2H, long-format expansion, CSV text (to_csv bytes), file write"}
+    # the reference's real PSO configuration: KMeans subsample to 100 points, 40 particles, 500 iterations
+    import contextlib
+    import io
+    from gaussian_process_b200 import pso
+    x, y, e = synthetic.problem(1024, 2, 0)
+    trace = []
+    np.random.seed(0)
+    with contextlib.redirect_stdout(io.StringIO()):
+        pso.len_scale_opt(x, y, e, False, lhs_random_state=0, max_iter=20)           # warm-up (module load, pinned buffers)
+        np.random.seed(0)
+        t0 = time.perf_counter()
+        best = pso.len_scale_opt(x, y, e, False, lhs_random_state=0, trace=trace)
+        dt = time.perf_counter() - t0
+    n_evals = sum(len(sc) for _p, sc in trace)
+    out["len_scale_opt_default"] = {"workload": "len_scale_opt as GP_fit calls it: C2 points (N=1024, d=2), KMeans subsample to 100, 40 particles, 500 iterations",
+                                    "seconds": dt, "swarm_evaluations": len(trace), "loss_evaluations": n_evals,
+                                    "e2e": {"value": n_evals / dt, "unit": "loss_evals/s",
+                                            "includes": "KMeans subsample, LHS, host PSO update, H2D positions, loss kernel, D2H counts, host finish"},
+                                    "best_length_scales": [float(v) for v in best]}
     return out
 
 
@@ -300,9 +369,10 @@ def run_ours(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    cpu_base = None
+    cpu_base = cpu_aux = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu_base = cpu_baseline_sample()            # before CUDA is initialised in this process
+        cpu_aux = None if args.no_aux else cpu_aux_baselines()
 
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
@@ -399,6 +469,8 @@ def run_ours(args):
         del ctx
         engine.release_workspaces()
         aux = aux_measurements(torch, engine)
+        for k, v in (cpu_aux or {}).items():
+            aux.setdefault(k, {})["cpu_baseline"] = v
 
     if world > 1:
         t = torch.tensor([dev_ms, e2e_s], dtype=torch.float64, device=dev)

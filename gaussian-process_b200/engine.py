@@ -343,48 +343,37 @@ def _pinned_buffer(tag, nbytes):
     return buf
 
 
-def prob_surface(table, points=100, rows_per_pass=None):
-    """table (R, 2E) host payload -> (row_index[Rv], y[Rv,points], p[Rv,points]) of the emitting rows.
-    Passes of `rows_per_pass` rows are pipelined over two streams: while pass k's compacted result drains to the host
-    through page-locked staging buffers (the output is 1600 B per row, so this path is PCIe bound), pass k+1 uploads and
-    computes."""
+def prob_surface_passes(table, points=100, rows_per_pass=None):
+    """Generator over the passes of the surface reduction, in row order: yields (row_index[k] int64 (global),
+    y[k,points], p[k,points]) of the emitting rows of one pass.  The arrays are views of page-locked staging buffers and
+    stay valid only until the generator is advanced again.  Passes of `rows_per_pass` rows are pipelined over two
+    streams: while the consumer works on pass k (copy out, CSV text), pass k+1 uploads, computes and drains."""
     lib = _lib.load()
     table = _f64(table)
     r, ncols = table.shape
     if r == 0 or ncols == 0:
-        return np.zeros(0, dtype=np.int64), np.zeros((0, points)), np.zeros((0, points))
+        return
     if rows_per_pass is None:
         rows_per_pass = max(1, min(r, (1 << 27) // (points * 8)))        # 128 MB of y (and of p) per pass
     dev = device()
-    y_out = np.empty((r, points))
-    p_out = np.empty((r, points))
-    idx_out = np.empty(r, dtype=np.int64)
-    y_t, p_t, idx_t = torch.from_numpy(y_out), torch.from_numpy(p_out), torch.from_numpy(idx_out)
     streams = [torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)]
     main = torch.cuda.current_stream()
     for st_ in streams:
         st_.wait_stream(main)
     slot_bytes = rows_per_pass * points * 8
-    pending = [None, None]              # per slot: (rows kept, staging views, first row, done event)
-    n_out = 0
+    pending = []                        # passes in flight, oldest first: (rows kept, staging views, first row, done event)
 
-    def drain(slot):
-        nonlocal n_out
-        item = pending[slot]
-        if item is None:
-            return
+    def finished(item):
         k, ys, ps, ids, r0, done = item
         done.synchronize()
-        y_t[n_out:n_out + k].copy_(ys[:k])                                # threaded host copy out of the staging buffer
-        p_t[n_out:n_out + k].copy_(ps[:k])
-        idx_t[n_out:n_out + k].copy_(ids[:k])
-        idx_out[n_out:n_out + k] += r0
-        n_out += k
-        pending[slot] = None
+        idx = ids[:k].numpy()
+        idx += r0
+        return idx, ys[:k].numpy(), ps[:k].numpy()
 
     for i, r0 in enumerate(range(0, r, rows_per_pass)):
         slot = i & 1
-        drain(slot)                                                       # its staging buffers are about to be reused
+        if len(pending) == 2:                                             # this slot's staging buffers are about to be reused
+            yield finished(pending.pop(0))
         rc = min(rows_per_pass, r - r0)
         stage_in = _pinned_buffer(("surf_in", slot), rows_per_pass * ncols * 8)[:rc * ncols * 8].view(torch.float64).view(rc, ncols)
         stage_in.copy_(torch.from_numpy(table[r0:r0 + rc]))
@@ -411,12 +400,31 @@ def prob_surface(table, points=100, rows_per_pass=None):
             ids[:k].copy_(keep, non_blocking=True)
             done = torch.cuda.Event()
             done.record(streams[slot])
-        pending[slot] = (k, ys, ps, ids, r0, done)
-    drain(0 if pending[0] is not None and (pending[1] is None or pending[0][4] < pending[1][4]) else 1)
-    drain(0)
-    drain(1)
+        pending.append((k, ys, ps, ids, r0, done))
+    while pending:
+        yield finished(pending.pop(0))
     main.wait_stream(streams[0])
     main.wait_stream(streams[1])
+
+
+def prob_surface(table, points=100, rows_per_pass=None):
+    """table (R, 2E) host payload -> (row_index[Rv], y[Rv,points], p[Rv,points]) of the emitting rows (the output is
+    1600 B per row, so this path is bound by the host side: PCIe and the copy out of the staging buffers)."""
+    table = _f64(table)
+    r, ncols = table.shape
+    if r == 0 or ncols == 0:
+        return np.zeros(0, dtype=np.int64), np.zeros((0, points)), np.zeros((0, points))
+    y_out = np.empty((r, points))
+    p_out = np.empty((r, points))
+    idx_out = np.empty(r, dtype=np.int64)
+    y_t, p_t = torch.from_numpy(y_out), torch.from_numpy(p_out)
+    n_out = 0
+    for idx, ys, ps in prob_surface_passes(table, points, rows_per_pass):
+        k = idx.shape[0]
+        y_t[n_out:n_out + k].copy_(torch.from_numpy(ys))                  # threaded host copy out of the staging buffer
+        p_t[n_out:n_out + k].copy_(torch.from_numpy(ps))
+        idx_out[n_out:n_out + k] = idx
+        n_out += k
     if n_out == r:
         return idx_out, y_out, p_out
     return idx_out[:n_out].copy(), y_out[:n_out].copy(), p_out[:n_out].copy()

@@ -2,7 +2,8 @@
 
 The row loop of generate_prob_surf (calc_prob_surf.py:67-81: finite mask, linspace y-axis,
 sum_gaussians) is one `gpk_prob_surface` launch over the whole merged table; the frame assembly (:83) stays in
-pandas and the frozen text format of `to_csv` (:84) is written by libgpk's threaded formatter (tables.write_csv)."""
+pandas (surface_frame) for callers that want the table; generate_prob_surf itself streams pass by pass into libgpk's
+threaded formatter (the frozen text format of `to_csv`, :84) without ever holding the long-format table."""
 import os
 
 import numpy as np
@@ -47,11 +48,42 @@ def surface_frame(df, ndims, points=POINTS):
     return pd.DataFrame(out, columns=df.columns[:ndims].tolist() + ["quantity", "prob"])
 
 
+STREAM_ROWS = 1 << 15             # merged rows per CSV block of the streaming writer (3.3 M output rows, ~160 MB of float64)
+
+
+def write_surface_csv(df, ndims, output_file, points=POINTS, rows_per_pass=None):
+    """The file generate_prob_surf writes (:80-84), produced pass by pass: each pass of the GPU reduction is expanded to
+    its long-format block (coords repeated `points` times, quantity, prob), formatted by libgpk's threaded CSV
+    formatter and appended, while the next pass runs on the device.  Host memory stays bounded by the pass size, so the
+    64^4-row configuration (1.7e9 output rows) never exists as one frame.  Returns the number of output rows."""
+    columns = df.columns[:ndims].tolist() + ["quantity", "prob"]
+    header = tables.plain_header(columns)
+    if header is None:                                     # column names that need quoting: let pandas write the file
+        out = surface_frame(df, ndims, points)
+        out.to_csv(output_file, index=False)
+        return len(out)
+    values = df.to_numpy(dtype=np.float64)
+    coords, payload = values[:, :ndims], values[:, ndims:]
+    n_rows = 0
+    with open(output_file, "wb") as f:
+        f.write(header.encode("utf-8"))
+        for idx, y, p in engine.prob_surface_passes(payload, points, rows_per_pass):
+            for b0 in range(0, idx.shape[0], STREAM_ROWS):
+                sel = idx[b0:b0 + STREAM_ROWS]
+                k = sel.shape[0]
+                block = np.empty((k * points, ndims + 2))
+                block[:, :ndims] = np.repeat(coords[sel], points, axis=0)
+                block[:, ndims] = y[b0:b0 + k].reshape(-1)
+                block[:, ndims + 1] = p[b0:b0 + k].reshape(-1)
+                f.write(tables.format_block(block))
+                n_rows += k * points
+    return n_rows
+
+
 def generate_prob_surf(df, ndims, options_path="options.yaml"):
     """Drop-in for calc_prob_surf.generate_prob_surf (:39-88): same prints, same CSV."""
     print("Calculating Probability")
     output_file = resolve_output_path(options_path)
-    output_df = surface_frame(df, ndims)
-    tables.write_csv(output_df, output_file)               # the bytes of to_csv(index=False), :84
+    write_surface_csv(df, ndims, output_file)              # the bytes of to_csv(index=False), :84
     print(f"Probability results written to {output_file}")
     return

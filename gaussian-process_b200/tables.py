@@ -119,24 +119,35 @@ def _plain_header(columns):
     return ",".join(names) + "\n"
 
 
+def format_block(block, threads=0):
+    """float64 (rows, cols) C-contiguous block -> the bytes of its to_csv(index=False, header=False) text
+    (libgpk's threaded formatter, gpk_csv_format_f64)."""
+    import ctypes as C
+    from . import _lib
+    lib = _lib.load()
+    block = np.ascontiguousarray(block, dtype=np.float64)
+    rows, ncol = block.shape
+    cap = lib.gpk_csv_bound(rows, ncol)
+    out = np.empty(cap, dtype=np.uint8)
+    n = lib.gpk_csv_format_f64(block.ctypes.data_as(C.c_void_p), rows, ncol, ncol,
+                               out.ctypes.data_as(C.c_void_p), cap, threads)
+    if n < 0:
+        raise _lib.GpkError("gpk_csv_format_f64 rejected its arguments")
+    return memoryview(out)[:n]
+
+
+def plain_header(columns):
+    """Header line of to_csv for column names that need no quoting, else None."""
+    return _plain_header(columns)
+
+
 def write_csv(df, path, threads=0):
     """df.to_csv(path, index=False) for an all-float64 table; anything else is handed to pandas."""
     header = _plain_header(df.columns)
     if header is None or len(df.columns) == 0 or any(dt != np.float64 for dt in df.dtypes):
         df.to_csv(path, index=False)
         return
-    import ctypes as C
-    from . import _lib
-    lib = _lib.load()
-    ncol = len(df.columns)
     with open(path, "wb") as f:
         f.write(header.encode("utf-8"))
         for r0 in range(0, len(df), _CSV_BLOCK_ROWS):
-            block = np.ascontiguousarray(df.iloc[r0:r0 + _CSV_BLOCK_ROWS].to_numpy(dtype=np.float64))
-            cap = lib.gpk_csv_bound(block.shape[0], ncol)
-            out = np.empty(cap, dtype=np.uint8)
-            n = lib.gpk_csv_format_f64(block.ctypes.data_as(C.c_void_p), block.shape[0], ncol, ncol,
-                                       out.ctypes.data_as(C.c_void_p), cap, threads)
-            if n < 0:
-                raise _lib.GpkError("gpk_csv_format_f64 rejected its arguments")
-            f.write(memoryview(out)[:n])
+            f.write(format_block(df.iloc[r0:r0 + _CSV_BLOCK_ROWS].to_numpy(dtype=np.float64), threads))

@@ -220,6 +220,32 @@ def test_generate_prob_surf_csv(mods, tmp_path, monkeypatch):
     np.testing.assert_allclose(mods["cps"].sum_gaussians(t, gaus), orc.sum_gaussians(t, gaus), rtol=1e-9, atol=1e-15)
 
 
+def test_surface_csv_streaming_equals_frame_writer(mods, tmp_path, monkeypatch):
+    """The pass-by-pass writer of generate_prob_surf produces the bytes of to_csv on the whole long-format frame,
+    whatever the pass and block sizes (silent rows, ragged last pass, no emitting row at all)."""
+    import pandas as pd
+    from gaussian_process_b200 import surface, tables
+    t = orc.synthetic_surface_table(3001, 5, seed=11, p_gap=0.6)
+    coords = np.random.default_rng(5).random((t.shape[0], 3))
+    cols = ["a", "b", "c"] + [f"e{i}" for i in range(t.shape[1])]
+    df = pd.DataFrame(np.hstack([coords, t]), columns=cols)
+    tables.write_csv(surface.surface_frame(df, 3), tmp_path / "whole.csv")
+    want = (tmp_path / "whole.csv").read_bytes()
+    assert want.count(b"\n") > 100
+    for rows_per_pass, stream_rows in ((None, 1 << 15), (700, 256), (97, 1000), (3001, 1)):
+        monkeypatch.setattr(surface, "STREAM_ROWS", stream_rows)
+        n = surface.write_surface_csv(df, 3, tmp_path / "stream.csv", rows_per_pass=rows_per_pass)
+        got = (tmp_path / "stream.csv").read_bytes()
+        assert got == want, (rows_per_pass, stream_rows)
+        assert n == want.count(b"\n") - 1
+    # pandas on the same frame (the reference's writer)
+    surface.surface_frame(df, 3).to_csv(tmp_path / "pandas.csv", index=False)
+    assert (tmp_path / "pandas.csv").read_bytes() == want
+    silent = pd.DataFrame(np.hstack([coords[:10], np.full((10, 4), np.inf)]), columns=cols[:7])
+    assert surface.write_surface_csv(silent, 3, tmp_path / "empty.csv") == 0
+    assert (tmp_path / "empty.csv").read_bytes() == b"a,b,c,quantity,prob\n"
+
+
 # ------------------------------------------------------------------ PSO trajectories (config C1 + N=100)
 TIE = 1e-10     # a pull within this of 1.0 in the reference itself is a rounding tie (see DESIGN.md, parity)
 
