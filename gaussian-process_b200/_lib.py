@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgpk.so")
+LIB_PATH = os.environ.get("GPK_LIB") or os.path.join(_HERE, "libgpk.so")     # GPK_LIB: instrumented builds (tools/)
 
 _vp, _i, _ll, _sz = C.c_void_p, C.c_int, C.c_longlong, C.c_size_t
 

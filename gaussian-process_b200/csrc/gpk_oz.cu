@@ -39,6 +39,10 @@ constexpr int OZ_CHUNK = OZ_NS * OZ_DIGIT;      // 128 rows x 32 k x 7 digits = 
 constexpr int OZ_HALF = OZ_NS * OZ_DIGIT_HALF;  // 64 rows, digits back to back (shared-memory image of B)
 constexpr int OZ_STAGE = OZ_CHUNK + OZ_HALF;    // A (128 rows) + B (64 rows)
 constexpr int OZ_STAGES = 5;
+#ifndef OZ_PREFETCH_CHUNKS
+#define OZ_PREFETCH_CHUNKS 0
+#endif
+constexpr int OZ_PREFETCH = OZ_PREFETCH_CHUNKS;   // A chunks prefetched into L2 beyond the shared-memory ring (0 = off)
 constexpr int OZ_THREADS = 320;                 // warp 0 producer, warp 1 MMA issuer, warps 2..9 epilogue
 constexpr int OZ_TMEM_COLS = 512;
 constexpr int OZ_TILE_N = 64;
@@ -80,6 +84,9 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         if (clock64() - t0 > 4000000000LL) __trap();
     }
 }
+__device__ __forceinline__ void bulk_prefetch_l2(const void* src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;\n" ::"l"(src), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(dst),
                  "l"(src), "r"(bytes), "r"(bar)
@@ -119,6 +126,23 @@ __device__ __forceinline__ double ll2d_exact(long long v) {
     return __longlong_as_double(0x4338000000000000LL + v) - 6755399441055744.0;
 }
 
+// Exact double of the integer a0 2^16 + a1 2^8 + a2 (int32 accumulators, |value| < 2^48).  The register pair
+// magic_hi : (a2 ^ 0x80000000), magic_hi = 0x43380000, is the double 2^52 + 2^51 + 2^31 + a2; the other two terms are added
+// to it as 64-bit integers by two 32 x 32 + 64 multiply-adds, which keeps the mantissa field inside (0, 2^52); one FP64
+// subtraction of 2^52 + 2^51 + 2^31 finishes the conversion.  magic_hi arrives as a run-time value: with the constant
+// visible the compiler moves its addition behind the products and spends a carry chain per conversion.
+__device__ __forceinline__ double oz_acc3(uint32_t a0, uint32_t a1, uint32_t a2, uint32_t magic_hi) {
+    long long w = (long long)(((unsigned long long)magic_hi << 32) | (unsigned long long)(a2 ^ 0x80000000u));
+    w += (long long)(int)a1 * 256;
+    w += (long long)(int)a0 * 65536;
+    return __longlong_as_double(w) - 6755401588539392.0;      // 2^52 + 2^51 + 2^31
+}
+__device__ __forceinline__ double oz_acc2(uint32_t a0, uint32_t a1, uint32_t magic_hi) {
+    long long w = (long long)(((unsigned long long)magic_hi << 32) | (unsigned long long)(a1 ^ 0x80000000u));
+    w += (long long)(int)a0 * 256;
+    return __longlong_as_double(w) - 6755401588539392.0;
+}
+
 // byte b of four 32-bit words -> one word (digit b of four consecutive k)
 __device__ __forceinline__ uint32_t pack_digit(const uint32_t* w, int b) {
     const uint32_t sel = (uint32_t)b | ((uint32_t)(4 + b) << 4);
@@ -128,6 +152,16 @@ __device__ __forceinline__ uint32_t pack_digit(const uint32_t* w, int b) {
 }
 
 enum OzEpi { OZ_SUB = 0, OZ_STORE = 1, OZ_STORE_NEG = 2, OZ_SUMSQ = 3 };
+
+#ifdef OZ_PROFILE
+// Instrumented build only (tools/oz_stall.py): where the MMA thread of every CTA spends its cycles, summed per EPI kind:
+// [epi][0] total loop, [1] waiting for operands (full barriers), [2] waiting for the epilogue (freebar), [3] waiting for
+// the tile queue, [4] issuing MMAs, [5] tiles, [6] K chunks, [7] CTAs
+__device__ unsigned long long g_oz_prof[4][8];
+#define OZ_PROF_T(var) const long long var = clock64()
+#else
+#define OZ_PROF_T(var)
+#endif
 
 struct OzTile {
     const uint8_t* a;     // first chunk of the A row block (128 rows), chunks are consecutive in K
@@ -235,9 +269,15 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
                 mbar_arrive(qfull0 + 8 * qs);
                 if (tile < 0) break;
                 if (!f.make(tile, t)) continue;
+            if (OZ_PREFETCH > 0) {               // A chunks beyond the ring: HBM -> L2 ahead of the copy that needs them
+                for (int k = OZ_STAGES; k < OZ_STAGES + OZ_PREFETCH && k < t.nk; ++k)
+                    bulk_prefetch_l2(t.a + (size_t)k * OZ_CHUNK, OZ_CHUNK);
+            }
             for (int k = 0; k < t.nk; ++k, ++kg) {
                 const uint32_t s = kg % OZ_STAGES;
                 const uint32_t ph = (kg / OZ_STAGES) & 1u;
+                if (OZ_PREFETCH > 0 && k + OZ_STAGES + OZ_PREFETCH < t.nk)
+                    bulk_prefetch_l2(t.a + (size_t)(k + OZ_STAGES + OZ_PREFETCH) * OZ_CHUNK, OZ_CHUNK);
                 mbar_wait(empty0 + 8 * s, ph ^ 1u);
                 mbar_expect_tx(full0 + 8 * s, OZ_STAGE);
                 const uint32_t dst = stage0 + s * OZ_STAGE;
@@ -253,34 +293,60 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
         if (lane == 0) {
             OzTile t;
             uint32_t kg = 0, it = 0;
+#ifdef OZ_PROFILE
+            long long pf_full = 0, pf_free = 0, pf_q = 0, pf_issue = 0, pf_tiles = 0, pf_chunks = 0;
+            const long long pf_start = clock64();
+#endif
             for (uint32_t n = 0;; ++n) {
                 const uint32_t qs = n % OZ_QDEPTH;
+                OZ_PROF_T(q0);
                 mbar_wait(qfull0 + 8 * qs, (n / OZ_QDEPTH) & 1u);
                 const int tile = qtile[qs];
                 mbar_arrive(qempty0 + 8 * qs);
                 if (tile < 0) break;
                 if (!f.make(tile, t)) continue;
+                OZ_PROF_T(q1);
                 mbar_wait(freebar, (it & 1u) ^ 1u);      // the epilogue has drained the previous tile
                 tc_fence_after();
+                OZ_PROF_T(q2);
+#ifdef OZ_PROFILE
+                pf_q += q1 - q0; pf_free += q2 - q1; ++pf_tiles;
+#endif
                 ++it;
             for (int k = 0; k < t.nk; ++k, ++kg) {
                 const uint32_t s = kg % OZ_STAGES;
                 const uint32_t ph = (kg / OZ_STAGES) & 1u;
+                OZ_PROF_T(c0);
                 mbar_wait(full0 + 8 * s, ph);
                 tc_fence_after();
+                OZ_PROF_T(c1);
                 const uint64_t da = OZ_SDESC | (uint64_t)(((stage0 + s * OZ_STAGE) >> 4) & 0x3FFF);
                 const uint64_t db = OZ_SDESC | (uint64_t)(((stage0 + s * OZ_STAGE + OZ_CHUNK) >> 4) & 0x3FFF);
                 oz_issue_chunk<NG>(tmem, da, db, k == 0);
                 umma_commit(empty0 + 8 * s);     // frees the stage when these MMAs have read it
+#ifdef OZ_PROFILE
+                pf_full += c1 - c0; pf_issue += clock64() - c1; ++pf_chunks;
+#endif
             }
             umma_commit(accbar);                 // accumulators complete
             }
+#ifdef OZ_PROFILE
+            atomicAdd(&g_oz_prof[EPI][0], (unsigned long long)(clock64() - pf_start));
+            atomicAdd(&g_oz_prof[EPI][1], (unsigned long long)pf_full);
+            atomicAdd(&g_oz_prof[EPI][2], (unsigned long long)pf_free);
+            atomicAdd(&g_oz_prof[EPI][3], (unsigned long long)pf_q);
+            atomicAdd(&g_oz_prof[EPI][4], (unsigned long long)pf_issue);
+            atomicAdd(&g_oz_prof[EPI][5], (unsigned long long)pf_tiles);
+            atomicAdd(&g_oz_prof[EPI][6], (unsigned long long)pf_chunks);
+            atomicAdd(&g_oz_prof[EPI][7], 1ull);
+#endif
         }
     } else {
         // epilogue warps 2..9: TMEM lane quadrant = warp % 4, one output row and 32 of the 64 columns per thread
         const int q = warp & 3;
         const int ch = (warp - 2) >> 2;
         const int row = q * 32 + lane;
+        const uint32_t magic_hi = 0x43380000u + ((uint32_t)ntiles >> 31);     // = 0x43380000 (ntiles >= 0), opaque to the compiler
         OzTile t;
         uint32_t it = 0;
         for (uint32_t n = 0;; ++n) {
@@ -290,7 +356,7 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
         mbar_arrive(qempty0 + 8 * qs);
         if (tile < 0) break;
         if (!f.make(tile, t)) continue;
-        const double rs = (t.sa ? t.sa[row] : 1.0) * t.sa_const * 0x1p-14;
+        const double rs = (t.sa ? t.sa[row] : 1.0) * t.sa_const * 0x1p-70;       // 2^-14 of the digit scaling, 2^-56 of x
         double* crow = t.c + (size_t)row * t.ldc + ch * 32;
         const double* sbp = t.sb ? t.sb + ch * 32 : nullptr;
         const double drs = (t.dig_rs ? t.dig_rs[row] : 1.0) * t.dig_rconst * 0x1p55;
@@ -321,12 +387,13 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
             }
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-                const long long hi = ((long long)(int)a[0][j] << 16) + ((long long)(int)a[1][j] << 8) + (long long)(int)a[2][j];
-                const long long mid = ((long long)(int)a[3][j] << 16) + ((long long)(int)a[4][j] << 8) + (long long)(int)a[5][j];
-                long long lo = (long long)(int)a[6][j] << 8;
-                if (NG == 8) lo += (long long)(int)a[NG - 1][j];
-                double x = fma(ll2d_exact(mid), 0x1p-40, ll2d_exact(lo) * 0x1p-56);
-                x = fma(ll2d_exact(hi), 0x1p-16, x);
+                // three exact integers hi = a0 2^16 + a1 2^8 + a2, mid = a3 2^16 + a4 2^8 + a5, lo = a6 2^8 + a7, each built
+                // directly inside the bit pattern of a double (oz_acc3 / oz_acc2) and finished by one FP64 subtraction:
+                // this phase is issue bound (8 warps on 4 schedulers hold TMEM while they convert)
+                const double hi = oz_acc3(a[0][j], a[1][j], a[2][j], magic_hi);
+                const double mid = oz_acc3(a[3][j], a[4][j], a[5][j], magic_hi);
+                const double lo = (NG == 8) ? oz_acc2(a[6][j], a[NG - 1][j], magic_hi) : oz_acc2(a[6][j], 0u, magic_hi);
+                const double x = fma(hi, 0x1p40, fma(mid, 0x1p16, lo));      // units of 2^-56 (rs carries the factor)
                 const double v = x * (rs * (sbp ? sbp[cc + j] : 1.0));
                 if (EPI == OZ_SUB) val[cc + j] -= v;
                 else if (EPI == OZ_STORE) val[cc + j] = v;
@@ -1074,3 +1141,16 @@ int launch_oz_predict_chunk(const uint8_t* state, const double* xs, const double
 }
 
 }  // namespace gpk
+
+#ifdef OZ_PROFILE
+// instrumented build only: copies the 4 x 8 counters to the host and optionally clears them
+extern "C" __attribute__((visibility("default"))) int gpk_debug_oz_prof(unsigned long long* out32, int reset) {
+    if (cudaDeviceSynchronize() != cudaSuccess) return 1;
+    if (cudaMemcpyFromSymbol(out32, gpk::g_oz_prof, sizeof(unsigned long long) * 32) != cudaSuccess) return 1;
+    if (reset) {
+        unsigned long long z[32] = {};
+        if (cudaMemcpyToSymbol(gpk::g_oz_prof, z, sizeof z) != cudaSuccess) return 1;
+    }
+    return 0;
+}
+#endif
