@@ -141,6 +141,24 @@ def test_loss_vs_oracle_seeded(mods, precision, n, d, p, seed):
             assert np.abs(counts[k] - c_ref).max() <= 1
 
 
+def test_loss_randomised_sweep(mods):
+    """60 seeded random cases (tools/parity_sweep.py: ragged N around the 128-block boundaries, 1 <= d <= 6, odd swarm
+    sizes, inactive particles, uncertainties over three decades, clustered points, short and long length scales), both
+    arithmetic modes, against the checker: counts identical outside rounding ties, residual and sd within 1e-7 of the
+    checker even on the ill-conditioned cases (its own 1 - sum v^2 cancellation sets that floor)."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("parity_sweep", os.path.join(ROOT, "tools", "parity_sweep.py"))
+    sweep = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(sweep)
+    prev = mods["engine"].get_precision()
+    try:
+        n, bad, wr, ws = sweep.run(seconds=120.0, max_cases=60, seed=7, sizes=[3, 127, 128, 129, 255, 257, 385, 513, 640, 1025],
+                                   verbose=False)
+    finally:
+        mods["engine"].set_precision(prev)
+    assert n == 60 and bad == 0, (n, bad, wr, ws)
+
+
 def test_loss_not_positive_definite_raises(mods):
     x = np.array([[0.0, 0.0, 1.0]])          # duplicate point, zero noise -> singular K
     y = np.array([0.0, 1.0, 0.5])
