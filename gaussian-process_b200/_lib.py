@@ -17,6 +17,9 @@ SIGNATURES = {
     "gpk_cov_batched": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _ll, _ll, _vp]),
     "gpk_potrf_workspace_bytes": (_sz, [_i, _i]),
     "gpk_potrf_batched": (_i, [_vp, _i, _i, _vp, _vp, _sz, _vp]),
+    "gpk_staged_workspace_bytes": (_sz, [_i, _i]),
+    "gpk_fit_alpha_batched": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _sz, _vp]),
+    "gpk_selfpredict_counts": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "gpk_loss_workspace_bytes": (_sz, [_i, _i, _i]),
     "gpk_loss_batched": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "gpk_fit_workspace_bytes": (_sz, [_i, _i]),

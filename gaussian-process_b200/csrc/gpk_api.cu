@@ -250,6 +250,77 @@ int gpk_potrf_batched(double* K_inout, int P, int Np, int* info, void* workspace
     return factor_phase(K_inout, Np, T, P, dinv, dinvT, info, nullptr, DIAG_WRITE_FACTOR, OzBuffers{}, st);
 }
 
+// ---- staged interface (gpk_fit_alpha_batched, gpk_selfpredict_counts): the stages gpk_loss_batched fuses,
+// callable one by one on factors produced by gpk_potrf_batched.  Native FP64 arithmetic (the digit state of the
+// emulated mode is not part of this interface).
+struct StagedLayout { size_t mat, dinv, dinvT, mt, z, cn, alpha, info, total; };
+static StagedLayout staged_layout(int P, int Np) {
+    StagedLayout L{};
+    const size_t T = Np / NB;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += align256(bytes); return o; };
+    L.mat = take((size_t)P * Np * Np * 8);
+    L.dinv = take((size_t)P * T * NB * NB * 8);
+    L.dinvT = take((size_t)P * T * NB * NB * 8);
+    L.mt = take((size_t)P * NB * Np * 8);
+    L.z = take((size_t)P * Np * 8);
+    L.cn = take((size_t)P * Np * 8);
+    L.alpha = take((size_t)P * Np * 8);
+    L.info = take((size_t)P * sizeof(int));
+    L.total = off;
+    return L;
+}
+
+// W = L^-1 into the workspace copy (lower block triangle): diagonal blocks by substitution, the rest by the blocked
+// inverse of the fused path (native DMMA contractions)
+static int staged_inverse(const double* L, int P, int Np, char* ws, const StagedLayout& S, const unsigned char* active,
+                          cudaStream_t st) {
+    const int T = Np / NB;
+    double* mat = (double*)(ws + S.mat);
+    if (cudaMemcpyAsync(mat, L, (size_t)P * Np * Np * 8, cudaMemcpyDeviceToDevice, st) != cudaSuccess) { set_error("copy of the factors failed"); return 1; }
+    if (cudaMemsetAsync(ws + S.info, 0, (size_t)P * sizeof(int), st) != cudaSuccess) { set_error("memset info failed"); return 1; }
+    if (launch_tri_inv_diag(L, mat, Np, T, P, (double*)(ws + S.dinv), (double*)(ws + S.dinvT), (int*)(ws + S.info), active, st)) return 1;
+    return inverse_phase(mat, Np, T, P, (const double*)(ws + S.dinvT), (double*)(ws + S.mt), active, OzBuffers{}, st);
+}
+
+size_t gpk_staged_workspace_bytes(int P, int Np) {
+    if (P < 1 || Np < NB || Np % NB != 0) return 0;
+    return staged_layout(P, Np).total;
+}
+
+int gpk_fit_alpha_batched(const double* L, const double* y, int P, int N, int Np, double* alpha_out, void* workspace,
+                          size_t workspace_bytes, void* stream) {
+    if (P < 1 || N < 1 || Np < NB || Np % NB != 0 || N > Np) { set_error("gpk_fit_alpha_batched: P=%d N=%d Np=%d", P, N, Np); return 2; }
+    const StagedLayout S = staged_layout(P, Np);
+    if (workspace == nullptr || workspace_bytes < S.total) { set_error("gpk_fit_alpha_batched: workspace too small"); return 3; }
+    cudaStream_t st = (cudaStream_t)stream;
+    set_stream(st);
+    char* ws = (char*)workspace;
+    if (staged_inverse(L, P, Np, ws, S, nullptr, st)) return 1;
+    const double* mat = (const double*)(ws + S.mat);
+    if (launch_wy(mat, Np, N, P, y, (double*)(ws + S.z), nullptr, st)) return 1;
+    return launch_colnorm_alpha(mat, Np, P, (const double*)(ws + S.z), (double*)(ws + S.cn), alpha_out, nullptr, st);
+}
+
+int gpk_selfpredict_counts(const double* L, const double* alpha, const double* y, const double* e,
+                           const double* sigma_vals, const unsigned char* active, int P, int N, int Np, int S,
+                           int* counts_out, double* resid_out, double* sig_out, void* workspace, size_t workspace_bytes,
+                           void* stream) {
+    (void)y;        // mu - y = -e^2 alpha: the targets enter through alpha only
+    if (P < 1 || N < 1 || Np < NB || Np % NB != 0 || N > Np || S < 0 || S > MAX_S) { set_error("gpk_selfpredict_counts: P=%d N=%d Np=%d S=%d", P, N, Np, S); return 2; }
+    const StagedLayout SL = staged_layout(P, Np);
+    if (workspace == nullptr || workspace_bytes < SL.total) { set_error("gpk_selfpredict_counts: workspace too small"); return 3; }
+    cudaStream_t st = (cudaStream_t)stream;
+    set_stream(st);
+    char* ws = (char*)workspace;
+    if (staged_inverse(L, P, Np, ws, SL, active, st)) return 1;
+    const double* mat = (const double*)(ws + SL.mat);
+    // column norms of W (diag of K^-1); the alpha this kernel also forms from z goes to scratch
+    if (cudaMemsetAsync(ws + SL.z, 0, (size_t)P * Np * 8, st) != cudaSuccess) { set_error("memset z failed"); return 1; }
+    if (launch_colnorm_alpha(mat, Np, P, (const double*)(ws + SL.z), (double*)(ws + SL.cn), (double*)(ws + SL.alpha), active, st)) return 1;
+    return launch_counts(alpha, (const double*)(ws + SL.cn), e, sigma_vals, P, N, Np, S, counts_out, resid_out, sig_out, active, st);
+}
+
 size_t gpk_loss_workspace_bytes(int P, int N, int d) {
     if (N <= SMALL_N_MAX) return 256;
     size_t best = 0;                      // enough for any particle-group split (gpk_set_groups)

@@ -61,6 +61,9 @@ enum DiagMode { DIAG_WRITE_INVERSE = 0, DIAG_WRITE_FACTOR = 1 };
 int launch_diag_block(double* mat, int Np, int J, int P, double* dinv, double* dinvT, int T,
                       int* info, const unsigned char* active, int mode, cudaStream_t st);
 
+int launch_tri_inv_diag(const double* Lsrc, double* dst, int Np, int T, int P, double* dinv, double* dinvT, int* info,
+                        const unsigned char* active, cudaStream_t st);
+
 // gpk_gemm.cu
 int launch_syrk_update(double* mat, int Np, int T, int J, int P, const unsigned char* active, cudaStream_t st);
 int launch_trsm_panel(double* mat, int Np, int T, int J, int P, const double* dinv,

@@ -61,4 +61,58 @@ int launch_diag_block(double* mat, int Np, int J, int P, double* dinv, double* d
     return check_launch("k_diag_block");
 }
 
+// Staged interface only (gpk_fit_alpha_batched / gpk_selfpredict_counts): the diagonal blocks of an already computed
+// factor L (gpk_potrf_batched output) are inverted by forward substitution on the identity, one column per thread, and
+// written where the fused path's diagonal kernel leaves them: dst diagonal block, dinv, dinvT.
+constexpr int TI_TRI = NB * (NB + 1) / 2;                       // packed lower triangle: (r, c) at r (r + 1) / 2 + c
+constexpr size_t TI_SMEM_BYTES = (size_t)2 * TI_TRI * sizeof(double);
+
+__global__ void __launch_bounds__(NB, 1)
+k_tri_inv_diag(const double* __restrict__ Lsrc, double* __restrict__ dst, int Np, int T, double* __restrict__ dinv,
+               double* __restrict__ dinvT, int* __restrict__ info, const unsigned char* __restrict__ active) {
+    extern __shared__ double smem[];
+    double* Ls = smem;                        // L_JJ, packed
+    double* Xs = smem + TI_TRI;               // X = L_JJ^-1, packed
+    const int J = blockIdx.x, p = blockIdx.y;
+    if (active && !active[p]) return;
+    const int t = threadIdx.x;
+    const double* blk = Lsrc + (size_t)p * Np * Np + (size_t)J * NB * Np + (size_t)J * NB;
+    for (int idx = t; idx < NB * NB; idx += NB) {
+        const int r = idx >> 7, c = idx & (NB - 1);
+        if (c <= r) Ls[r * (r + 1) / 2 + c] = blk[(size_t)r * Np + c];
+    }
+    __syncthreads();
+    if (!(Ls[t * (t + 1) / 2 + t] > 0.0)) atomicCAS(&info[p], 0, J * NB + t + 1);
+    // column t of X: x_i = (delta_it - sum_{k=t}^{i-1} L_ik x_k) / L_ii; a thread reads only its own column of Xs
+    for (int i = t; i < NB; ++i) {
+        const double* Li = Ls + i * (i + 1) / 2;
+        double acc = (i == t) ? 1.0 : 0.0;
+        for (int k = t; k < i; ++k) acc = fma(-Li[k], Xs[k * (k + 1) / 2 + t], acc);
+        Xs[i * (i + 1) / 2 + t] = acc / Li[i];
+    }
+    __syncthreads();
+    double* dI = dinv + ((size_t)p * T + J) * NB * NB;
+    double* dT = dinvT + ((size_t)p * T + J) * NB * NB;
+    double* out = dst + (size_t)p * Np * Np + (size_t)J * NB * Np + (size_t)J * NB;
+    for (int idx = t; idx < NB * NB; idx += NB) {
+        const int r = idx >> 7, c = idx & (NB - 1);
+        const double x_rc = (c <= r) ? Xs[r * (r + 1) / 2 + c] : 0.0;
+        dI[idx] = x_rc;
+        dT[idx] = (r <= c) ? Xs[c * (c + 1) / 2 + r] : 0.0;
+        out[(size_t)r * Np + c] = x_rc;
+    }
+}
+
+int launch_tri_inv_diag(const double* Lsrc, double* dst, int Np, int T, int P, double* dinv, double* dinvT, int* info,
+                        const unsigned char* active, cudaStream_t st) {
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(k_tri_inv_diag, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TI_SMEM_BYTES);
+        if (e != cudaSuccess) { set_error("k_tri_inv_diag smem attr: %s", cudaGetErrorString(e)); return 1; }
+        configured = true;
+    }
+    k_tri_inv_diag<<<dim3(T, P), NB, TI_SMEM_BYTES, st>>>(Lsrc, dst, Np, T, dinv, dinvT, info, active);
+    return check_launch("k_tri_inv_diag");
+}
+
 }  // namespace gpk

@@ -143,6 +143,59 @@ def potrf_batched(k):
     return np.tril(dk.cpu().numpy()), info.cpu().numpy()
 
 
+def _pad_factors(L, n):
+    """(P,n,n) host factors -> (P,Np,Np) device batch with identity in the padding (what gpk_potrf_batched leaves)."""
+    L = _f64(L)
+    p = L.shape[0]
+    n_pad = int(_lib.load().gpk_padded_n(n))
+    full = np.zeros((p, n_pad, n_pad))
+    full[:, :n, :n] = np.tril(L[:, :n, :n])
+    idx = np.arange(n, n_pad)
+    full[:, idx, idx] = 1.0
+    return to_dev(full), n_pad
+
+
+def fit_alpha_batched(L, y):
+    """Staged fit (SURVEY 8b `gpk_fit_alpha_batched`): alpha_p = L_p^-T (L_p^-1 y) for a batch of Cholesky factors
+    (P,N,N), GP_func.py:24.  Returns (P,N)."""
+    lib = _lib.load()
+    y = _f64(y)
+    n = y.shape[0]
+    dl, n_pad = _pad_factors(L, n)
+    p = dl.shape[0]
+    alpha = torch.zeros((p, n_pad), dtype=torch.float64, device=device())
+    ws = workspace(lib.gpk_staged_workspace_bytes(p, n_pad), "staged")
+    dy = to_dev(y)
+    st = lib.gpk_fit_alpha_batched(dl.data_ptr(), dy.data_ptr(), p, n, n_pad, alpha.data_ptr(), ws.data_ptr(),
+                                   ws.numel(), _stream())
+    _lib.check(st, "gpk_fit_alpha_batched")
+    return alpha[:, :n].cpu().numpy()
+
+
+def selfpredict_counts(L, alpha, y, e, sigma_vals, active=None):
+    """Staged calibration counts (SURVEY 8b `gpk_selfpredict_counts`) from factors (P,N,N) and alpha (P,N):
+    returns (counts (P,S) int32, mu - y (P,N), sd (P,N)), find_len_scales.py:159-163 before the mean."""
+    lib = _lib.load()
+    y, e, sigma_vals, alpha = _f64(y), _f64(e), _f64(sigma_vals), _f64(alpha)
+    n, s = y.shape[0], sigma_vals.shape[0]
+    dl, n_pad = _pad_factors(L, n)
+    p = dl.shape[0]
+    dev = device()
+    da = torch.zeros((p, n_pad), dtype=torch.float64, device=dev)
+    da[:, :n] = to_dev(alpha)
+    dact = to_dev(np.asarray(active, dtype=np.uint8)) if active is not None else None
+    counts = torch.empty((p, s), dtype=torch.int32, device=dev)
+    resid = torch.empty((p, n), dtype=torch.float64, device=dev)
+    sd = torch.empty((p, n), dtype=torch.float64, device=dev)
+    ws = workspace(lib.gpk_staged_workspace_bytes(p, n_pad), "staged")
+    dy, de, dsig = to_dev(y), to_dev(e), to_dev(sigma_vals)           # named: the buffers must outlive the call
+    st = lib.gpk_selfpredict_counts(dl.data_ptr(), da.data_ptr(), dy.data_ptr(), de.data_ptr(),
+                                    dsig.data_ptr(), dact.data_ptr() if dact is not None else None, p, n, n_pad,
+                                    s, counts.data_ptr(), resid.data_ptr(), sd.data_ptr(), ws.data_ptr(), ws.numel(), _stream())
+    _lib.check(st, "gpk_selfpredict_counts")
+    return counts.cpu().numpy(), resid.cpu().numpy(), sd.cpu().numpy()
+
+
 # ------------------------------------------------------------------------------------ (b)
 class LossContext:
     """Device-resident training set + sigma grid for repeated swarm evaluations (one per PSO

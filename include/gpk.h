@@ -49,6 +49,18 @@ GPK_API size_t gpk_potrf_workspace_bytes(int P, int Np);
 GPK_API int gpk_potrf_batched(double* K_inout, int P, int Np, int* info, void* workspace, size_t workspace_bytes,
                       void* stream);
 
+/* (b) staged form of the fit / self-prediction, on factors left by gpk_potrf_batched ([P][Np][Np], padding =
+ *     identity): alpha = L^-T (L^-1 y), GP_func.py:24, and the calibration counts of find_len_scales.py:159-163 from
+ *     (L, alpha).  gpk_loss_batched is the fused form of cov + potrf + these two and is what the PSO calls; these entry
+ *     points exist for callers that keep the factor.  alpha is [P][Np] (row stride Np, entries >= N are 0).  Native FP64. */
+GPK_API size_t gpk_staged_workspace_bytes(int P, int Np);
+GPK_API int gpk_fit_alpha_batched(const double* L, const double* y, int P, int N, int Np, double* alpha_out,
+                          void* workspace, size_t workspace_bytes, void* stream);
+GPK_API int gpk_selfpredict_counts(const double* L, const double* alpha, const double* y, const double* e,
+                           const double* sigma_vals, const unsigned char* active, int P, int N, int Np, int S,
+                           int* counts_out, double* resid_out, double* sig_out, void* workspace,
+                           size_t workspace_bytes, void* stream);
+
 /* (b) the PSO hot call: evaluate_loss for a whole swarm, find_len_scales.py:154-163 up to the counts.
  *     counts[p][s] = #{ i : |mu_i - y_i| / max(sd_i * sigma_vals[s], 1e-12) <= 1 } (int32); the host finishes
  *     :163-177 in NumPy.  active[p] == 0 marks an out-of-bounds particle (find_len_scales.py:156): it is not

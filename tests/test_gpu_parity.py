@@ -76,6 +76,47 @@ def test_potrf_not_positive_definite(mods):
     assert info[0] == 0 and info[1] == 201
 
 
+@pytest.mark.parametrize("n,d,p", [(128, 2, 2), (300, 3, 3), (1000, 2, 2)])
+def test_staged_fit_and_selfpredict(mods, n, d, p):
+    """The staged C-ABI entry points (cov -> potrf -> fit_alpha -> selfpredict_counts) reproduce the fused
+    gpk_loss_batched and the checker: alpha against a LAPACK solve, counts / residual / sd against the oracle."""
+    eng = mods["engine"]
+    x, y, e = orc.synthetic_problem(n, d, n)
+    pos, lo, hi = orc.synthetic_particles(x, p, n)
+    s, ex = orc.sigma_grid()
+    k = eng.cov_batched(x, x, pos, e)
+    n_pad = -(-n // 128) * 128
+    kp = np.zeros((p, n_pad, n_pad))
+    kp[:, :n, :n] = k
+    kp[:, np.arange(n, n_pad), np.arange(n, n_pad)] = 1.0
+    L, info = eng.potrf_batched(kp)
+    assert not info.any()
+    L = L[:, :n, :n]
+    alpha = eng.fit_alpha_batched(L, y)
+    counts, resid, sd = eng.selfpredict_counts(L, alpha, y, e, s, active=np.array([1] * (p - 1) + [0]))
+    fused = eng.LossContext(x, y, e, s)
+    prev = eng.get_precision()
+    eng.set_precision("fp64")
+    try:
+        c_f, _i, r_f, sd_f = fused.counts(pos, want_detail=True)
+    finally:
+        eng.set_precision(prev)
+    for q in range(p):
+        a_ref = np.linalg.solve(k[q], y)
+        np.testing.assert_allclose(alpha[q], a_ref, rtol=1e-8, atol=1e-9 * np.abs(a_ref).max())
+        if q == p - 1:
+            assert not counts[q].any()                       # inactive particle: zero counts, nothing else defined
+            continue
+        c_ref, r_ref, sd_ref, pulls = orc.calibration_counts(pos[q], x, y, e, s)
+        np.testing.assert_allclose(resid[q], r_ref, rtol=1e-8, atol=1e-11)
+        np.testing.assert_allclose(sd[q], sd_ref, rtol=1e-8)
+        np.testing.assert_allclose(resid[q], r_f[q], rtol=1e-9, atol=1e-13)
+        np.testing.assert_allclose(sd[q], sd_f[q], rtol=1e-10)
+        if np.min(np.abs(np.abs(pulls) - 1)) > 1e-8:
+            np.testing.assert_array_equal(counts[q], c_ref)
+            np.testing.assert_array_equal(counts[q], c_f[q])
+
+
 # ------------------------------------------------------------------ (b) loss
 def _loss_check(mods, c, name):
     s, ex = orc.sigma_grid()
