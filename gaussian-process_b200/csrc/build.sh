@@ -13,10 +13,12 @@ for f in gpk_api gpk_cov gpk_diag gpk_gemm gpk_loss gpk_oz gpk_surface; do
   fi
   objs+=(build/$f.o)
 done
-if [ ! -f build/gpk_csv.o ] || [ gpk_csv.cpp -nt build/gpk_csv.o ] || [ ../../include/gpk.h -nt build/gpk_csv.o ]; then
-  $NVCC $FLAGS "$@" -x cu -c gpk_csv.cpp -o build/gpk_csv.o &
-fi
-objs+=(build/gpk_csv.o)
+for f in gpk_csv gpk_finish; do
+  if [ ! -f build/$f.o ] || [ $f.cpp -nt build/$f.o ] || [ ../../include/gpk.h -nt build/$f.o ]; then
+    $NVCC $FLAGS "$@" -x cu -c $f.cpp -o build/$f.o &
+  fi
+  objs+=(build/$f.o)
+done
 wait
 $NVCC -shared -gencode arch=compute_100a,code=sm_100a -o $OUT "${objs[@]}"
 echo "built $(readlink -f $OUT)"

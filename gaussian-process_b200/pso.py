@@ -31,13 +31,28 @@ def out_of_bounds_mask(positions, lower, upper):
     return np.any(positions <= lower, axis=1) | np.any(positions >= upper, axis=1)
 
 
-def finish_losses(counts, n_points, positions, sigma_vals, expected, lower, upper, oob):
+def finish_losses(counts, n_points, positions, sigma_vals, expected, lower, upper, oob, work=None, wasserstein=None):
     """counts (P,S) -> PSO scores (P,), the arithmetic of find_len_scales.py:163-177 and the sign
-    flip of :182, vectorised over particles (row-wise identical to the scalar expressions)."""
+    flip of :182, vectorised over particles (row-wise identical to the scalar expressions).
+    `work` = (d_sigma (1,S-1), buffer (P,S), buffer (P,S-1)), optional, for the PSO loop: np.trapz recomputes
+    diff(sigma_vals) and allocates five (P,S) temporaries per call; with `work` the integral is formed by trapz's own
+    expression `(d * (y[1:] + y[:-1]) / 2.0).sum(-1)`, same operations in the same order, in preallocated storage."""
     positions = np.atleast_2d(positions)
-    measured = counts.astype(np.float64) / n_points                       # np.mean(bool, axis=0)
-    diff = np.abs(measured - expected[None, :])
-    wasserstein = np.trapz(diff, sigma_vals, axis=1)
+    if wasserstein is not None:
+        pass                                       # formed by libgpk's one-pass host routine (SwarmLoss._integral)
+    elif work is None:
+        measured = counts.astype(np.float64) / n_points                   # np.mean(bool, axis=0)
+        diff = np.abs(measured - expected[None, :])
+        wasserstein = np.trapz(diff, sigma_vals, axis=1)
+    else:
+        d_sigma, a, b = work
+        np.divide(counts, float(n_points), out=a)                         # int32 -> float64, then the division
+        np.subtract(a, expected[None, :], out=a)
+        np.abs(a, out=a)
+        np.add(a[:, 1:], a[:, :-1], out=b)
+        np.multiply(d_sigma, b, out=b)
+        np.divide(b, 2.0, out=b)
+        wasserstein = b.sum(-1)
     span = upper - lower
     with np.errstate(invalid="ignore", divide="ignore"):     # degenerate (zero-range) dims are always out of bounds
         d_lo = (positions - lower) / span
@@ -54,22 +69,54 @@ class SwarmLoss:
     def __init__(self, x_known, y_known, e_known, sigma_vals, expected_percents, lower_bounds, upper_bounds):
         self.ctx = engine.LossContext(x_known, y_known, e_known, sigma_vals)
         self.n = np.asarray(x_known).shape[1]
-        self.sigma_vals = np.asarray(sigma_vals, dtype=np.float64)
-        self.expected = np.asarray(expected_percents, dtype=np.float64)
+        self.sigma_vals = np.ascontiguousarray(sigma_vals, dtype=np.float64)
+        self.expected = np.ascontiguousarray(expected_percents, dtype=np.float64)
         self.lower = np.asarray(lower_bounds, dtype=np.float64)
         self.upper = np.asarray(upper_bounds, dtype=np.float64)
         self.evaluations = 0
+        self._d_sigma = np.diff(self.sigma_vals).reshape(1, -1)
+        self._work = None
+        self._fast = None                  # None: not yet checked against NumPy; True / False afterwards
+        self._table = np.arange(self.n + 1, dtype=np.int32).astype(np.float64) / self.n      # counts / n, every value
+        self._scratch = np.empty(2 * self.sigma_vals.shape[0])
+
+    def _integral(self, counts):
+        """np.trapz(|counts / n - expected|, sigma_vals, axis=1) by libgpk's host routine (gpk_finish_wasserstein: NumPy's
+        operation order and pairwise summation in one pass).  Verified against the NumPy expressions on the first swarm
+        evaluation of this object; any difference switches it off for good."""
+        if self._fast is False or counts.dtype != np.int32 or not counts.flags.c_contiguous:
+            return None
+        import ctypes as C
+        lib = engine._lib.load()
+        out = np.empty(counts.shape[0])
+        vp = C.c_void_p
+        st = lib.gpk_finish_wasserstein(vp(counts.ctypes.data), counts.shape[0], counts.shape[1], vp(self._table.ctypes.data),
+                                        self.n, vp(self.expected.ctypes.data), vp(self._d_sigma.ctypes.data),
+                                        vp(self._scratch.ctypes.data), vp(out.ctypes.data))
+        if st != 0:
+            self._fast = False
+            return None
+        if self._fast is None:
+            ref = np.trapz(np.abs(counts.astype(np.float64) / self.n - self.expected[None, :]), self.sigma_vals, axis=1)
+            self._fast = bool(np.array_equal(ref, out))
+            if not self._fast:
+                return None
+        return out
 
     def __call__(self, positions):
         positions = np.atleast_2d(np.asarray(positions, dtype=np.float64))
         oob = out_of_bounds_mask(positions, self.lower, self.upper)
         if np.all(oob):
             return np.full(positions.shape[0], OOB_SCORE)
-        counts, info = self.ctx.counts(positions, active=~oob)
+        counts, info = self.ctx.counts_view(positions, active=~oob)         # views: consumed before the next evaluation
         if np.any(info != 0):
             raise np.linalg.LinAlgError("Matrix is not positive definite")   # GP_func.py:22 behaviour
         self.evaluations += positions.shape[0]
-        return finish_losses(counts, self.n, positions, self.sigma_vals, self.expected, self.lower, self.upper, oob)
+        p, s = counts.shape
+        if self._work is None or self._work[1].shape[0] != p:
+            self._work = (self._d_sigma, np.empty((p, s)), np.empty((p, s - 1)))
+        return finish_losses(counts, self.n, positions, self.sigma_vals, self.expected, self.lower, self.upper, oob,
+                             work=self._work, wasserstein=self._integral(counts))
 
 
 def evaluate_loss_batch(positions, x_known, y_known, e_known, sigma_vals, expected_percents, lower_bounds,

@@ -145,6 +145,13 @@ GPK_API size_t gpk_csv_bound(long long rows, int cols);
 GPK_API long long gpk_csv_format_f64(const double* table, long long rows, int cols, long long ld, char* out,
                                      size_t out_cap, int threads);
 
+/* HOST function.  Loss finish of find_len_scales.py:163-166 for P particles: W_p = np.trapz(|counts[p] / n_points - expected|,
+ * sigma_vals) with d_sigma = diff(sigma_vals) ([S-1]) and measured_of[k] = k / n_points for k = 0..n_points (the caller's
+ * table of the quotients); NumPy's operation order and pairwise summation, one pass per particle.  scratch: 2 S doubles.
+ * Returns 0, 2 for bad arguments, 3 for a count outside 0..n_points. */
+GPK_API int gpk_finish_wasserstein(const int* counts, long long P, int S, const double* measured_of, int n_points,
+                           const double* expected, const double* d_sigma, double* scratch, double* out);
+
 /* Measurement aid (bench.py roofline): per-kernel-class device time by events recorded after every launch
  * on `stream` between begin and end.  Not thread-safe; name_out is a HOST buffer. */
 GPK_API int gpk_timing_begin(void* stream);

@@ -90,3 +90,29 @@ def test_synthetic_generators_equal_the_oracles():
         for a, b in zip(synthetic.particles(x, 7, seed), orc.synthetic_particles(x, 7, seed)):
             np.testing.assert_array_equal(a, b)
     np.testing.assert_array_equal(synthetic.surface_table(500, 4, seed=3), orc.synthetic_surface_table(500, 4, seed=3))
+
+
+def test_host_finish_equals_numpy_trapz():
+    """libgpk's one-pass host finish (gpk_finish_wasserstein) returns the bits of np.trapz(|counts / n - expected|, sigma)
+    (find_len_scales.py:163-166): random and monotone count rows, every count range the path meets, grid lengths around
+    the split points of NumPy's pairwise summation."""
+    import ctypes as C
+    from gaussian_process_b200 import _lib, pso
+    lib = _lib.load()
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)      # noqa: E731
+    rng = np.random.default_rng(3)
+    for S in (2, 3, 8, 9, 17, 128, 129, 130, 137, 257, 513, 999, 1000):
+        sv = np.linspace(0.001, 3, S)
+        ex = pso.sigma_to_percent(sv)
+        d = np.diff(sv)
+        for n in (1, 2, 21, 100, 4096, 8192):
+            for mono in (False, True):
+                counts = rng.integers(0, n + 1, (17, S))
+                counts = (np.sort(counts, axis=1) if mono else counts).astype(np.int32)
+                table = np.arange(n + 1, dtype=np.int32).astype(np.float64) / n
+                out, scratch = np.empty(17), np.empty(2 * S)
+                assert lib.gpk_finish_wasserstein(vp(counts), 17, S, vp(table), n, vp(ex), vp(d), vp(scratch), vp(out)) == 0
+                ref = np.trapz(np.abs(counts.astype(np.float64) / n - ex[None, :]), sv, axis=1)
+                np.testing.assert_array_equal(out, ref)
+    bad = np.full((1, 4), 7, dtype=np.int32)
+    assert lib.gpk_finish_wasserstein(vp(bad), 1, 4, vp(np.zeros(4)), 3, vp(np.zeros(4)), vp(np.zeros(3)), vp(np.empty(8)), vp(np.empty(1))) == 3

@@ -9,6 +9,7 @@ for f in gpk_api gpk_cov gpk_diag gpk_gemm gpk_loss gpk_oz gpk_surface; do
   $NVCC $FLAGS -c $f.cu -o build/prof/$f.o &
 done
 $NVCC $FLAGS -x cu -c gpk_csv.cpp -o build/prof/gpk_csv.o &
+$NVCC $FLAGS -x cu -c gpk_finish.cpp -o build/prof/gpk_finish.o &
 wait
 $NVCC -shared -gencode arch=compute_100a,code=sm_100a -o ../../tools/libgpk_prof.so build/prof/*.o
 echo "built tools/libgpk_prof.so"
