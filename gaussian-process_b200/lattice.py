@@ -38,7 +38,16 @@ def _snap(value, res):
 
 def _sort_unique(a):
     """sorted(set(map(tuple, a))) (convex_hull.py:29-35): rows de-duplicated, lexicographic order."""
-    return np.unique(np.asarray(a, dtype=np.float64), axis=0)
+    a = np.asarray(a, dtype=np.float64)
+    if a.ndim != 2 or a.shape[0] < 2:
+        return np.unique(a, axis=0)
+    # stable lexicographic sort + neighbour comparison: the rows np.unique(a, axis=0) returns, without its
+    # structured-dtype sort (4x faster at 4e4 rows); of rows that compare equal the first one inserted is kept,
+    # as a Python set does
+    s = a[np.lexsort(a.T[::-1])]
+    keep = np.ones(s.shape[0], dtype=bool)
+    keep[1:] = np.any(s[1:] != s[:-1], axis=1)
+    return np.ascontiguousarray(s[keep])
 
 
 def _run_lengths(k0, cur0, end, res):
