@@ -4,7 +4,9 @@ The path has no data-path collective except one tiny exchange per PSO iteration:
 evaluates its contiguous slice of the swarm and the per-particle losses are all-gathered (P float64,
 2 KB at P=256 -- latency bound; NCCL over NVLink on GPUs, gloo in the CPU tests).  Every rank then
 runs the identical host PSO update from the identical seeded RNG stream, so positions never travel
-(SURVEY 8e).  Experiments and grid tiles are embarrassingly parallel: `shard_slice` only."""
+(SURVEY 8e).  Experiments, grid tiles and surface rows are embarrassingly parallel: contiguous `shard_slice` blocks per
+rank; `gather_rows` reassembles per-point results (16 B per grid point), `sharded_prob_surface` keeps the surface output
+sharded and exchanges only the per-rank numbers of emitting rows (one int64 each) for the compaction offsets."""
 import numpy as np
 import torch
 import torch.distributed as dist
@@ -95,3 +97,71 @@ class ShardedSwarm:
         lo, hi = shard_slice(n, rank, size)
         local = self.fn(positions[lo:hi]) if hi > lo else np.zeros(0)
         return all_gather_losses(local, n, self.group)
+
+
+def gather_rows(local, n_total, group=None):
+    """local: this rank's contiguous block of rows (shard_slice order) of a float64 array (rows, ...) -> the full
+    (n_total, ...) array on every rank.  One fixed-width all-gather (blocks padded to the widest one)."""
+    rank, size = dist_world()
+    local = np.ascontiguousarray(local, dtype=np.float64)
+    if size == 1:
+        return local
+    tail = local.shape[1:]
+    per_row = int(np.prod(tail)) if tail else 1
+    width = -(-n_total // size)
+    buf = torch.zeros(width * per_row, dtype=torch.float64)
+    buf[:local.size] = torch.from_numpy(local.reshape(-1))
+    if dist.get_backend(group) == "nccl":
+        buf = buf.cuda()
+    out = torch.empty(size * width * per_row, dtype=torch.float64, device=buf.device)
+    dist.all_gather_into_tensor(out, buf, group=group)
+    out = out.cpu().numpy().reshape(size, width, *tail)
+    parts = []
+    for r in range(size):
+        lo, hi = shard_slice(n_total, r, size)
+        parts.append(out[r, :hi - lo])
+    return np.concatenate(parts)
+
+
+def sharded_predict(predict_fn, x_fit, group=None):
+    """Grid tiles over the ranks: predict_fn(x_fit_block (d,m)) -> (mean (m,), sd (m,)) is called on this
+    rank's contiguous block of grid points; the full (mean, sd) come back on every rank.  The fit is replicated, not
+    broadcast: refitting costs 20 ms at N=4096, less than moving the 134 MB factor."""
+    rank, size = dist_world()
+    x_fit = np.asarray(x_fit, dtype=np.float64)
+    m = x_fit.shape[1]
+    lo, hi = shard_slice(m, rank, size)
+    if hi > lo:
+        mu, sd = predict_fn(np.ascontiguousarray(x_fit[:, lo:hi]))
+        both = np.stack([np.asarray(mu, dtype=np.float64).reshape(-1), np.asarray(sd, dtype=np.float64).reshape(-1)], axis=1)
+    else:
+        both = np.zeros((0, 2))
+    full = gather_rows(both, m, group)
+    return np.ascontiguousarray(full[:, 0]), np.ascontiguousarray(full[:, 1])
+
+
+def surface_offsets(n_local, group=None):
+    """Compaction of the surface output across ranks: all-gather of the per-rank numbers of emitting rows (one int64
+    each) and their exclusive prefix sum.  Returns (offset of this rank's block, total)."""
+    rank, size = dist_world()
+    if size == 1:
+        return 0, int(n_local)
+    mine = torch.tensor([int(n_local)], dtype=torch.int64)
+    if dist.get_backend(group) == "nccl":
+        mine = mine.cuda()
+    every = torch.empty(size, dtype=torch.int64, device=mine.device)
+    dist.all_gather_into_tensor(every, mine, group=group)
+    every = every.cpu().numpy()
+    return int(every[:rank].sum()), int(every.sum())
+
+
+def sharded_prob_surface(surface_fn, table, group=None):
+    """Surface rows over the ranks: surface_fn(table_block) -> (row_index (k,), y (k,points), p (k,points))
+    of the block's emitting rows.  This rank reduces rows [lo, hi); the outputs stay sharded (config C5 emits 27 GB).
+    Returns (offset, total, global row_index, y, p): this rank's block occupies rows offset .. offset + k of the
+    compacted result of `total` rows."""
+    rank, size = dist_world()
+    lo, hi = shard_slice(table.shape[0], rank, size)
+    idx, y, p = surface_fn(table[lo:hi])
+    offset, total = surface_offsets(len(idx), group)
+    return offset, total, np.asarray(idx, dtype=np.int64) + lo, y, p

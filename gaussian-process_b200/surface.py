@@ -51,23 +51,32 @@ def surface_frame(df, ndims, points=POINTS):
 STREAM_ROWS = 1 << 15             # merged rows per CSV block of the streaming writer (3.3 M output rows, ~160 MB of float64)
 
 
-def write_surface_csv(df, ndims, output_file, points=POINTS, rows_per_pass=None):
+def write_surface_csv(df, ndims, output_file, points=POINTS, rows_per_pass=None, passes_fn=None, row_range=None,
+                      header=True):
     """The file generate_prob_surf writes (:80-84), produced pass by pass: each pass of the GPU reduction is expanded to
     its long-format block (coords repeated `points` times, quantity, prob), formatted by libgpk's threaded CSV
     formatter and appended, while the next pass runs on the device.  Host memory stays bounded by the pass size, so the
-    64^4-row configuration (1.7e9 output rows) never exists as one frame.  Returns the number of output rows."""
+    64^4-row configuration (1.7e9 output rows) never exists as one frame.  Returns the number of output rows.
+    `row_range` = (lo, hi) restricts the file to those merged rows and `header=False` drops the header line (the parts
+    of write_surface_csv_sharded); `passes_fn` replaces engine.prob_surface_passes (tests)."""
     columns = df.columns[:ndims].tolist() + ["quantity", "prob"]
-    header = tables.plain_header(columns)
-    if header is None:                                     # column names that need quoting: let pandas write the file
+    header_line = tables.plain_header(columns)
+    if header_line is None:                                # column names that need quoting: let pandas write the file
+        if row_range is not None:
+            raise ValueError("column names that need CSV quoting are not supported by the sharded writer")
         out = surface_frame(df, ndims, points)
         out.to_csv(output_file, index=False)
         return len(out)
     values = df.to_numpy(dtype=np.float64)
+    if row_range is not None:
+        values = values[row_range[0]:row_range[1]]
     coords, payload = values[:, :ndims], values[:, ndims:]
+    passes_fn = passes_fn or engine.prob_surface_passes
     n_rows = 0
     with open(output_file, "wb") as f:
-        f.write(header.encode("utf-8"))
-        for idx, y, p in engine.prob_surface_passes(payload, points, rows_per_pass):
+        if header:
+            f.write(header_line.encode("utf-8"))
+        for idx, y, p in passes_fn(payload, points, rows_per_pass):
             for b0 in range(0, idx.shape[0], STREAM_ROWS):
                 sel = idx[b0:b0 + STREAM_ROWS]
                 k = sel.shape[0]
@@ -80,10 +89,45 @@ def write_surface_csv(df, ndims, output_file, points=POINTS, rows_per_pass=None)
     return n_rows
 
 
+def write_surface_csv_sharded(df, ndims, output_file, points=POINTS, rows_per_pass=None, passes_fn=None):
+    """The same file written by all ranks of the process group (surface rows): rank r reduces and formats the
+    contiguous block shard_slice(len(df), r, size) of the merged rows into `<output_file>.part<r>` (rank 0's part carries
+    the header), then rank 0 concatenates the parts in rank order: the bytes are those of the single-process writer,
+    because every output row depends on its own merged row only.  The per-rank output row counts are exchanged
+    (sharding.surface_offsets) and the total is returned on every rank."""
+    import shutil
+    from . import sharding
+    rank, size = sharding.dist_world()
+    if size == 1:
+        return write_surface_csv(df, ndims, output_file, points, rows_per_pass, passes_fn)
+    import torch.distributed as dist
+    lo, hi = sharding.shard_slice(len(df), rank, size)
+    part = f"{output_file}.part{rank}"
+    n_local = write_surface_csv(df, ndims, part, points, rows_per_pass, passes_fn, row_range=(lo, hi), header=(rank == 0))
+    _offset, total = sharding.surface_offsets(n_local)
+    dist.barrier()
+    if rank == 0:
+        with open(output_file, "wb") as out:
+            for r in range(size):
+                with open(f"{output_file}.part{r}", "rb") as src:
+                    shutil.copyfileobj(src, out, 1 << 24)
+                os.remove(f"{output_file}.part{r}")
+    dist.barrier()
+    return total
+
+
 def generate_prob_surf(df, ndims, options_path="options.yaml"):
-    """Drop-in for calc_prob_surf.generate_prob_surf (:39-88): same prints, same CSV."""
-    print("Calculating Probability")
+    """Drop-in for calc_prob_surf.generate_prob_surf (:39-88): same prints, same CSV.  Under an initialised process
+    group the merged rows shard across the ranks (every rank calls this with the same table, as main.py does)."""
+    from . import sharding
+    rank, size = sharding.dist_world()
+    if rank == 0:
+        print("Calculating Probability")
     output_file = resolve_output_path(options_path)
-    write_surface_csv(df, ndims, output_file)              # the bytes of to_csv(index=False), :84
-    print(f"Probability results written to {output_file}")
+    if size > 1:
+        write_surface_csv_sharded(df, ndims, output_file)
+    else:
+        write_surface_csv(df, ndims, output_file)          # the bytes of to_csv(index=False), :84
+    if rank == 0:
+        print(f"Probability results written to {output_file}")
     return

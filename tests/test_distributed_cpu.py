@@ -66,3 +66,76 @@ def test_sharded_swarm_world2(tmp_path):
                              trace=trace, distributed=False)
     assert np.array_equal(best, r0["best"])
     assert np.array_equal(np.array([t[0] for t in trace]), r0["pos"])
+
+
+def _rows_worker(rank, size, port, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(size))
+    sys.path.insert(0, ROOT)
+    import pandas as pd
+    import torch.distributed as dist
+    from oracle import gp_oracle as orc
+    from gaussian_process_b200 import sharding, surface
+    dist.init_process_group("gloo", rank=rank, world_size=size)
+    rng = np.random.default_rng(5)
+    # 1) ragged row gather
+    full = rng.random((7, 3))
+    lo, hi = sharding.shard_slice(7, rank, size)
+    got = sharding.gather_rows(full[lo:hi], 7)
+    # 2) grid tiles: the checker's GP as the per-rank predictor
+    x, y, e = orc.synthetic_problem(30, 2, 1)
+    grid = rng.random((2, 101))
+    ls = np.array([0.3, 0.4])
+    calls = []
+
+    def predict(block):
+        calls.append(block.shape[1])
+        return orc.gp(x, y, e, block, ls)
+
+    mu, sd = sharding.sharded_predict(predict, grid)
+    # 3) surface rows: offsets of the compacted output + the sharded CSV writer
+    t = orc.synthetic_surface_table(41, 3, seed=2, p_gap=0.7)
+    off, total, idx, yy, pp = sharding.sharded_prob_surface(lambda blk: orc.prob_surface_rows(blk), t)
+    coords = rng.random((41, 2))
+    df = pd.DataFrame(np.hstack([coords, t]), columns=["a", "b"] + [f"c{i}" for i in range(t.shape[1])])
+
+    def passes(payload, points, rows_per_pass):
+        yield orc.prob_surface_rows(payload, points)
+
+    n_out = surface.write_surface_csv_sharded(df, 2, os.path.join(out_dir, "surf.csv"), passes_fn=passes)
+    np.savez(os.path.join(out_dir, f"rows{rank}.npz"), got=got, full=full, mu=mu, sd=sd, calls=np.array(calls), off=off,
+             total=total, idx=idx, yy=yy, pp=pp, n_out=n_out)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_sharded_grid_and_surface_rows_world2(tmp_path):
+    """Grid tiles and surface rows over two ranks (gloo): gathered predictions, compaction offsets and the sharded CSV
+    writer equal the single-process results."""
+    port = 31500 + os.getpid() % 2000
+    mp.spawn(_rows_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    r0, r1 = np.load(tmp_path / "rows0.npz"), np.load(tmp_path / "rows1.npz")
+    assert np.array_equal(r0["got"], r0["full"]) and np.array_equal(r1["got"], r0["full"])
+    sys.path.insert(0, ROOT)
+    import pandas as pd
+    from oracle import gp_oracle as orc
+    from gaussian_process_b200 import surface
+    rng = np.random.default_rng(5)
+    rng.random((7, 3))
+    x, y, e = orc.synthetic_problem(30, 2, 1)
+    grid = rng.random((2, 101))
+    mu, sd = orc.gp(x, y, e, grid, np.array([0.3, 0.4]))
+    for r in (r0, r1):
+        np.testing.assert_allclose(r["mu"], mu, rtol=1e-13, atol=1e-15)      # same code on a block of the columns
+        np.testing.assert_allclose(r["sd"], sd, rtol=1e-13)
+    assert r0["calls"].tolist() == [51] and r1["calls"].tolist() == [50]
+    t = orc.synthetic_surface_table(41, 3, seed=2, p_gap=0.7)
+    idx, yy, pp = orc.prob_surface_rows(t)
+    assert int(r0["off"]) == 0 and int(r1["off"]) == len(r0["idx"]) and int(r0["total"]) == int(r1["total"]) == len(idx)
+    assert np.array_equal(np.concatenate([r0["idx"], r1["idx"]]), idx)
+    assert np.array_equal(np.concatenate([r0["yy"], r1["yy"]]), yy) and np.array_equal(np.concatenate([r0["pp"], r1["pp"]]), pp)
+    coords = rng.random((41, 2))
+    df = pd.DataFrame(np.hstack([coords, t]), columns=["a", "b"] + [f"c{i}" for i in range(t.shape[1])])
+    n = surface.write_surface_csv(df, 2, tmp_path / "single.csv", passes_fn=lambda payload, points, rpp: iter([orc.prob_surface_rows(payload, points)]))
+    assert (tmp_path / "single.csv").read_bytes() == (tmp_path / "surf.csv").read_bytes()
+    assert int(r0["n_out"]) == int(r1["n_out"]) == n == 100 * len(idx)
+    assert not list(tmp_path.glob("surf.csv.part*"))

@@ -87,3 +87,22 @@ def test_main_workflow_end_to_end(tmp_path, monkeypatch):
     np.testing.assert_array_equal(surf[["energy", "angle"]].to_numpy(), np.repeat(df.to_numpy()[idx, :nd], 100, axis=0))
     np.testing.assert_allclose(surf["quantity"].to_numpy(), ys.reshape(-1), rtol=1e-12, atol=1e-300)
     np.testing.assert_allclose(surf["prob"].to_numpy(), ps.reshape(-1), rtol=1e-9, atol=1e-15)
+
+
+def test_sharded_predict_and_surface_single_rank(tmp_path):
+    """The grid-tile / surface-row sharding entry points on one rank (no process group) reduce to the plain calls."""
+    from oracle import gp_oracle as orc
+    from gaussian_process_b200 import engine, sharding
+    x, y, e = orc.synthetic_problem(200, 2, 2)
+    grid = np.random.default_rng(0).random((2, 333))
+    ls = np.array([0.3, 0.5])
+    fit = engine.GPFit(x, y, e, ls)
+    mu, sd = sharding.sharded_predict(fit.predict, grid)
+    mu_r, sd_r = orc.gp(x, y, e, grid, ls)
+    np.testing.assert_allclose(mu, mu_r, rtol=1e-9, atol=1e-12)
+    np.testing.assert_allclose(sd, sd_r, rtol=1e-9)
+    t = orc.synthetic_surface_table(500, 4, seed=1)
+    off, total, idx, yy, pp = sharding.sharded_prob_surface(engine.prob_surface, t)
+    idx_r, yy_r, pp_r = orc.prob_surface_rows(t)
+    assert off == 0 and total == len(idx_r) and np.array_equal(idx, idx_r) and np.array_equal(yy, yy_r)
+    np.testing.assert_allclose(pp, pp_r, rtol=1e-9, atol=1e-15)

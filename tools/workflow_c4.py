@@ -78,7 +78,12 @@ gp_fit.GP = timed("GP fit + predict", gp_fit.GP)
 gp_fit.merge_outer = timed("outer merge", gp_fit.merge_outer)
 gp_fit.write_csv = timed("CSV of the merged table", gp_fit.write_csv)
 
-with tempfile.TemporaryDirectory() as tmp:
+holder = tempfile.TemporaryDirectory() if rank == 0 else None
+shared = [holder.name if rank == 0 else None]
+if world > 1:
+    dist.broadcast_object_list(shared, src=0)            # one working directory for all ranks (sharded CSV parts)
+if True:
+    tmp = shared[0]
     os.chdir(tmp)
     # warm-up on a small problem (module load, workspaces, pinned buffers)
     small = [("data/w.txt", [x_list[0][:, :300]], [(pairs[0][0][:300], pairs[0][1][:300])], labels)]
@@ -93,14 +98,17 @@ with tempfile.TemporaryDirectory() as tmp:
     with contextlib.redirect_stdout(io.StringIO()):
         df, nd = gp_fit.create_GP()
     t_fit = time.perf_counter() - t0
-    t_surf = None
     if rank == 0:
         open("options.yaml", "w").write('out_file_name: "results/prob_surf.txt"\n')
-        t1 = time.perf_counter()
-        with contextlib.redirect_stdout(io.StringIO()):
-            cps.generate_prob_surf(df, nd)
-        t_surf = time.perf_counter() - t1
-        surf_bytes = os.path.getsize("results/prob_surf.txt")
+    if world > 1:
+        dist.barrier()
+    t1 = time.perf_counter()
+    with contextlib.redirect_stdout(io.StringIO()):
+        cps.generate_prob_surf(df, nd)                   # all ranks: the merged rows shard across them
+    t_surf = time.perf_counter() - t1
+    surf_bytes = os.path.getsize("results/prob_surf.txt") if rank == 0 else 0
+    if world > 1:
+        dist.barrier()
     os.chdir(ROOT)
 if rank == 0:
     print(json.dumps({
@@ -110,4 +118,7 @@ if rank == 0:
         "phases_rank0_seconds": {k: round(v, 3) for k, v in phase.items()},
         "merged_table_shape": list(df.shape)}))
 if world > 1:
+    dist.barrier()
     dist.destroy_process_group()
+if holder is not None:
+    holder.cleanup()
