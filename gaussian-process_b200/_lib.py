@@ -39,6 +39,8 @@ SIGNATURES = {
     "gpk_oz_gemm_tn": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _i, _vp, _i, _vp]),
     "gpk_csv_bound": (_sz, [_ll, _i]),
     "gpk_csv_format_f64": (_ll, [_vp, _ll, _i, _ll, _vp, _sz, _i]),
+    "gpk_csv_surface_bound": (_sz, [_ll, _i, _i]),
+    "gpk_csv_format_surface": (_ll, [_vp, _vp, _vp, _ll, _i, _i, _vp, _sz, _i]),
     "gpk_finish_wasserstein": (_i, [_vp, _ll, _i, _vp, _i, _vp, _vp, _vp, _vp]),
     "gpk_timing_begin": (_i, [_vp]),
     "gpk_timing_end": (_i, []),

@@ -124,4 +124,60 @@ long long gpk_csv_format_f64(const double* table, long long rows, int cols, long
     return (long long)total;
 }
 
+size_t gpk_csv_surface_bound(long long rows, int ndims, int points) {
+    if (rows <= 0 || ndims < 0 || points <= 0) return 0;
+    return (size_t)rows * (size_t)points * (size_t)(ndims + 2) * (kMaxField + 1);
+}
+
+// Long-format surface block (calc_prob_surf.py:80-81: every merged row emits `points` output rows
+// [coords..., quantity, prob]) straight from the reduction's outputs: the text of the coordinates is formatted once
+// per merged row and copied in front of each of its output rows, only quantity and prob are formatted per output row.
+// Same bytes as gpk_csv_format_f64 on the expanded (rows * points, ndims + 2) table.
+long long gpk_csv_format_surface(const double* coords, const double* y, const double* p, long long rows, int ndims,
+                                 int points, char* out, size_t out_cap, int threads) {
+    if (rows < 0 || ndims < 0 || points <= 0 || (rows > 0 && (!y || !p || !out || (ndims > 0 && !coords)))) return -1;
+    if (out_cap < gpk_csv_surface_bound(rows, ndims, points)) return -1;
+    if (rows == 0) return 0;
+    int nt = threads > 0 ? threads : (int)std::thread::hardware_concurrency();
+    nt = (int)std::max<long long>(1, std::min<long long>(nt, (rows + 63) / 64));
+    const size_t row_slot = (size_t)points * (size_t)(ndims + 2) * (kMaxField + 1);
+    std::vector<long long> first(nt + 1);
+    std::vector<size_t> len(nt, 0);
+    for (int t = 0; t <= nt; ++t) first[t] = rows * t / nt;
+    auto work = [&](int t) {
+        char* q = out + (size_t)first[t] * row_slot;
+        char* const q0 = q;
+        std::vector<char> prefix((size_t)ndims * (kMaxField + 1) + 1);
+        for (long long r = first[t]; r < first[t + 1]; ++r) {
+            char* e = prefix.data();
+            for (int c = 0; c < ndims; ++c) {
+                e = format_value(coords[r * ndims + c], e);
+                *e++ = ',';
+            }
+            const size_t plen = (size_t)(e - prefix.data());
+            const double* yr = y + r * (long long)points;
+            const double* pr = p + r * (long long)points;
+            for (int j = 0; j < points; ++j) {
+                std::memcpy(q, prefix.data(), plen);
+                q += plen;
+                q = format_value(yr[j], q);
+                *q++ = ',';
+                q = format_value(pr[j], q);
+                *q++ = '\n';
+            }
+        }
+        len[t] = (size_t)(q - q0);
+    };
+    std::vector<std::thread> pool;
+    for (int t = 1; t < nt; ++t) pool.emplace_back(work, t);
+    work(0);
+    for (auto& th : pool) th.join();
+    size_t total = len[0];
+    for (int t = 1; t < nt; ++t) {
+        std::memmove(out + total, out + (size_t)first[t] * row_slot, len[t]);
+        total += len[t];
+    }
+    return (long long)total;
+}
+
 }  // extern "C"

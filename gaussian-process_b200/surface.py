@@ -53,9 +53,9 @@ STREAM_ROWS = 1 << 15             # merged rows per CSV block of the streaming w
 
 def write_surface_csv(df, ndims, output_file, points=POINTS, rows_per_pass=None, passes_fn=None, row_range=None,
                       header=True):
-    """The file generate_prob_surf writes (:80-84), produced pass by pass: each pass of the GPU reduction is expanded to
-    its long-format block (coords repeated `points` times, quantity, prob), formatted by libgpk's threaded CSV
-    formatter and appended, while the next pass runs on the device.  Host memory stays bounded by the pass size, so the
+    """The file generate_prob_surf writes (:80-84), produced pass by pass: each pass of the GPU reduction is formatted as
+    its long-format rows (coords repeated `points` times, quantity, prob) by libgpk's threaded CSV formatter (the
+    coordinate text once per merged row) and appended, while the next pass runs on the device.  Host memory stays bounded by the pass size, so the
     64^4-row configuration (1.7e9 output rows) never exists as one frame.  Returns the number of output rows.
     `row_range` = (lo, hi) restricts the file to those merged rows and `header=False` drops the header line (the parts
     of write_surface_csv_sharded); `passes_fn` replaces engine.prob_surface_passes (tests)."""
@@ -80,11 +80,7 @@ def write_surface_csv(df, ndims, output_file, points=POINTS, rows_per_pass=None,
             for b0 in range(0, idx.shape[0], STREAM_ROWS):
                 sel = idx[b0:b0 + STREAM_ROWS]
                 k = sel.shape[0]
-                block = np.empty((k * points, ndims + 2))
-                block[:, :ndims] = np.repeat(coords[sel], points, axis=0)
-                block[:, ndims] = y[b0:b0 + k].reshape(-1)
-                block[:, ndims + 1] = p[b0:b0 + k].reshape(-1)
-                f.write(tables.format_block(block))
+                f.write(tables.format_surface_block(coords[sel], y[b0:b0 + k], p[b0:b0 + k]))
                 n_rows += k * points
     return n_rows
 

@@ -136,6 +136,27 @@ def format_block(block, threads=0):
     return memoryview(out)[:n]
 
 
+def format_surface_block(coords, y, p, threads=0):
+    """Bytes of the long-format surface rows of `coords` (k, ndims), `y`, `p` (k, points): what format_block returns for
+    the expanded (k * points, ndims + 2) table, with the coordinate text formatted once per merged row
+    (gpk_csv_format_surface)."""
+    import ctypes as C
+    from . import _lib
+    lib = _lib.load()
+    coords = np.ascontiguousarray(coords, dtype=np.float64)
+    y = np.ascontiguousarray(y, dtype=np.float64)
+    p = np.ascontiguousarray(p, dtype=np.float64)
+    k, points = y.shape
+    ndims = coords.shape[1]
+    cap = lib.gpk_csv_surface_bound(k, ndims, points)
+    out = np.empty(cap, dtype=np.uint8)
+    n = lib.gpk_csv_format_surface(coords.ctypes.data_as(C.c_void_p), y.ctypes.data_as(C.c_void_p),
+                                   p.ctypes.data_as(C.c_void_p), k, ndims, points, out.ctypes.data_as(C.c_void_p), cap, threads)
+    if n < 0:
+        raise _lib.GpkError("gpk_csv_format_surface rejected its arguments")
+    return memoryview(out)[:n]
+
+
 def plain_header(columns):
     """Header line of to_csv for column names that need no quoting, else None."""
     return _plain_header(columns)

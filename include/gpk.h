@@ -145,6 +145,13 @@ GPK_API size_t gpk_csv_bound(long long rows, int cols);
 GPK_API long long gpk_csv_format_f64(const double* table, long long rows, int cols, long long ld, char* out,
                                      size_t out_cap, int threads);
 
+/* HOST function.  The long-format block generate_prob_surf writes (calc_prob_surf.py:80-84) from the reduction's outputs:
+ * merged row r emits `points` lines "coords[r][0],...,coords[r][ndims-1],y[r][j],p[r][j]\n".  The coordinate text is
+ * formatted once per merged row.  Same bytes as gpk_csv_format_f64 on the expanded table; bound from gpk_csv_surface_bound. */
+GPK_API size_t gpk_csv_surface_bound(long long rows, int ndims, int points);
+GPK_API long long gpk_csv_format_surface(const double* coords, const double* y, const double* p, long long rows, int ndims,
+                                 int points, char* out, size_t out_cap, int threads);
+
 /* HOST function.  Loss finish of find_len_scales.py:163-166 for P particles: W_p = np.trapz(|counts[p] / n_points - expected|,
  * sigma_vals) with d_sigma = diff(sigma_vals) ([S-1]) and measured_of[k] = k / n_points for k = 0..n_points (the caller's
  * table of the quotients); NumPy's operation order and pairwise summation, one pass per particle.  scratch: 2 S doubles.
