@@ -63,6 +63,9 @@ def finish_losses(counts, n_points, positions, sigma_vals, expected, lower, uppe
     return np.where(oob, OOB_SCORE, scores)
 
 
+_FAST_FINISH = {}      # sigma-grid length -> True / False: libgpk's host finish checked against NumPy once per process
+
+
 class SwarmLoss:
     """evaluate_loss for a whole swarm.  Holds the device-resident training set."""
 
@@ -76,15 +79,15 @@ class SwarmLoss:
         self.evaluations = 0
         self._d_sigma = np.diff(self.sigma_vals).reshape(1, -1)
         self._work = None
-        self._fast = None                  # None: not yet checked against NumPy; True / False afterwards
         self._table = np.arange(self.n + 1, dtype=np.int32).astype(np.float64) / self.n      # counts / n, every value
         self._scratch = np.empty(2 * self.sigma_vals.shape[0])
 
     def _integral(self, counts):
         """np.trapz(|counts / n - expected|, sigma_vals, axis=1) by libgpk's host routine (gpk_finish_wasserstein: NumPy's
         operation order and pairwise summation in one pass).  Verified against the NumPy expressions on the first swarm
-        evaluation of this object; any difference switches it off for good."""
-        if self._fast is False or counts.dtype != np.int32 or not counts.flags.c_contiguous:
+        evaluation of the process (per grid length); any difference switches it off for good."""
+        key = counts.shape[1]
+        if _FAST_FINISH.get(key) is False or counts.dtype != np.int32 or not counts.flags.c_contiguous:
             return None
         import ctypes as C
         lib = engine._lib.load()
@@ -94,12 +97,12 @@ class SwarmLoss:
                                         self.n, vp(self.expected.ctypes.data), vp(self._d_sigma.ctypes.data),
                                         vp(self._scratch.ctypes.data), vp(out.ctypes.data))
         if st != 0:
-            self._fast = False
+            _FAST_FINISH[key] = False
             return None
-        if self._fast is None:
+        if key not in _FAST_FINISH:
             ref = np.trapz(np.abs(counts.astype(np.float64) / self.n - self.expected[None, :]), self.sigma_vals, axis=1)
-            self._fast = bool(np.array_equal(ref, out))
-            if not self._fast:
+            _FAST_FINISH[key] = bool(np.array_equal(ref, out))
+            if not _FAST_FINISH[key]:
                 return None
         return out
 
