@@ -4,12 +4,21 @@ the B200 kernels.  Put this directory ahead of the reference on sys.path: GP_fit
 import _bootstrap  # noqa: F401
 import numpy as np
 
-from gaussian_process_b200 import engine
+from gaussian_process_b200 import engine, sharding
+
+SHARD_MIN_POINTS = 1 << 16      # grid sizes from which the prediction is split over the ranks of the process group
 
 
 def GP(x_known, y_known, e_known, x_fit, lengths, batch_size=10000):
     """GP regression mean and uncertainty at x_fit (reference GP_func.py:12-45).
-    x_known (d,N), x_fit (d,M), lengths (d,) -> (y_fit (M,), e_fit (M,)) float64."""
+    x_known (d,N), x_fit (d,M), lengths (d,) -> (y_fit (M,), e_fit (M,)) float64.
+    Under an initialised process group in which every rank makes the same call (the swarm-sharded mode of
+    GP_fit.create_GP), a grid of at least SHARD_MIN_POINTS points is predicted in contiguous tiles, one per rank
+    (sharding.sharded_predict); the values are those of the single-rank call."""
+    x_fit = np.asarray(x_fit, dtype=np.float64)
+    if sharding.world()[1] > 1 and x_fit.ndim == 2 and x_fit.shape[1] >= SHARD_MIN_POINTS:
+        fit = engine.GPFit(x_known, y_known, e_known, lengths)
+        return sharding.sharded_predict(fit.predict, x_fit)
     return engine.gp(x_known, y_known, e_known, x_fit, lengths, batch_size)
 
 
