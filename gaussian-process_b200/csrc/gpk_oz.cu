@@ -192,7 +192,7 @@ struct OzTile {
 // A digit s meets the B digits t = 0 .. min(7, NG - s) - 1 in pieces of at most 4 digits (N <= 256); the piece
 // starting at t0 accumulates into the TMEM columns of the groups s + t0 ...  With NG = 8 the digit s = 4 goes first
 // so that at the first chunk every accumulator is initialised by an instruction that covers it completely.
-template <int NG>
+template <int NG, int TN>
 __device__ __forceinline__ void oz_issue_chunk(uint32_t tmem, uint64_t da, uint64_t db, bool first) {
 #pragma unroll
     for (int si = 0; si < OZ_NS; ++si) {
@@ -202,9 +202,9 @@ __device__ __forceinline__ void oz_issue_chunk(uint32_t tmem, uint64_t da, uint6
         for (int t0 = 0; t0 < total; t0 += 4) {
             const int cnt = (total - t0 < 4) ? (total - t0) : 4;
             const bool init_piece = (NG == 8) ? (s == 4 || (s == 0 && t0 == 0)) : (s == 0);
-            const uint32_t idesc = OZ_IDESC | ((uint32_t)((cnt * OZ_TILE_N) >> 3) << 17);
-            umma_i8(tmem + (s + t0) * OZ_TILE_N, da + (uint64_t)(s * (OZ_DIGIT >> 4)),
-                    db + (uint64_t)(t0 * (OZ_DIGIT_HALF >> 4)), idesc, (init_piece && first) ? 0u : 1u);
+            const uint32_t idesc = OZ_IDESC | ((uint32_t)((cnt * TN) >> 3) << 17);
+            umma_i8(tmem + (s + t0) * TN, da + (uint64_t)(s * (OZ_DIGIT >> 4)),
+                    db + (uint64_t)(t0 * ((TN * 32) >> 4)), idesc, (init_piece && first) ? 0u : 1u);
         }
     }
 }
@@ -216,19 +216,28 @@ __device__ __forceinline__ void oz_issue_chunk(uint32_t tmem, uint64_t da, uint6
 // epilogue drains the accumulators (all 512 TMEM columns hold one tile: MMA and epilogue of one CTA alternate).
 constexpr int OZ_QDEPTH = 4;
 
-template <int EPI, int NG, class F>
+// TN = tile width: 64 (one tile fills TMEM: 8 groups x 64 columns) or 32 (two accumulator sets of 256 columns: the epilogue
+// of one tile overlaps the MMAs of the next; used by the 4-chunk panel contractions, whose tiles are too short to amortise
+// the MMA / epilogue hand-off).
+template <int EPI, int NG, int TN, class F>
 __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uint8_t* smem) {
+    static_assert(TN == 64 || TN == 32, "tile width");
+    static_assert(EPI != OZ_SUMSQ || TN == 64, "the sum-of-squares epilogue is written for 64-column tiles");
+    constexpr uint32_t NSETS = (TN == 32) ? 2u : 1u;        // accumulator sets in TMEM
+    constexpr uint32_t SET_COLS = NG * TN;
+    constexpr uint32_t B_DIGIT = TN * 32;                   // bytes of one B digit of a stage (TN rows x 32 k)
+    constexpr uint32_t STAGE_TX = OZ_CHUNK + OZ_NS * B_DIGIT;
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
     uint8_t* ctrl = smem + (size_t)OZ_STAGES * OZ_STAGE;
     const uint32_t full0 = smem_u32(ctrl);                 // OZ_STAGES x 8 B
     const uint32_t empty0 = full0 + 8 * OZ_STAGES;         // OZ_STAGES x 8 B
-    const uint32_t accbar = empty0 + 8 * OZ_STAGES;        // 8 B: accumulators complete (MMA -> epilogue)
-    const uint32_t freebar = accbar + 8;                   // 8 B: accumulators drained (epilogue -> MMA)
-    const uint32_t qfull0 = freebar + 8;                   // OZ_QDEPTH x 8 B: tile id written (producer -> consumers)
+    const uint32_t accbar = empty0 + 8 * OZ_STAGES;        // 2 x 8 B: accumulators of set s complete (MMA -> epilogue)
+    const uint32_t freebar = accbar + 16;                  // 2 x 8 B: accumulators of set s drained (epilogue -> MMA)
+    const uint32_t qfull0 = freebar + 16;                  // OZ_QDEPTH x 8 B: tile id written (producer -> consumers)
     const uint32_t qempty0 = qfull0 + 8 * OZ_QDEPTH;       // OZ_QDEPTH x 8 B: tile id read by every consumer
-    volatile int* qtile = reinterpret_cast<volatile int*>(ctrl + 8 * (2 * OZ_STAGES + 2 + 2 * OZ_QDEPTH));
-    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(ctrl + 8 * (2 * OZ_STAGES + 2 + 2 * OZ_QDEPTH) + 4 * OZ_QDEPTH);
+    volatile int* qtile = reinterpret_cast<volatile int*>(ctrl + 8 * (2 * OZ_STAGES + 4 + 2 * OZ_QDEPTH));
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(ctrl + 8 * (2 * OZ_STAGES + 4 + 2 * OZ_QDEPTH) + 4 * OZ_QDEPTH);
     const uint32_t stage0 = smem_u32(smem);
 
     if (tid == 0) {
@@ -236,8 +245,10 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
             mbar_init(full0 + 8 * s, 1);
             mbar_init(empty0 + 8 * s, 1);
         }
-        mbar_init(accbar, 1);
-        mbar_init(freebar, OZ_THREADS - 64);
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(accbar + 8 * b, 1);
+            mbar_init(freebar + 8 * b, OZ_THREADS - 64);
+        }
         for (int q = 0; q < OZ_QDEPTH; ++q) {
             mbar_init(qfull0 + 8 * q, 1);
             mbar_init(qempty0 + 8 * q, 1 + OZ_THREADS - 64);      // the MMA thread and every epilogue thread
@@ -279,12 +290,12 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
                 if (OZ_PREFETCH > 0 && k + OZ_STAGES + OZ_PREFETCH < t.nk)
                     bulk_prefetch_l2(t.a + (size_t)(k + OZ_STAGES + OZ_PREFETCH) * OZ_CHUNK, OZ_CHUNK);
                 mbar_wait(empty0 + 8 * s, ph ^ 1u);
-                mbar_expect_tx(full0 + 8 * s, OZ_STAGE);
+                mbar_expect_tx(full0 + 8 * s, STAGE_TX);
                 const uint32_t dst = stage0 + s * OZ_STAGE;
                 bulk_g2s(dst, t.a + (size_t)k * OZ_CHUNK, OZ_CHUNK, full0 + 8 * s);
 #pragma unroll
-                for (int d = 0; d < OZ_NS; ++d)       // 64 rows of every B digit, stored back to back
-                    bulk_g2s(dst + OZ_CHUNK + d * OZ_DIGIT_HALF, t.b + (size_t)k * OZ_CHUNK + d * OZ_DIGIT, OZ_DIGIT_HALF,
+                for (int d = 0; d < OZ_NS; ++d)       // TN rows of every B digit, stored back to back
+                    bulk_g2s(dst + OZ_CHUNK + d * B_DIGIT, t.b + (size_t)k * OZ_CHUNK + d * OZ_DIGIT, B_DIGIT,
                              full0 + 8 * s);
             }
             }
@@ -306,7 +317,8 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
                 if (tile < 0) break;
                 if (!f.make(tile, t)) continue;
                 OZ_PROF_T(q1);
-                mbar_wait(freebar, (it & 1u) ^ 1u);      // the epilogue has drained the previous tile
+                const uint32_t set = it % NSETS, use = it / NSETS;
+                mbar_wait(freebar + 8 * set, (use & 1u) ^ 1u);      // the epilogue has drained this set's previous tile
                 tc_fence_after();
                 OZ_PROF_T(q2);
 #ifdef OZ_PROFILE
@@ -322,13 +334,13 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
                 OZ_PROF_T(c1);
                 const uint64_t da = OZ_SDESC | (uint64_t)(((stage0 + s * OZ_STAGE) >> 4) & 0x3FFF);
                 const uint64_t db = OZ_SDESC | (uint64_t)(((stage0 + s * OZ_STAGE + OZ_CHUNK) >> 4) & 0x3FFF);
-                oz_issue_chunk<NG>(tmem, da, db, k == 0);
+                oz_issue_chunk<NG, TN>(tmem + set * SET_COLS, da, db, k == 0);
                 umma_commit(empty0 + 8 * s);     // frees the stage when these MMAs have read it
 #ifdef OZ_PROFILE
                 pf_full += c1 - c0; pf_issue += clock64() - c1; ++pf_chunks;
 #endif
             }
-            umma_commit(accbar);                 // accumulators complete
+            umma_commit(accbar + 8 * set);       // accumulators complete
             }
 #ifdef OZ_PROFILE
             atomicAdd(&g_oz_prof[EPI][0], (unsigned long long)(clock64() - pf_start));
@@ -342,7 +354,8 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
 #endif
         }
     } else {
-        // epilogue warps 2..9: TMEM lane quadrant = warp % 4, one output row and 32 of the 64 columns per thread
+        // epilogue warps 2..9: TMEM lane quadrant = warp % 4, one output row and CW = TN / 2 of the tile's columns per thread
+        constexpr int CW = TN / 2;
         const int q = warp & 3;
         const int ch = (warp - 2) >> 2;
         const int row = q * 32 + lane;
@@ -357,33 +370,37 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
         if (tile < 0) break;
         if (!f.make(tile, t)) continue;
         const double rs = (t.sa ? t.sa[row] : 1.0) * t.sa_const * 0x1p-70;       // 2^-14 of the digit scaling, 2^-56 of x
-        double* crow = t.c + (size_t)row * t.ldc + ch * 32;
-        const double* sbp = t.sb ? t.sb + ch * 32 : nullptr;
+        double* crow = t.c + (size_t)row * t.ldc + ch * CW;
+        const double* sbp = t.sb ? t.sb + ch * CW : nullptr;
         const double drs = (t.dig_rs ? t.dig_rs[row] : 1.0) * t.dig_rconst * 0x1p55;
-        const double* dcs = t.dig_cs ? t.dig_cs + ch * 32 : nullptr;
-        uint8_t* drow = t.dig ? t.dig + (size_t)ch * OZ_CHUNK + (row >> 3) * 256 + (row & 7) * 16 : nullptr;
+        const double* dcs = t.dig_cs ? t.dig_cs + ch * CW : nullptr;
+        // digit record of the output: a 64-column tile covers two K chunks of the next contraction (one per column half), a
+        // 32-column tile one chunk, in which the column half selects the 16-byte unit
+        uint8_t* drow = t.dig ? t.dig + (TN == 64 ? (size_t)ch * OZ_CHUNK : (size_t)ch * 128) + (row >> 3) * 256 + (row & 7) * 16
+                              : nullptr;
         // phase A (TMEM busy): accumulators -> FP64 output values in registers; phase B (after the accumulators are
         // released to the MMA thread): global stores and digit emission, overlapping the next tile's MMAs
-        double val[32];
+        double val[CW];
         if (EPI == OZ_SUB) {                     // the tile is final input data: fetch it while the MMAs run
 #pragma unroll
-            for (int j = 0; j < 8; ++j) ldg_f64x4(crow + 4 * j, val[4 * j], val[4 * j + 1], val[4 * j + 2], val[4 * j + 3]);
+            for (int j = 0; j < CW / 4; ++j) ldg_f64x4(crow + 4 * j, val[4 * j], val[4 * j + 1], val[4 * j + 2], val[4 * j + 3]);
         }
-        mbar_wait(accbar, it & 1u);
+        const uint32_t set = it % NSETS, use = it / NSETS;
+        mbar_wait(accbar + 8 * set, use & 1u);
         tc_fence_after();
         ++it;
-        const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + ch * 32;
+        const uint32_t taddr = tmem + set * SET_COLS + ((uint32_t)(q * 32) << 16) + ch * CW;
 #pragma unroll
-        for (int cc = 0; cc < 32; cc += 8) {
+        for (int cc = 0; cc < CW; cc += 8) {
             uint32_t a[NG][8];
 #pragma unroll
-            for (int g = 0; g < NG; ++g) tmem_ld8(taddr + g * OZ_TILE_N + cc, a[g]);
+            for (int g = 0; g < NG; ++g) tmem_ld8(taddr + g * TN + cc, a[g]);
             tmem_wait_ld();
             if (t.dbg) {
 #pragma unroll
                 for (int g = 0; g < NG; ++g)
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) t.dbg[(g * 128 + row) * OZ_TILE_N + ch * 32 + cc + j] = (int)a[g][j];
+                    for (int j = 0; j < 8; ++j) t.dbg[(g * 128 + row) * TN + ch * CW + cc + j] = (int)a[g][j];
             }
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
@@ -402,21 +419,21 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
             }
         }
         tc_fence_before();
-        mbar_arrive(freebar);                    // TMEM may be overwritten
+        mbar_arrive(freebar + 8 * set);          // this set of accumulators may be overwritten
         if (EPI != OZ_SUMSQ) {
             if (t.store) {
 #pragma unroll
-                for (int j = 0; j < 8; ++j) stg_f64x4(crow + 4 * j, val[4 * j], val[4 * j + 1], val[4 * j + 2], val[4 * j + 3]);
+                for (int j = 0; j < CW / 4; ++j) stg_f64x4(crow + 4 * j, val[4 * j], val[4 * j + 1], val[4 * j + 2], val[4 * j + 3]);
             }
             if (t.amax) {
                 double m = 0.0;
 #pragma unroll
-                for (int j = 0; j < 32; ++j) m = fmax(m, fabs(val[j] * t.amax_cs[ch * 32 + j]));
+                for (int j = 0; j < CW; ++j) m = fmax(m, fabs(val[j] * t.amax_cs[ch * CW + j]));
                 atomicMax(t.amax + row, (unsigned long long)__double_as_longlong(m));
             }
             if (drow) {                          // digits of the stored values: one 16-byte unit (16 consecutive k) per store
 #pragma unroll
-                for (int cc = 0; cc < 32; cc += 16) {
+                for (int cc = 0; cc < CW; cc += 16) {
                     uint32_t lo[16], hi[16];
 #pragma unroll
                     for (int j = 0; j < 16; ++j) {
@@ -440,7 +457,7 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
                 }
             }
         }
-        if (EPI == OZ_SUMSQ) {
+        if constexpr (EPI == OZ_SUMSQ && TN == 64) {
             // butterfly: 32 columns x 32 rows (lanes) -> lane l holds the sum over the quadrant's rows of column l
 #pragma unroll
             for (int step = 16; step >= 1; step >>= 1) {
@@ -465,10 +482,10 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
 }
 
 // ---- tile descriptions (functors) and the one persistent kernel ---------------------------------------------------
-template <int EPI, int NG, class F>
+template <int EPI, int NG, int TN, class F>
 __global__ void __launch_bounds__(OZ_THREADS, 1) k_oz(const F f, int ntiles, int* counter) {
     extern __shared__ __align__(128) uint8_t oz_smem[];
-    oz_run<EPI, NG, F>(f, ntiles, counter, oz_smem);
+    oz_run<EPI, NG, TN, F>(f, ntiles, counter, oz_smem);
 }
 
 __device__ __forceinline__ void oz_no_digits(OzTile& t) {
@@ -724,9 +741,10 @@ k_oz_slice_d(const double* __restrict__ dinv, const double* __restrict__ dinvT, 
     oz_slice_tile(src, NB, inv, 1.0, cs, dig + (((size_t)p * T + J) * 2 + which) * (4 * (size_t)OZ_CHUNK));
 }
 
-// Panel solve on the digit GEMM: L_IJ = S_IJ D_J^T, tile = p * nx + 2 * (I - J - 1) + half.  A = digits of
+// Panel solve on the digit GEMM: L_IJ = S_IJ D_J^T, tile = p * nx + (128 / TN) * (I - J - 1) + column part.  A = digits of
 // S_IJ / (rowsig_i rowsig_j) left by the SYRK epilogue, B = digits of D_J rowsig_j; the epilogue stores L_IJ and its
 // digits (L / rowsig_i).
+template <int TN>
 struct OzTrsmTiles {
     double* mat; int Np, T, J, nx;
     const uint8_t* sdig; size_t sdig_stride;
@@ -737,18 +755,19 @@ struct OzTrsmTiles {
     __device__ __forceinline__ bool make(int tile, OzTile& t) const {
         const int p = tile / nx, bx = tile - p * nx;
         if (active && !active[p]) return false;
-        const int I = J + 1 + (bx >> 1), h = bx & 1;
+        constexpr int PARTS = NB / TN;
+        const int I = J + 1 + bx / PARTS, h = bx % PARTS;
         const int kch = Np / 32;
         t.a = sdig + (size_t)p * sdig_stride + (size_t)I * 4 * OZ_CHUNK;
-        t.b = ddig + (((size_t)p * T + J) * 2 + 0) * (4 * (size_t)OZ_CHUNK) + (size_t)h * OZ_DIGIT_HALF;
+        t.b = ddig + (((size_t)p * T + J) * 2 + 0) * (4 * (size_t)OZ_CHUNK) + (size_t)h * (TN * 32);
         t.nk = 4;
-        t.c = mat + (size_t)p * Np * Np + (size_t)I * NB * Np + (size_t)J * NB + h * OZ_TILE_N;
+        t.c = mat + (size_t)p * Np * Np + (size_t)I * NB * Np + (size_t)J * NB + h * TN;
         t.ldc = Np;
         t.sa = rowsig + I * NB;
         t.sa_const = 1.0;
-        t.sb = dsc + (((size_t)p * T + J) * 2 + 0) * NB + h * OZ_TILE_N;
+        t.sb = dsc + (((size_t)p * T + J) * 2 + 0) * NB + h * TN;
         oz_no_digits(t);
-        t.dig = slices + (size_t)p * slice_stride + ((size_t)I * kch + 4 * J + 2 * h) * OZ_CHUNK;
+        t.dig = slices + (size_t)p * slice_stride + ((size_t)I * kch + 4 * J + (h * TN) / 32) * OZ_CHUNK;
         t.dig_rs = rowinv + I * NB;
         t.store = 0;           // L_IJ is consumed as digits only (later SYRKs, phase-2 panel); the inverse overwrites the block
         return true;
@@ -756,7 +775,8 @@ struct OzTrsmTiles {
 };
 
 // Phase-2 panel on the digit GEMM: Mt[n][r] = sum_j D_J^T[n][j] L[r][J NB + j], r in block R,
-// tile = p * nx + 2 * (R - J - 1) + half.
+// tile = p * nx + (128 / TN) * (R - J - 1) + column part.
+template <int TN>
 struct OzInvpTiles {
     double* mt; int Np, T, J, nx;
     const uint8_t* ddig; const double* dsc;
@@ -767,19 +787,20 @@ struct OzInvpTiles {
     __device__ __forceinline__ bool make(int tile, OzTile& t) const {
         const int p = tile / nx, bx = tile - p * nx;
         if (active && !active[p]) return false;
-        const int R = J + 1 + (bx >> 1), h = bx & 1;
+        constexpr int PARTS = NB / TN;
+        const int R = J + 1 + bx / PARTS, h = bx % PARTS;
         const int kch = Np / 32;
         t.a = ddig + (((size_t)p * T + J) * 2 + 1) * (4 * (size_t)OZ_CHUNK);
-        t.b = slices + (size_t)p * slice_stride + ((size_t)R * kch + 4 * J) * OZ_CHUNK + (size_t)h * OZ_DIGIT_HALF;
+        t.b = slices + (size_t)p * slice_stride + ((size_t)R * kch + 4 * J) * OZ_CHUNK + (size_t)h * (TN * 32);
         t.nk = 4;
-        t.c = mt + (size_t)p * NB * Np + (size_t)R * NB + h * OZ_TILE_N;
+        t.c = mt + (size_t)p * NB * Np + (size_t)R * NB + h * TN;
         t.ldc = Np;
         t.sa = dsc + (((size_t)p * T + J) * 2 + 1) * NB;
         t.sa_const = 1.0;
-        t.sb = rowsig + R * NB + h * OZ_TILE_N;
+        t.sb = rowsig + R * NB + h * TN;
         oz_no_digits(t);
         t.amax = mtmax + (size_t)p * NB;
-        t.amax_cs = gaminv + R * NB + h * OZ_TILE_N;
+        t.amax_cs = gaminv + R * NB + h * TN;
         return true;
     }
 };
@@ -975,6 +996,21 @@ static int g_oz_groups = 8;     // digit groups kept: 8 -> 34 digit products (de
 void oz_set_groups(int ng) { g_oz_groups = (ng == 7) ? 7 : 8; }
 int oz_get_groups() { return g_oz_groups; }
 
+// Tile width of the 4-chunk panel contractions (TRSM, phase-2 panel).  64 (default): one accumulator set fills TMEM, MMA and
+// epilogue of a CTA alternate.  GPK_OZ_PANEL_TN=32: two accumulator sets, the epilogue of one tile overlaps the MMAs of the
+// next.  Measured (profiles/r01_ab_panel_tn.log): the hand-off wait drops from 4000 to 900 cycles per tile, but a 32-column
+// tile costs 5700 cycles against 10 000 for a 64-column one (MMAs of N <= 128 are bound by the A operand reads, and the
+// per-tile queue / operand latencies double): 195.9 vs 192.5 ms per step, so 64 stays.  The results do not depend on it
+// (exact integer accumulation, element-wise epilogue): the loss checksum is identical.
+static int oz_panel_tn() {
+    static int v = 0;
+    if (v == 0) {
+        const char* e = getenv("GPK_OZ_PANEL_TN");
+        v = (e && atoi(e) == 32) ? 32 : 64;
+    }
+    return v;
+}
+
 static int oz_grid(int ntiles) {
     static int sms = 0;
     if (sms == 0) {
@@ -987,17 +1023,17 @@ static int oz_grid(int ntiles) {
     return ntiles < sms ? ntiles : sms;       // one persistent CTA per SM (215 KB of shared memory, all of TMEM)
 }
 
-// launches k_oz<EPI, 7 or 8, F> on one persistent CTA per SM (one smem-attribute call per instantiation)
-template <int EPI, class F>
+// launches k_oz<EPI, 7 or 8, TN, F> on one persistent CTA per SM (one smem-attribute call per instantiation)
+template <int EPI, int TN = OZ_TILE_N, class F>
 static int oz_launch(const F& f, int ntiles, int* counter, cudaStream_t st) {
     static bool done7 = false, done8 = false;
     if (ntiles <= 0) return 0;
     if (g_oz_groups == 7) {
-        if (oz_smem_attr(k_oz<EPI, 7, F>, done7)) return 1;
-        k_oz<EPI, 7, F><<<oz_grid(ntiles), OZ_THREADS, OZ_SMEM_BYTES, st>>>(f, ntiles, counter);
+        if (oz_smem_attr(k_oz<EPI, 7, TN, F>, done7)) return 1;
+        k_oz<EPI, 7, TN, F><<<oz_grid(ntiles), OZ_THREADS, OZ_SMEM_BYTES, st>>>(f, ntiles, counter);
     } else {
-        if (oz_smem_attr(k_oz<EPI, 8, F>, done8)) return 1;
-        k_oz<EPI, 8, F><<<oz_grid(ntiles), OZ_THREADS, OZ_SMEM_BYTES, st>>>(f, ntiles, counter);
+        if (oz_smem_attr(k_oz<EPI, 8, TN, F>, done8)) return 1;
+        k_oz<EPI, 8, TN, F><<<oz_grid(ntiles), OZ_THREADS, OZ_SMEM_BYTES, st>>>(f, ntiles, counter);
     }
     return 0;
 }
@@ -1024,9 +1060,15 @@ int launch_oz_trsm(double* mat, int Np, int T, int J, int P, const uint8_t* sdig
                    const double* rowsig, const double* rowinv, uint8_t* slices, int* counter, const unsigned char* active,
                    cudaStream_t st) {
     if (J >= T - 1) return 0;
-    const OzTrsmTiles f{mat, Np, T, J, 2 * (T - 1 - J), sdig, oz_panel_bytes(Np), ddig, dsc, rowsig, rowinv, slices,
-                        oz_slice_bytes(Np), active};
-    if (oz_launch<OZ_STORE>(f, f.nx * P, counter, st)) return 1;
+    if (oz_panel_tn() == 32) {
+        const OzTrsmTiles<32> f{mat, Np, T, J, 4 * (T - 1 - J), sdig, oz_panel_bytes(Np), ddig, dsc, rowsig, rowinv, slices,
+                                oz_slice_bytes(Np), active};
+        if (oz_launch<OZ_STORE, 32>(f, f.nx * P, counter, st)) return 1;
+    } else {
+        const OzTrsmTiles<64> f{mat, Np, T, J, 2 * (T - 1 - J), sdig, oz_panel_bytes(Np), ddig, dsc, rowsig, rowinv, slices,
+                                oz_slice_bytes(Np), active};
+        if (oz_launch<OZ_STORE, 64>(f, f.nx * P, counter, st)) return 1;
+    }
     return check_launch("k_oz_trsm");
 }
 
@@ -1034,8 +1076,13 @@ int launch_oz_invp(double* mt, int Np, int T, int J, int P, const uint8_t* ddig,
                    const double* rowsig, unsigned long long* mtmax, const double* gaminv, int* counter,
                    const unsigned char* active, cudaStream_t st) {
     if (J >= T - 1) return 0;
-    const OzInvpTiles f{mt, Np, T, J, 2 * (T - 1 - J), ddig, dsc, slices, oz_slice_bytes(Np), rowsig, mtmax, gaminv, active};
-    if (oz_launch<OZ_STORE>(f, f.nx * P, counter, st)) return 1;
+    if (oz_panel_tn() == 32) {
+        const OzInvpTiles<32> f{mt, Np, T, J, 4 * (T - 1 - J), ddig, dsc, slices, oz_slice_bytes(Np), rowsig, mtmax, gaminv, active};
+        if (oz_launch<OZ_STORE, 32>(f, f.nx * P, counter, st)) return 1;
+    } else {
+        const OzInvpTiles<64> f{mt, Np, T, J, 2 * (T - 1 - J), ddig, dsc, slices, oz_slice_bytes(Np), rowsig, mtmax, gaminv, active};
+        if (oz_launch<OZ_STORE, 64>(f, f.nx * P, counter, st)) return 1;
+    }
     return check_launch("k_oz_invp");
 }
 
