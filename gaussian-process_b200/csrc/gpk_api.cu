@@ -342,6 +342,11 @@ int gpk_loss_batched(const double* X, const double* y, const double* e, const do
     if (N <= SMALL_N_MAX)
         return launch_small_loss(X, y, e, ls, active, sigma_vals, P, N, d, S, counts_out, info, resid_out, sig_out, st);
 
+    if (g_precision && round_up(N, NB) >= 16384) {
+        // a group accumulator receives up to 8 digit products of magnitude <= 2^14 per k: exact in int32 for K < 2^14 only
+        set_error("gpk_loss_batched: the emulated-FP64 mode supports N <= 16256 (int32 accumulators); use mode 0");
+        return 2;
+    }
     // blocked path: waves of as many particles as the workspace holds, each wave split into independent
     // particle groups on concurrent streams (the chain SYRK -> diag -> TRSM of one group is serial; kernels of
     // other groups fill its wave tails and hide the latency-bound diagonal kernel)
@@ -418,6 +423,7 @@ int gpk_fit(const double* X, const double* y, const double* e, const double* ls,
             double* alpha_out, double* xs_out, double* sq_out, int* info, void* workspace, size_t workspace_bytes,
             void* stream) {
     if (bad_dims("gpk_fit", N, d, 0)) return 2;
+    if (g_precision && round_up(N, NB) >= 16384) { set_error("gpk_fit: the emulated-FP64 mode supports N <= 16256 (int32 accumulators); use mode 0"); return 2; }
     if (workspace_bytes < gpk_fit_workspace_bytes(N, d)) { set_error("gpk_fit: workspace too small"); return 3; }
     cudaStream_t st = (cudaStream_t)stream;
     set_stream(st);

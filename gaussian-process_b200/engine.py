@@ -59,6 +59,7 @@ def to_dev(a, dtype=None):
 #            profiles/r01_mode_crossover.log), else "fp64"                        (default; env GPK_PRECISION)
 _MODES = {"fp64": 0, "emu": 1, "emu28": 2}
 EMU_MIN_N = 1024
+EMU_MAX_N = 16256             # contraction length below 2^14: the int32 sums of 8 digit products of 2^14 each cannot overflow
 _precision_pref = os.environ.get("GPK_PRECISION", "auto")
 
 
@@ -79,9 +80,11 @@ def _resolve_precision(e_host, n=None):
     pref = _precision_pref
     ok = bool(np.all(np.isfinite(e_host)) and np.all(np.abs(e_host) > 1e-150)) if e_host.size else False
     if pref == "auto":
-        return 1 if ok and (n is None or n >= EMU_MIN_N) else 0
+        return 1 if ok and (n is None or EMU_MIN_N <= n <= EMU_MAX_N) else 0
     if pref != "fp64" and not ok:
         raise ValueError("emulated-FP64 mode needs finite, non-zero e_known (use GPK_PRECISION=fp64)")
+    if pref != "fp64" and n is not None and n > EMU_MAX_N:
+        raise ValueError(f"emulated-FP64 mode supports N <= {EMU_MAX_N} (exact int32 accumulation); use GPK_PRECISION=fp64")
     return _MODES[pref]
 
 

@@ -119,7 +119,7 @@ GPK_API int gpk_set_groups(int groups);
  *      products of weight >= 2^-56 run on the int8 tcgen05 tensor cores with exact int32 accumulation in TMEM, and
  *      the FP64 result is rebuilt in the epilogue.  Rounding level: that of an FP64 dot product of the same length
  *      (checked against the reference in tests/test_gpu_parity.py).  Requires e > 0 (the column bound
- *      |L^-1[i][k]| <= 1 / e_k is used);
+ *      |L^-1[i][k]| <= 1 / e_k is used) and N <= 16256 (8 products of 2^14 per k stay exact in int32 for K < 2^14);
  *   2  as 1 with the 28 digit products of weight >= 2^-48 only (21 % less tensor work, ~2^8 larger truncation).
  * The mode also sizes gpk_loss_workspace_bytes / gpk_fit_workspace_bytes: set it before querying them. */
 GPK_API int gpk_set_precision(int mode);
