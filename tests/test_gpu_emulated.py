@@ -155,3 +155,42 @@ def test_graph_replay_equals_direct_launches(env, mode, monkeypatch):
         assert len(ctx_d._graphs) == 0
     finally:
         engine.set_precision("auto")
+
+
+def test_panel_tile_width_does_not_change_results(env, tmp_path):
+    """The 32-column double-buffered panel tiles (GPK_OZ_PANEL_TN=32, read once per process) give the counts, residuals and
+    standard deviations of the default 64-column tiles bit for bit; emu mode N <= 16256 guard."""
+    import os
+    import subprocess
+    import sys
+    torch, lib, _lib, engine = env
+    code = r"""
+import sys, numpy as np
+sys.path.insert(0, sys.argv[1])
+from oracle import gp_oracle as orc
+from gaussian_process_b200 import engine
+x, y, e = orc.synthetic_problem(700, 3, 9)
+pos, lo, hi = orc.synthetic_particles(x, 9, 2)
+s, ex = orc.sigma_grid()
+engine.set_precision("emu")
+c, i, r, sd = engine.LossContext(x, y, e, s).counts(pos, want_detail=True)
+np.savez(sys.argv[2], c=c, i=i, r=r, sd=sd)
+"""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for tn in ("64", "32"):
+        out = str(tmp_path / f"tn{tn}.npz")
+        env_vars = dict(os.environ, GPK_OZ_PANEL_TN=tn)
+        subprocess.run([sys.executable, "-c", code, root, out], check=True, env=env_vars, timeout=300)
+        outs.append(np.load(out))
+    for k in ("c", "i", "r", "sd"):
+        assert np.array_equal(outs[0][k], outs[1][k]), k
+    assert not outs[0]["i"].any()
+    prev = engine.get_precision()
+    engine.set_precision("emu")
+    try:
+        with pytest.raises(ValueError):
+            engine._resolve_precision(np.full(4, 0.1), 20000)
+    finally:
+        engine.set_precision(prev)
+    assert engine._resolve_precision(np.full(4, 0.1), 20000) in (0, 1) and (prev != "auto" or engine._resolve_precision(np.full(4, 0.1), 20000) == 0)
