@@ -441,6 +441,26 @@ def run_ours(args):
         ctx.counts_device(dpos, dact, P)
         torch.cuda.synchronize()
 
+    # ---- and with 28 instead of 34 digit products (twice the error of the native FP64 kernels on well-conditioned
+    #      problems, profiles/r01_small_e_accuracy_v2.log; an option, not the default) ----
+    emu28 = None
+    if args.precision == "emu" and not args.no_native:
+        engine.set_precision("emu28")
+        for _ in range(2):
+            ctx.counts_device(dpos, dact, P)
+        torch.cuda.synchronize()
+        n0, n1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n0.record(st)
+        for _ in range(2):
+            c_28, _i = ctx.counts_device(dpos, dact, P)
+        n1.record(st)
+        torch.cuda.synchronize()
+        emu28 = {"value": P * 2 / (n0.elapsed_time(n1) * 1e-3), "unit": UNIT, "per": "GPU", "steps": 2,
+                 "counts_identical_to_default": bool(torch.equal(c_28, counts))}
+        engine.set_precision(args.precision)
+        ctx.counts_device(dpos, dact, P)
+        torch.cuda.synchronize()
+
     # ---- per-kernel-class device time: one extra, separately instrumented step (single stream, events after
     #      every launch); the timed region above runs uninstrumented with concurrent particle groups ----
     _lib.timing_begin(st.cuda_stream)
@@ -521,6 +541,7 @@ def run_ours(args):
                          "kernel_share_of_step": {k: round(v[0] / total_cls_ms, 4) for k, v in sorted(classes.items(), key=lambda kv: -kv[1][0])}},
             "cpu_baseline": cpu_base,
             "native_fp64": native,
+            "emu28": emu28,
             "aux": aux,
             "loss_checksum": float(np.sum(losses[:P])),
         }

@@ -31,7 +31,8 @@ def longdouble_selfpred(x, y, e, ls):
 
 
 s, ex = pso.sigma_grid()
-n, dd = 384, 2
+n, dd = (int(sys.argv[1]) if len(sys.argv) > 1 else 384), 2
+MODES = ("fp64", "emu", "emu28")
 for emin, emax in ((0.05, 0.2), (1e-2, 1e-1), (1e-3, 1e-1), (1e-4, 1e-2), (1e-5, 1e-3)):
     x, y, _ = orc.synthetic_problem(n, dd, 3)
     rng = np.random.default_rng(1)
@@ -39,8 +40,9 @@ for emin, emax in ((0.05, 0.2), (1e-2, 1e-1), (1e-3, 1e-1), (1e-4, 1e-2), (1e-5,
     ls = np.array([0.3, 0.4])
     r_ref, sd_ref = longdouble_selfpred(x, y, e, ls)
     row = []
-    for mode in ("fp64", "emu"):
+    for mode in MODES:
         engine.set_precision(mode)
         c, info, r, sd = engine.LossContext(x, y, e, s).counts(ls[None, :], want_detail=True)
-        row.append((np.max(np.abs(r[0] - r_ref) / np.abs(r_ref).max()), np.max(np.abs(sd[0] - sd_ref) / sd_ref), int(info[0])))
-    print(f"e in [{emin:g}, {emax:g}]: fp64 resid {row[0][0]:.2e} sd {row[0][1]:.2e} | emu resid {row[1][0]:.2e} sd {row[1][1]:.2e} | info {row[0][2]} {row[1][2]}", flush=True)
+        row.append((np.max(np.abs(r[0] - r_ref) / np.abs(r_ref).max()), np.max(np.abs(sd[0] - sd_ref) / sd_ref), int(info[0]), c[0].copy()))
+    print(f"N={n} e in [{emin:g}, {emax:g}]: " + " | ".join(f"{m} resid {v[0]:.2e} sd {v[1]:.2e}" for m, v in zip(MODES, row))
+          + f" | counts equal to fp64: {[bool(np.array_equal(v[3], row[0][3])) for v in row]}", flush=True)
