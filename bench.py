@@ -339,6 +339,34 @@ def aux_measurements(torch, engine):
     out["prob_surface"]["csv_e2e"] = {"value": Rc / s_csv, "unit": "rows/s", "merged_rows": Rc, "output_rows": int(n_out),
                                       "csv_bytes": int(nbytes), "host_threads": os.cpu_count(),
                                       "includes": "H2D, reduction, D2H, long-format expansion, CSV text (to_csv bytes), file write"}
+    # BASELINE config C2: N=1024, d=2, 64 particles (loss), 200 x 200 grid (prediction)
+    from gaussian_process_b200 import pso as _pso
+    x2, y2, e2 = synthetic.problem(1024, 2, 0)
+    pos2, _lo2, _hi2 = synthetic.particles(x2, 64, 0)
+    sv2, _ex2 = _pso.sigma_grid()
+    ctx2 = engine.LossContext(x2, y2, e2, sv2)
+    dpos2 = engine.to_dev(pos2)
+    dact2 = torch.ones(64, dtype=torch.uint8, device=dpos2.device)
+    for _ in range(3):
+        ctx2.counts_device(dpos2, dact2, 64)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(20):
+        ctx2.counts_device(dpos2, dact2, 64)
+    e1.record()
+    torch.cuda.synchronize()
+    g = np.linspace(0.0, 1.0, 200)
+    grid2 = np.ascontiguousarray(np.stack(np.meshgrid(g, g, indexing="ij")).reshape(2, -1))
+    engine.gp(x2, y2, e2, grid2, np.array([0.25, 0.25]))
+    t0 = time.perf_counter()
+    engine.gp(x2, y2, e2, grid2, np.array([0.25, 0.25]))
+    t_c2 = time.perf_counter() - t0
+    out["config_c2"] = {"workload": "C2: N=1024, d=2, 64 particles; 200 x 200 prediction grid",
+                        "loss": {"value": 64 * 20 / (e0.elapsed_time(e1) * 1e-3), "unit": "loss_evals/s", "ms_per_swarm": e0.elapsed_time(e1) / 20,
+                                 "precision": {0: "fp64", 1: "emu", 2: "emu28"}[ctx2.mode]},
+                        "predict_e2e": {"value": grid2.shape[1] / t_c2, "unit": "grid_pts/s", "includes": "fit + H2D + predict + D2H"}}
+    del ctx2
     # the reference's real PSO configuration: KMeans subsample to 100 points, 40 particles, 500 iterations
     import contextlib
     import io
