@@ -17,34 +17,44 @@
 // diagonal (v below it, vup above it) and a compile-time choice inside a diagonal tile.  Same products, same order and
 // same rounding as the element-wise predicated form (a masked term adds an exact zero).  sqrt and the reciprocal of
 // the next pivot (both correctly rounded, as sqrt() and 1.0 / x are) are computed by the one thread that owns it.
-// All operands of a step come from registers plus 24 broadcast loads; two block barriers per step.
+// All operands of a step come from registers plus 24 broadcast loads; one block barrier per step (see chol_inv_regs).
 #pragma once
 #include "gpk_common.cuh"
 
 namespace gpk {
 
 constexpr int CI_LD = NB + 1;    // row stride of the shared staging array used around the register kernel
-constexpr int CI_WORK = 3 * NB + 8;      // doubles of shared scratch chol_inv_regs needs (v, vcm, vup, pivot slots)
+// doubles of shared scratch chol_inv_regs needs: two generations of (v, vcm, vup), the initial diagonal, two pivot slots
+constexpr int CI_WORK = 7 * NB + 8;
 constexpr size_t CI_SMEM_BYTES = (size_t)NB * CI_LD * sizeof(double) + (size_t)(CI_WORK + NB) * sizeof(double);
 
 // All 256 threads must call.  work: CI_WORK doubles, xd: NB doubles, both in shared memory.
 // Returns 0 or (1 + index of the first non-positive / NaN pivot), identical in every thread.
+//
+// One block barrier per step: the published vectors alternate between two generations (step j writes generation j & 1,
+// which was last read in step j - 2, i.e. before the barrier of step j - 1 that every writer has passed).  The hand-over
+// of the pivot between the thread that owns E(j,j) and the 16 threads that own column j costs no barrier either: every
+// thread tracks the pivots of its own 8 tile columns, pv[c] = A(c,c) - sum_{m<j} v_m[c]^2, with the very FMAs the
+// diagonal tile applies to E(c,c) (same operands, same order: bit-identical), so the owners of column j + 1 start its
+// square root and reciprocal right after the step-j loads, ahead of their 64 update FMAs.
 __device__ __forceinline__ int chol_inv_regs(double (&E)[8][8], int n, double* work, double* xd) {
-    double* v = work;
-    double* vcm = work + NB;
-    double* vup = work + 2 * NB;
-    double* piv = work + 3 * NB;            // two slots of (pivot, sqrt, 1 / sqrt)
+    double* dgs = work + 6 * NB;             // initial diagonal
+    double* piv = work + 7 * NB;             // pivot of step j at piv[j & 1] (for the positivity check of all threads)
     const int tid = threadIdx.x;
     const int tr = tid >> 4, tc = tid & 15;
     const int R0 = tr * 8, C0 = tc * 8;
-    const double* row_lo = (tc > tr) ? vup : v;          // row multiplier of the elements with c <= r
-    const double* row_up = (tc < tr) ? v : vup;          // ... and of those with c > r
     int bad = 0;
-    if (tid == 0) {
-        const double d0 = E[0][0], s0 = __dsqrt_rn(d0);
-        piv[0] = d0; piv[1] = s0; piv[2] = __drcp_rn(s0);
+    if (tr == tc) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) dgs[R0 + k] = E[k][k];
     }
     __syncthreads();
+    double pv[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) pv[k] = dgs[C0 + k];
+    // square root and reciprocal of the pivot of the column this thread scales next (valid in the owners of that column)
+    double s_next = 0.0, inv_next = 0.0;
+    if (tc == 0) { s_next = __dsqrt_rn(pv[0]); inv_next = __drcp_rn(s_next); }
     // steps are taken 8 at a time so that the column inside the owning tile (jj) is a compile-time index:
     // the register tile must never be indexed dynamically (it would be demoted to local memory)
     for (int jb = 0; jb * 8 < n; ++jb) {
@@ -52,10 +62,14 @@ __device__ __forceinline__ int chol_inv_regs(double (&E)[8][8], int n, double* w
         for (int jj = 0; jj < 8; ++jj) {
             const int j = jb * 8 + jj;
             if (j < n) {                               // uniform over the CTA
-                const double* slot = piv + 3 * (j & 1);
-                if (!(slot[0] > 0.0) && bad == 0) bad = j + 1;
+                double* v = work + (j & 1) * 3 * NB;
+                double* vcm = v + NB;
+                double* vup = v + 2 * NB;
+                const double* row_lo = (tc > tr) ? vup : v;          // row multiplier of the elements with c <= r
+                const double* row_up = (tc < tr) ? v : vup;          // ... and of those with c > r
                 if (jb == tc) {                        // this thread owns part of column j
-                    const double s = slot[1], inv = slot[2];
+                    const double s = s_next, inv = inv_next;
+                    if (tr == 0) piv[j & 1] = pv[jj];
 #pragma unroll
                     for (int rr = 0; rr < 8; ++rr) {
                         const int r = R0 + rr;
@@ -74,31 +88,37 @@ __device__ __forceinline__ int chol_inv_regs(double (&E)[8][8], int n, double* w
                     }
                 }
                 __syncthreads();
-                // tiles left of column j are final; tiles above the diagonal whose rows are all > j have not started
-                if (C0 + 7 > j && !(tc > tr && R0 > j)) {
-                    double lo[8], up[8], vc[8];
+                if (!(piv[j & 1] > 0.0) && bad == 0) bad = j + 1;
+                if (C0 + 7 > j) {                      // columns <= j are final
+                    double vc[8];
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) { lo[k] = row_lo[R0 + k]; up[k] = row_up[R0 + k]; vc[k] = vcm[k * 16 + tc]; }
-                    // the owner of the next pivot updates that element first and publishes it with its square root and
-                    // reciprocal, so that the serial chain of the factorisation does not wait for its other 63 products
+                    for (int k = 0; k < 8; ++k) vc[k] = vcm[k * 16 + tc];
+                    // the thread's copy of its columns' pivots, then (owners of column j + 1) that pivot's root and
+                    // reciprocal, so that the serial chain of the factorisation does not wait for the 64 products below
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) pv[k] = fma(-vc[k], vc[k], pv[k]);
                     const int jn = j + 1;
-                    if ((jn >> 3) == tr && tr == tc && jn < n) {
-                        const int q = (jj + 1) & 7;                 // compile-time after unrolling
-                        const double dn = fma(-lo[q], vc[q], E[q][q]);
-                        const double sn = __dsqrt_rn(dn);
-                        double* nslot = piv + 3 * (jn & 1);
-                        nslot[0] = dn; nslot[1] = sn; nslot[2] = __drcp_rn(sn);
+                    if ((jn >> 3) == tc && jn < n) {
+                        const double dn = pv[(jj + 1) & 7];           // compile-time index after unrolling
+                        s_next = __dsqrt_rn(dn);
+                        inv_next = __drcp_rn(s_next);
                     }
+                    // tiles above the diagonal whose rows are all > j have not started
+                    if (!(tc > tr && R0 > j)) {
+                        double lo[8], up[8];
 #pragma unroll
-                    for (int rr = 0; rr < 8; ++rr)
+                        for (int k = 0; k < 8; ++k) { lo[k] = row_lo[R0 + k]; up[k] = row_up[R0 + k]; }
 #pragma unroll
-                        for (int cc = 0; cc < 8; ++cc)
-                            E[rr][cc] = fma(-((cc <= rr) ? lo[rr] : up[rr]), vc[cc], E[rr][cc]);
+                        for (int rr = 0; rr < 8; ++rr)
+#pragma unroll
+                            for (int cc = 0; cc < 8; ++cc)
+                                E[rr][cc] = fma(-((cc <= rr) ? lo[rr] : up[rr]), vc[cc], E[rr][cc]);
+                    }
                 }
-                __syncthreads();
             }
         }
     }
+    __syncthreads();                                   // the callers reuse the scratch and read xd
     return bad;
 }
 
