@@ -100,11 +100,20 @@ __device__ __forceinline__ int chol_inv_regs(double (&E)[8][8], int n, double* w
                     const int jn = j + 1;
                     if ((jn >> 3) == tc && jn < n) {
                         const double dn = pv[(jj + 1) & 7];           // compile-time index after unrolling
+#ifdef CI_EXP_NOSQRT                          /* timing experiment only: no square-root / reciprocal chain */
+                        s_next = dn;
+                        inv_next = 0.5;
+#else
                         s_next = __dsqrt_rn(dn);
                         inv_next = __drcp_rn(s_next);
+#endif
                     }
                     // tiles above the diagonal whose rows are all > j have not started
+#ifdef CI_EXP_NOFMA                           /* timing experiment only: no trailing update */
+                    if (false) {
+#else
                     if (!(tc > tr && R0 > j)) {
+#endif
                         double lo[8], up[8];
 #pragma unroll
                         for (int k = 0; k < 8; ++k) { lo[k] = row_lo[R0 + k]; up[k] = row_up[R0 + k]; }
