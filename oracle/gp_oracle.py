@@ -325,3 +325,16 @@ def synthetic_surface_table(r, n_exp, seed=0, p_gap=0.25):
     t[:, 0::2] = mu
     t[:, 1::2] = sd
     return t
+
+
+def adversarial_problem(n, d, seed=0, e_lo=1e-6, e_hi=1.0, n_isolated=8):
+    """Stress case for the emulated-FP64 row scales: e log-uniform over six decades, and a few isolated points
+    (far from every other point, so their row of K is ~ e_i^2 on the diagonal only) carrying the smallest e.
+    Returns x (d,n), y (n,), e (n,)."""
+    rng = np.random.default_rng(seed)
+    x = rng.random((d, n))
+    x[:, :n_isolated] = 3.0 + 2.0 * np.arange(n_isolated)[None, :] + rng.random((d, n_isolated))
+    y = np.sin(2 * np.pi * x).sum(axis=0) + 0.1 * rng.standard_normal(n)
+    e = np.exp(rng.uniform(np.log(e_lo), np.log(e_hi), n))
+    e[:n_isolated] = e_lo * (1.0 + rng.random(n_isolated))
+    return x, y, e

@@ -175,6 +175,55 @@ def gen_surface(ref):
     np.savez_compressed(os.path.join(OUT, "surface_cases.npz"), **d)
 
 
+def gen_large(ref):
+    """Reference outputs AT THE SIZES bench.py REPORTS: the C3 bench problem itself
+    (N=4096, d=3, seed 0; particles 0/85/170/255 of the 256-particle bench swarm + one on-bound particle),
+    a C4-sized GP() fit + 2000 grid points (N=8192, d=2), and an adversarial emulated-mode case (N=1024, e over six
+    decades with isolated points).  ~10 min of CPU in the build container."""
+    import time
+    d = {}
+    t0 = time.time()
+    x, y, e = orc.synthetic_problem(4096, 3, 0)
+    pos_all, lower, upper = orc.synthetic_particles(x, 256, 0)
+    pos = np.concatenate([pos_all[[0, 85, 170, 255]], pos_all[[7]]])
+    pos[4, 1] = upper[1]                      # on-bound -> 1e13 without a fit (find_len_scales.py:156)
+    c = loss_case(ref, x, y, e, pos, lower, upper)
+    c["swarm_index"] = np.array([0, 85, 170, 255, -1])
+    for k, v in c.items():
+        if k not in ("x", "y", "e"):          # regenerated from the seed by the test (checked by a digest)
+            d[f"c3_n4096__{k}"] = v
+    d["c3_n4096__xye_sum"] = np.array([x.sum(), y.sum(), e.sum()])
+    print("c3_n4096 min margin", c["margin"][:4].min(), "loss", c["loss"], f"{time.time()-t0:.0f}s", flush=True)
+
+    x, y, e = orc.adversarial_problem(1024, 2, 0)
+    lower, upper = orc.pso_bounds(x)
+    pos = orc.center_lhs(np.column_stack((lower, upper)), 4, np.random.RandomState(1))
+    c = loss_case(ref, x, y, e, pos, lower, upper)
+    for k, v in c.items():
+        d[f"adv_n1024__{k}"] = v
+    print("adv_n1024 min margin", c["margin"].min(), "loss", c["loss"], f"{time.time()-t0:.0f}s", flush=True)
+    np.savez_compressed(os.path.join(OUT, "loss_cases_large.npz"), **d)
+
+    g = {}
+    x, y, e = orc.synthetic_problem(8192, 2, 3)
+    rng = np.random.default_rng(103)
+    grid = rng.random((2000, 2))
+    ls = np.array([0.11, 0.17])
+    mu, sd = ref.GP_func.GP(x, y, e, grid.T, ls, batch_size=1000)
+    for k, v in dict(grid=grid, ls=ls, mu=mu, sd=sd).items():
+        g[f"c4_n8192__{k}"] = v
+    g["c4_n8192__xye_sum"] = np.array([x.sum(), y.sum(), e.sum()])
+    print("c4_n8192 GP done", f"{time.time()-t0:.0f}s", "sd range", sd.min(), sd.max(), flush=True)
+    x, y, e = orc.synthetic_problem(4096, 3, 0)
+    grid = np.random.default_rng(104).random((1500, 3))
+    ls = np.array([0.2, 0.3, 0.25])
+    mu, sd = ref.GP_func.GP(x, y, e, grid.T, ls)
+    for k, v in dict(grid=grid, ls=ls, mu=mu, sd=sd).items():
+        g[f"c3_n4096__{k}"] = v
+    print("c3_n4096 GP done", f"{time.time()-t0:.0f}s", flush=True)
+    np.savez_compressed(os.path.join(OUT, "gp_cases_large.npz"), **g)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ref = ref_shim.load()
