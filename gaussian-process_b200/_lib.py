@@ -20,20 +20,19 @@ SIGNATURES = {
     "gpk_staged_workspace_bytes": (_sz, [_i, _i]),
     "gpk_fit_alpha_batched": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _sz, _vp]),
     "gpk_selfpredict_counts": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
-    "gpk_loss_workspace_bytes": (_sz, [_i, _i, _i]),
-    "gpk_loss_batched": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
-    "gpk_fit_workspace_bytes": (_sz, [_i, _i]),
-    "gpk_fit": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "gpk_loss_workspace_bytes": (_sz, [_i, _i, _i, _i]),
+    "gpk_loss_batched": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, C.c_double, _vp, _vp, _vp, _vp, _vp,
+                              _vp, _vp, _sz, _vp]),
+    "gpk_fit_workspace_bytes": (_sz, [_i, _i, _i]),
+    "gpk_fit": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "gpk_predict_workspace_bytes": (_sz, [_i, _i]),
     "gpk_predict": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _ll, _vp, _vp, _i, _vp, _sz, _vp]),
     "gpk_predict_state_bytes": (_sz, [_i]),
     "gpk_predict_prepare": (_i, [_vp, _vp, _i, _vp, _sz, _vp]),
     "gpk_predict_emu_workspace_bytes": (_sz, [_i, _i]),
-    "gpk_predict_emu": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _ll, _vp, _vp, _i, _vp, _sz, _vp]),
+    "gpk_predict_emu": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _ll, _vp, _vp, _i, _vp, _sz, _vp]),
     "gpk_prob_surface": (_i, [_vp, _ll, _i, _i, _vp, _vp, _vp, _vp]),
-    "gpk_set_groups": (_i, [_i]),
-    "gpk_set_precision": (_i, [_i]),
-    "gpk_get_precision": (_i, []),
+    "gpk_set_groups": (_i, [_i, _i]),
     "gpk_oz_slice_bytes": (_sz, [_i, _i]),
     "gpk_oz_slice": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp]),
     "gpk_oz_gemm_tn": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _i, _vp, _i, _vp]),

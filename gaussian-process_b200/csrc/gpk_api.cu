@@ -73,7 +73,28 @@ int check_launch(const char* what) {
 constexpr int MAX_GROUPS = 8;
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
-static int g_precision = 0;    // 0 = native FP64 (DMMA), 1 = emulated FP64 on the int8 tcgen05 tensor cores
+// `precision` argument of the C ABI (include/gpk.h GPK_PREC_*) -> digit groups kept by the digit GEMM (0 = native FP64)
+static int groups_of(int precision) {
+    switch (precision) {
+        case GPK_PREC_EMU34: return 8;
+        case GPK_PREC_EMU28: return 7;
+        case GPK_PREC_EMU21: return 6;
+        case GPK_PREC_EMU15: return 5;
+        default: return 0;
+    }
+}
+static bool bad_precision(const char* who, int precision, int N) {
+    if (precision < GPK_PREC_FP64 || precision > GPK_PREC_EMU15) {
+        set_error("%s: precision %d (0 native FP64, 1..4 emulated FP64 with 34 / 28 / 21 / 15 digit products)", who, precision);
+        return true;
+    }
+    if (precision != GPK_PREC_FP64 && round_up(N, NB) >= 16384) {
+        // a group accumulator receives up to 8 digit products of magnitude <= 2^14 per k: exact in int32 for K < 2^14 only
+        set_error("%s: the emulated-FP64 modes support N <= 16256 (int32 accumulators); use precision 0", who);
+        return true;
+    }
+    return false;
+}
 
 BlockedLayout blocked_layout(int P, int N, int d, int emulated) {
     BlockedLayout L{};
@@ -92,6 +113,12 @@ BlockedLayout blocked_layout(int P, int N, int d, int emulated) {
     L.cn = take((size_t)P * Np * 8);
     L.z = take((size_t)P * Np * 8);
     L.alpha = take((size_t)P * Np * 8);
+    L.pkv = take((size_t)P * T * Np * 8);
+    L.pu = take((size_t)P * Np * 8);
+    L.pt = take((size_t)P * Np * 8);
+    L.pw = take((size_t)P * Np * 8);
+    L.probe = take((size_t)P * 8);
+    L.fail = take((size_t)P);
     L.oz_slices = L.oz_mt = L.oz_rows = L.oz_mtsc = L.oz_sdig = L.oz_ddig = L.oz_dsc = L.oz_cnt = 0;
     if (emulated) {
         L.oz_slices = take((size_t)P * oz_slice_bytes(L.Np));
@@ -189,6 +216,7 @@ static int inverse_phase(double* mat, int Np, int T, int P, const double* dinvT,
 
 // ---- concurrent particle groups ------------------------------------------------------------------
 static int g_groups = 4;
+static int g_min_group = 32;       // particles per group below which a swarm is not split further (gpk_set_groups)
 static cudaStream_t g_group_streams[MAX_GROUPS] = {};
 static cudaEvent_t g_join[MAX_GROUPS] = {};
 static cudaEvent_t g_fork = nullptr;
@@ -298,8 +326,8 @@ int gpk_fit_alpha_batched(const double* L, const double* y, int P, int N, int Np
     char* ws = (char*)workspace;
     if (staged_inverse(L, P, Np, ws, S, nullptr, st)) return 1;
     const double* mat = (const double*)(ws + S.mat);
-    if (launch_wy(mat, Np, N, P, y, (double*)(ws + S.z), nullptr, st)) return 1;
-    return launch_colnorm_alpha(mat, Np, P, (const double*)(ws + S.z), (double*)(ws + S.cn), alpha_out, nullptr, st);
+    if (launch_wy(mat, Np, N, P, y, (double*)(ws + S.z), nullptr, nullptr, nullptr, st)) return 1;
+    return launch_colnorm_alpha(mat, Np, P, (const double*)(ws + S.z), (double*)(ws + S.cn), alpha_out, nullptr, nullptr, nullptr, st);
 }
 
 int gpk_selfpredict_counts(const double* L, const double* alpha, const double* y, const double* e,
@@ -317,44 +345,92 @@ int gpk_selfpredict_counts(const double* L, const double* alpha, const double* y
     const double* mat = (const double*)(ws + SL.mat);
     // column norms of W (diag of K^-1); the alpha this kernel also forms from z goes to scratch
     if (cudaMemsetAsync(ws + SL.z, 0, (size_t)P * Np * 8, st) != cudaSuccess) { set_error("memset z failed"); return 1; }
-    if (launch_colnorm_alpha(mat, Np, P, (const double*)(ws + SL.z), (double*)(ws + SL.cn), (double*)(ws + SL.alpha), active, st)) return 1;
-    return launch_counts(alpha, (const double*)(ws + SL.cn), e, sigma_vals, P, N, Np, S, counts_out, resid_out, sig_out, active, st);
+    if (launch_colnorm_alpha(mat, Np, P, (const double*)(ws + SL.z), (double*)(ws + SL.cn), (double*)(ws + SL.alpha), nullptr, nullptr, active, st)) return 1;
+    return launch_counts(alpha, (const double*)(ws + SL.cn), e, sigma_vals, P, N, Np, S, counts_out, resid_out, sig_out,
+                         nullptr, 0.0, nullptr, nullptr, 1, active, st);
 }
 
-size_t gpk_loss_workspace_bytes(int P, int N, int d) {
+size_t gpk_loss_workspace_bytes(int P, int N, int d, int precision) {
     if (N <= SMALL_N_MAX) return 256;
     size_t best = 0;                      // enough for any particle-group split (gpk_set_groups)
     for (int G = 1; G <= MAX_GROUPS; ++G) {
-        const size_t b = (size_t)G * blocked_layout((P + G - 1) / G, N, d, g_precision).total;
+        const size_t b = (size_t)G * blocked_layout((P + G - 1) / G, N, d, precision != GPK_PREC_FP64).total;
         if (b > best) best = b;
     }
     return best;
 }
 
+// One pass of the blocked path over the particles of one group: covariance -> Cholesky -> inverse -> alpha, column norms ->
+// counts.  emu: the contractions run on the digit GEMM (oz_set_groups done by the caller).  probe: the residual probe is
+// formed on the way (rho -> ws.probe, rho > tol -> ws.fail).  zero_inactive = 0: particles outside `act` are left untouched.
+static int blocked_pass(const double* X, const double* y, const double* e, const double* lsp, const unsigned char* act,
+                        const double* sigma_vals, int Pc, int N, int d, int S, int* counts, int* info, double* resid_out,
+                        double* sig_out, char* ws, const BlockedLayout& L, int emu, bool probe, double tol,
+                        int zero_inactive, cudaStream_t gs) {
+    OzBuffers oz;
+    if (emu) {
+        oz = oz_buffers(ws, L);
+        if (cudaMemsetAsync(oz.cnt, 0, (4 * L.T + 8) * sizeof(int), gs) != cudaSuccess) { set_error("memset counters failed"); return 1; }
+        if (launch_oz_prep(e, N, L.Np, oz.rowsig, oz.rowinv, oz.gam, oz.gaminv, gs)) return 1;
+    }
+    double* mat = (double*)(ws + L.mat);
+    double* dinv = (double*)(ws + L.dinv);
+    double* dinvT = (double*)(ws + L.dinvT);
+    double* mt = (double*)(ws + L.mt);
+    double* xs = (double*)(ws + L.xs);
+    double* sq = (double*)(ws + L.sq);
+    double* cn = (double*)(ws + L.cn);
+    double* z = (double*)(ws + L.z);
+    double* alpha = (double*)(ws + L.alpha);
+    double* pkv = probe ? (double*)(ws + L.pkv) : nullptr;
+    double* pu = probe ? (double*)(ws + L.pu) : nullptr;
+    double* pt = probe ? (double*)(ws + L.pt) : nullptr;
+    double* pw = probe ? (double*)(ws + L.pw) : nullptr;
+    if (launch_scale_points(X, lsp, Pc, N, L.Np, d, xs, sq, act, gs)) return 1;
+    if (launch_cov_lower(xs, sq, e, Pc, N, L.Np, d, mat, pkv, act, gs)) return 1;
+    if (probe && launch_probe_sum(pkv, L.Np, L.T, Pc, pu, act, gs)) return 1;
+    if (factor_phase(mat, L.Np, L.T, Pc, dinv, dinvT, info, act, DIAG_WRITE_INVERSE, oz, gs)) return 1;
+    if (inverse_phase(mat, L.Np, L.T, Pc, dinvT, mt, act, oz, gs)) return 1;
+    if (launch_wy(mat, L.Np, N, Pc, y, z, pu, pt, act, gs)) return 1;
+    if (launch_colnorm_alpha(mat, L.Np, Pc, z, cn, alpha, pt, pw, act, gs)) return 1;
+    return launch_counts(alpha, cn, e, sigma_vals, Pc, N, L.Np, S, counts, resid_out, sig_out, pw, tol,
+                         (double*)(ws + L.probe), (unsigned char*)(ws + L.fail), zero_inactive, act, gs);
+}
+
 int gpk_loss_batched(const double* X, const double* y, const double* e, const double* ls,
                      const unsigned char* active, const double* sigma_vals, int P, int N, int d, int S,
-                     int* counts_out, int* info, double* resid_out, double* sig_out, void* workspace,
+                     int precision, int form, double check_tol, int* counts_out, int* info, double* resid_out,
+                     double* sig_out, double* probe_out, unsigned char* fallback_out, void* workspace,
                      size_t workspace_bytes, void* stream) {
     if (bad_dims("gpk_loss_batched", N, d, S) || P < 1) return 2;
+    if (bad_precision("gpk_loss_batched", precision, N)) return 2;
+    if (form != GPK_FORM_REDUCED && form != GPK_FORM_REFERENCE) { set_error("gpk_loss_batched: form %d", form); return 2; }
+    if (form == GPK_FORM_REFERENCE && N > SMALL_N_MAX) {
+        set_error("gpk_loss_batched: the reference-formula form (N^3 solve) exists on the one-CTA path only, N <= %d", SMALL_N_MAX);
+        return 2;
+    }
     cudaStream_t st = (cudaStream_t)stream;
     set_stream(st);
     if (cudaMemsetAsync(info, 0, (size_t)P * sizeof(int), st) != cudaSuccess) { set_error("memset info failed"); return 1; }
-    if (N <= SMALL_N_MAX)
-        return launch_small_loss(X, y, e, ls, active, sigma_vals, P, N, d, S, counts_out, info, resid_out, sig_out, st);
-
-    if (g_precision && round_up(N, NB) >= 16384) {
-        // a group accumulator receives up to 8 digit products of magnitude <= 2^14 per k: exact in int32 for K < 2^14 only
-        set_error("gpk_loss_batched: the emulated-FP64 mode supports N <= 16256 (int32 accumulators); use mode 0");
-        return 2;
+    if (N <= SMALL_N_MAX) {
+        // native FP64 in one CTA per particle: nothing is emulated, nothing to check
+        if (probe_out && cudaMemsetAsync(probe_out, 0, (size_t)P * 8, st) != cudaSuccess) { set_error("memset probe failed"); return 1; }
+        if (fallback_out && cudaMemsetAsync(fallback_out, 0, (size_t)P, st) != cudaSuccess) { set_error("memset fallback failed"); return 1; }
+        return launch_small_loss(X, y, e, ls, active, sigma_vals, P, N, d, S, counts_out, info, resid_out, sig_out, form, st);
     }
+
     // blocked path: waves of as many particles as the workspace holds, each wave split into independent
     // particle groups on concurrent streams (the chain SYRK -> diag -> TRSM of one group is serial; kernels of
     // other groups fill its wave tails and hide the latency-bound diagonal kernel)
-    const int emu = g_precision;
+    const int emu = precision != GPK_PREC_FP64;
+    if (emu) oz_set_groups(groups_of(precision));
+    const bool probe = check_tol > 0.0 || probe_out != nullptr;
+    const bool fallback = emu && check_tol > 0.0;
+    const double tol = check_tol > 0.0 ? check_tol : 1e300;
     const size_t per1 = blocked_layout(1, N, d, emu).total;
     if (workspace == nullptr || workspace_bytes < per1) { set_error("gpk_loss_batched: workspace too small (%zu < %zu)", workspace_bytes, per1); return 3; }
     int G = g_timing ? 1 : g_groups;
-    if (G > P / 8) G = P / 8;
+    if (G > P / g_min_group) G = P / g_min_group;
     if (G < 1) G = 1;
     if (G > 1 && ensure_group_streams(G)) return 1;
     auto fits = [&](int pw) { const int pg = (pw + G - 1) / G; return (size_t)G * blocked_layout(pg, N, d, emu).total <= workspace_bytes; };
@@ -374,31 +450,27 @@ int gpk_loss_batched(const double* X, const double* y, const double* e, const do
             if (G > 1) cudaStreamWaitEvent(gs, g_fork, 0);
             const BlockedLayout L = blocked_layout(Pc, N, d, emu);
             char* ws = (char*)workspace + (size_t)g * gbytes;
-            const OzBuffers oz = oz_buffers(ws, L);
-            if (emu) {
-                if (cudaMemsetAsync(oz.cnt, 0, (4 * L.T + 8) * sizeof(int), gs) != cudaSuccess) { set_error("memset counters failed"); return 1; }
-                if (launch_oz_prep(e, N, L.Np, oz.rowsig, oz.rowinv, oz.gam, oz.gaminv, gs)) return 1;
-            }
-            double* mat = (double*)(ws + L.mat);
-            double* dinv = (double*)(ws + L.dinv);
-            double* dinvT = (double*)(ws + L.dinvT);
-            double* mt = (double*)(ws + L.mt);
-            double* xs = (double*)(ws + L.xs);
-            double* sq = (double*)(ws + L.sq);
-            double* cn = (double*)(ws + L.cn);
-            double* z = (double*)(ws + L.z);
-            double* alpha = (double*)(ws + L.alpha);
             const unsigned char* act = active ? active + q0 : nullptr;
             const double* lsp = ls + (size_t)q0 * d;
-            if (launch_scale_points(X, lsp, Pc, N, L.Np, d, xs, sq, act, gs)) return 1;
-            if (launch_cov_lower(xs, sq, e, Pc, N, L.Np, d, mat, act, gs)) return 1;
-            if (factor_phase(mat, L.Np, L.T, Pc, dinv, dinvT, info + q0, act, DIAG_WRITE_INVERSE, oz, gs)) return 1;
-            if (inverse_phase(mat, L.Np, L.T, Pc, dinvT, mt, act, oz, gs)) return 1;
-            if (launch_wy(mat, L.Np, N, Pc, y, z, act, gs)) return 1;
-            if (launch_colnorm_alpha(mat, L.Np, Pc, z, cn, alpha, act, gs)) return 1;
-            if (launch_counts(alpha, cn, e, sigma_vals, Pc, N, L.Np, S, counts_out + (size_t)q0 * S,
-                              resid_out ? resid_out + (size_t)q0 * N : nullptr,
-                              sig_out ? sig_out + (size_t)q0 * N : nullptr, act, gs)) return 1;
+            int* cnt = counts_out + (size_t)q0 * S;
+            double* rs = resid_out ? resid_out + (size_t)q0 * N : nullptr;
+            double* sg = sig_out ? sig_out + (size_t)q0 * N : nullptr;
+            if (blocked_pass(X, y, e, lsp, act, sigma_vals, Pc, N, d, S, cnt, info + q0, rs, sg, ws, L, emu, probe, tol, 1, gs)) return 1;
+            if (probe_out && cudaMemcpyAsync(probe_out + q0, ws + L.probe, (size_t)Pc * 8, cudaMemcpyDeviceToDevice, gs) != cudaSuccess) { set_error("copy of the probe values failed"); return 1; }
+            if (fallback_out) {
+                cudaError_t ce = probe ? cudaMemcpyAsync(fallback_out + q0, ws + L.fail, (size_t)Pc, cudaMemcpyDeviceToDevice, gs)
+                                       : cudaMemsetAsync(fallback_out + q0, 0, (size_t)Pc, gs);
+                if (ce != cudaSuccess) { set_error("copy of the fallback flags failed"); return 1; }
+            }
+            if (fallback) {
+                // checked mixed precision: the particles whose probe failed are evaluated again by the native FP64 (DMMA)
+                // kernels, in the same call and on the same stream, with the fail flags as the active mask.  No host
+                // synchronisation (the call stays asynchronous and capturable): when nothing failed, every kernel of this
+                // pass exits at its first instruction.  The flags are copied first: this pass reuses the workspace.
+                unsigned char* mask = (unsigned char*)(ws + L.fail);
+                if (launch_clear_info(info + q0, mask, Pc, gs)) return 1;
+                if (blocked_pass(X, y, e, lsp, mask, sigma_vals, Pc, N, d, S, cnt, info + q0, rs, sg, ws, L, 0, false, 0.0, 0, gs)) return 1;
+            }
             if (G > 1) {
                 cudaEventRecord(g_join[g], gs);
                 cudaStreamWaitEvent(st, g_join[g], 0);
@@ -408,25 +480,28 @@ int gpk_loss_batched(const double* X, const double* y, const double* e, const do
     return 0;
 }
 
-size_t gpk_fit_workspace_bytes(int N, int d) {
+size_t gpk_fit_workspace_bytes(int N, int d, int precision) {
     (void)d;
     const size_t Np = round_up(N, NB), T = Np / NB;
     size_t b = 2 * align256(T * NB * NB * 8) + align256(NB * Np * 8) + 2 * align256(Np * 8);
-    if (g_precision)
+    b += align256(T * Np * 8) + 3 * align256(Np * 8) + 2 * align256(8);                 // residual probe
+    if (precision != GPK_PREC_FP64)
         b += align256(oz_slice_bytes((int)Np)) + align256(oz_mt_bytes((int)Np)) + align256(4 * Np * 8) + align256(3 * NB * 8) +
              align256(oz_panel_bytes((int)Np)) + align256(oz_ddig_bytes((int)Np)) + align256(T * 2 * NB * 8) +
              align256((4 * T + 8) * sizeof(int));
     return b;
 }
 
-int gpk_fit(const double* X, const double* y, const double* e, const double* ls, int N, int d, double* W_out,
-            double* alpha_out, double* xs_out, double* sq_out, int* info, void* workspace, size_t workspace_bytes,
-            void* stream) {
+int gpk_fit(const double* X, const double* y, const double* e, const double* ls, int N, int d, int precision,
+            double* W_out, double* alpha_out, double* xs_out, double* sq_out, int* info, double* probe_out,
+            void* workspace, size_t workspace_bytes, void* stream) {
     if (bad_dims("gpk_fit", N, d, 0)) return 2;
-    if (g_precision && round_up(N, NB) >= 16384) { set_error("gpk_fit: the emulated-FP64 mode supports N <= 16256 (int32 accumulators); use mode 0"); return 2; }
-    if (workspace_bytes < gpk_fit_workspace_bytes(N, d)) { set_error("gpk_fit: workspace too small"); return 3; }
+    if (bad_precision("gpk_fit", precision, N)) return 2;
+    if (workspace_bytes < gpk_fit_workspace_bytes(N, d, precision)) { set_error("gpk_fit: workspace too small"); return 3; }
     cudaStream_t st = (cudaStream_t)stream;
     set_stream(st);
+    const int emu = precision != GPK_PREC_FP64;
+    if (emu) oz_set_groups(groups_of(precision));
     const int Np = round_up(N, NB), T = Np / NB;
     char* ws = (char*)workspace;
     size_t off = 0;
@@ -435,8 +510,15 @@ int gpk_fit(const double* X, const double* y, const double* e, const double* ls,
     double* mt = (double*)(ws + off); off += align256((size_t)NB * Np * 8);
     double* z = (double*)(ws + off); off += align256((size_t)Np * 8);
     double* cn = (double*)(ws + off); off += align256((size_t)Np * 8);
+    double* pkv = (double*)(ws + off); off += align256((size_t)T * Np * 8);
+    double* pu = (double*)(ws + off); off += align256((size_t)Np * 8);
+    double* pt = (double*)(ws + off); off += align256((size_t)Np * 8);
+    double* pw = (double*)(ws + off); off += align256((size_t)Np * 8);
+    double* rho = (double*)(ws + off); off += align256(8);
+    unsigned char* fail = (unsigned char*)(ws + off); off += align256(8);
+    const bool probe = probe_out != nullptr;
     OzBuffers oz;
-    if (g_precision) {
+    if (emu) {
         oz.slices = (uint8_t*)(ws + off); off += align256(oz_slice_bytes(Np));
         oz.mtslices = (uint8_t*)(ws + off); off += align256(oz_mt_bytes(Np));
         double* r = (double*)(ws + off); off += align256((size_t)4 * Np * 8);
@@ -452,11 +534,16 @@ int gpk_fit(const double* X, const double* y, const double* e, const double* ls,
     }
     if (cudaMemsetAsync(info, 0, sizeof(int), st) != cudaSuccess) { set_error("memset info failed"); return 1; }
     if (launch_scale_points(X, ls, 1, N, Np, d, xs_out, sq_out, nullptr, st)) return 1;
-    if (launch_cov_lower(xs_out, sq_out, e, 1, N, Np, d, W_out, nullptr, st)) return 1;
+    if (launch_cov_lower(xs_out, sq_out, e, 1, N, Np, d, W_out, probe ? pkv : nullptr, nullptr, st)) return 1;
+    if (probe && launch_probe_sum(pkv, Np, T, 1, pu, nullptr, st)) return 1;
     if (factor_phase(W_out, Np, T, 1, dinv, dinvT, info, nullptr, DIAG_WRITE_INVERSE, oz, st)) return 1;
     if (inverse_phase(W_out, Np, T, 1, dinvT, mt, nullptr, oz, st)) return 1;
-    if (launch_wy(W_out, Np, N, 1, y, z, nullptr, st)) return 1;
-    if (launch_colnorm_alpha(W_out, Np, 1, z, cn, alpha_out, nullptr, st)) return 1;
+    if (launch_wy(W_out, Np, N, 1, y, z, probe ? pu : nullptr, pt, nullptr, st)) return 1;
+    if (launch_colnorm_alpha(W_out, Np, 1, z, cn, alpha_out, probe ? pt : nullptr, pw, nullptr, st)) return 1;
+    if (probe) {
+        if (launch_probe_value(pw, N, Np, 1, rho, fail, 1e300, nullptr, st)) return 1;
+        if (cudaMemcpyAsync(probe_out, rho, 8, cudaMemcpyDeviceToDevice, st) != cudaSuccess) { set_error("copy of the probe value failed"); return 1; }
+    }
     return 0;
 }
 
@@ -501,9 +588,14 @@ size_t gpk_predict_emu_workspace_bytes(int N, int chunk) {
 }
 
 int gpk_predict_emu(const void* state, const double* alpha, const double* xs, const double* sq, const double* ls, int N,
-                    int d, const double* Xfit, long long M, double* mu_out, double* sd_out, int chunk, void* workspace,
-                    size_t workspace_bytes, void* stream) {
+                    int d, int precision, const double* Xfit, long long M, double* mu_out, double* sd_out, int chunk,
+                    void* workspace, size_t workspace_bytes, void* stream) {
     if (bad_dims("gpk_predict_emu", N, d, 0) || chunk < 1) return 2;
+    if (precision == GPK_PREC_FP64 || bad_precision("gpk_predict_emu", precision, N)) {
+        if (precision == GPK_PREC_FP64) set_error("gpk_predict_emu: an emulated precision (GPK_PREC_EMU*) is required; gpk_predict is the native path");
+        return 2;
+    }
+    oz_set_groups(groups_of(precision));
     if (M <= 0) return 0;
     if (workspace_bytes < gpk_predict_emu_workspace_bytes(N, chunk)) { set_error("gpk_predict_emu: workspace too small"); return 3; }
     cudaStream_t st = (cudaStream_t)stream;
@@ -533,14 +625,6 @@ int gpk_sum_gaussians(const double* y, int n, const double* gaus, int ng, double
     return launch_sum_gaussians(y, n, gaus, ng, half_dy, p_out, (cudaStream_t)stream);
 }
 
-int gpk_set_precision(int mode) {
-    if (mode < 0 || mode > 2) { set_error("gpk_set_precision: 0 (native FP64), 1 (emulated FP64, 34 digit products) or 2 (emulated, 28 digit products)"); return 2; }
-    g_precision = mode ? 1 : 0;
-    if (mode) oz_set_groups(mode == 2 ? 7 : 8);
-    return 0;
-}
-int gpk_get_precision(void) { return g_precision ? (oz_get_groups() == 7 ? 2 : 1) : 0; }
-
 size_t gpk_oz_slice_bytes(int rows, int cols) { return (size_t)(rows / NB) * (cols / 32) * (oz_mt_bytes(32)); }
 
 int gpk_oz_slice(const double* src, int ld, int rows, int cols, const double* rowinv, void* dst, void* stream) {
@@ -551,15 +635,17 @@ int gpk_oz_slice(const double* src, int ld, int rows, int cols, const double* ro
 
 int gpk_oz_gemm_tn(const void* A, const void* B, int M, int N, int K, const double* sa, const double* sb, double* C,
                    int ldc, int* dbg, int groups, void* stream) {
+    if (groups < 5 || groups > 8) { set_error("gpk_oz_gemm_tn: groups 5..8 (15 / 21 / 28 / 34 digit products)"); return 2; }
     oz_set_groups(groups);
     if (M < NB || M % NB || N < NB || N % NB || K < NB || K % NB) { set_error("gpk_oz_gemm_tn: M, N, K must be positive multiples of %d", NB); return 2; }
     set_stream((cudaStream_t)stream);
     return launch_oz_gemm_tn((const uint8_t*)A, (const uint8_t*)B, M, N, K, sa, sb, C, ldc, dbg, (cudaStream_t)stream);
 }
 
-int gpk_set_groups(int groups) {
-    if (groups < 1 || groups > MAX_GROUPS) { set_error("gpk_set_groups: 1..%d", MAX_GROUPS); return 2; }
+int gpk_set_groups(int groups, int min_particles_per_group) {
+    if (groups < 1 || groups > MAX_GROUPS || min_particles_per_group < 1) { set_error("gpk_set_groups: groups 1..%d, at least 1 particle per group", MAX_GROUPS); return 2; }
     g_groups = groups;
+    g_min_group = min_particles_per_group;
     return 0;
 }
 

@@ -18,6 +18,19 @@ int check_launch(const char* what);   // cudaGetLastError -> status; also counts
 
 inline int round_up(int x, int m) { return (x + m - 1) / m * m; }
 
+#ifdef __CUDACC__
+// Fixed pseudo-random probe vector of the a-posteriori residual check (gpk_loss_batched / gpk_fit, include/gpk.h):
+// v_i = +-[0.5, 1) from a hash of the index, the same for every particle and every call.
+__device__ __forceinline__ double probe_v(int i) {
+    unsigned long long z = (unsigned long long)(unsigned)i * 0x9E3779B97F4A7C15ull + 0xD1B54A32D192ED03ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    const double m = 0.5 + (double)(z >> 12) * 0x1p-53;
+    return (z & 1ull) ? -m : m;
+}
+#endif
+
 // ---- workspace layout of the blocked loss / fit path ------------------------------------
 // All offsets in bytes, each section 256-byte aligned.
 struct BlockedLayout {
@@ -31,6 +44,13 @@ struct BlockedLayout {
     size_t cn;       // [P][Np]        column sums of squares of W  (= diag K^-1)
     size_t z;        // [P][Np]        W y
     size_t alpha;    // [P][Np]        W^T z = K^-1 y
+    // a-posteriori residual probe (include/gpk.h, check_tol): rho = |W^T W K v - v|_inf / |v|_inf for the fixed vector probe_v
+    size_t pkv;      // [P][T][Np]     per-tile partial sums of K v left by the covariance kernel
+    size_t pu;       // [P][Np]        u = K v
+    size_t pt;       // [P][Np]        t = W u
+    size_t pw;       // [P][Np]        w = W^T t
+    size_t probe;    // [P]            rho
+    size_t fail;     // [P] bytes      rho > check_tol: re-evaluated by the native FP64 kernels
     // emulated-FP64 (int8 digit) mode only, gpk_oz.cu:
     size_t oz_slices;  // [P] digit records of L (phase 1) then W gamma (phase 2), oz_slice_bytes(Np) each
     size_t oz_mt;      // [P] digit records of the phase-2 panel, oz_mt_bytes(Np) each
@@ -49,7 +69,7 @@ BlockedLayout blocked_layout(int P, int N, int d, int emulated);
 int launch_scale_points(const double* X, const double* ls, int P, int N, int Np, int d,
                         double* xs, double* sq, const unsigned char* active, cudaStream_t st);
 int launch_cov_lower(const double* xs, const double* sq, const double* e, int P, int N, int Np, int d,
-                     double* mat, const unsigned char* active, cudaStream_t st);
+                     double* mat, double* kv, const unsigned char* active, cudaStream_t st);
 int launch_cov_full(const double* X1, const double* X2, const double* e, const double* ls, int P,
                     int N1, int N2, int d, double* K, long long ldk, long long strideK, cudaStream_t st);
 int launch_cross_cov(const double* xs, const double* sq, const double* ls, const double* alpha, int N, int Np,
@@ -117,14 +137,19 @@ int oz_get_groups();
 // gpk_loss.cu
 int launch_small_loss(const double* X, const double* y, const double* e, const double* ls,
                       const unsigned char* active, const double* sigma_vals, int P, int N, int d, int S,
-                      int* counts, int* info, double* resid_out, double* sig_out, cudaStream_t st);
-int launch_wy(const double* mat, int Np, int N, int P, const double* y, double* z,
+                      int* counts, int* info, double* resid_out, double* sig_out, int form, cudaStream_t st);
+int launch_wy(const double* mat, int Np, int N, int P, const double* y, double* z, const double* pu, double* pt,
               const unsigned char* active, cudaStream_t st);
 int launch_colnorm_alpha(const double* mat, int Np, int P, const double* z, double* cn, double* alpha,
-                         const unsigned char* active, cudaStream_t st);
+                         const double* pt, double* pw, const unsigned char* active, cudaStream_t st);
+int launch_probe_sum(const double* kv, int Np, int T, int P, double* u, const unsigned char* active, cudaStream_t st);
 int launch_counts(const double* alpha, const double* cn, const double* e, const double* sigma_vals,
-                  int P, int N, int Np, int S, int* counts, double* resid_out, double* sig_out,
+                  int P, int N, int Np, int S, int* counts, double* resid_out, double* sig_out, const double* pw,
+                  double tol, double* probe, unsigned char* fail, int zero_inactive,
                   const unsigned char* active, cudaStream_t st);
+int launch_probe_value(const double* pw, int N, int Np, int P, double* probe, unsigned char* fail, double tol,
+                       const unsigned char* active, cudaStream_t st);
+int launch_clear_info(int* info, const unsigned char* mask, int P, cudaStream_t st);
 int launch_predict_finalize(const double* partial, int T, int Bp, int B, double* sigma_out, cudaStream_t st);
 
 // gpk_surface.cu

@@ -42,37 +42,73 @@ int launch_scale_points(const double* X, const double* ls, int P, int N, int Np,
     return check_launch("k_scale_points");
 }
 
-// rows r = (threadIdx.x >> 7), +2, ... of tile (I, .) for column j: K_ij + delta_ij e_i^2, identity in the padding
-template <int D>
-__device__ __forceinline__ void cov_lower_rows(const double* __restrict__ xsp, const double* __restrict__ sqp,
-                                               const double* __restrict__ e, int N, int Np, int I, int j,
-                                               const double (*s_xi)[NB], const double* s_sqi, double* __restrict__ out) {
+// rows r = (threadIdx.x >> 7), +2, ... of tile (I, .) for column j: K_ij + delta_ij e_i^2, identity in the padding.
+// PROBE: the tile's contributions to u = K v (v = probe_v, the residual probe of include/gpk.h) are formed on the way:
+// row sums sum_j K_ij v_j into s_row[warp & 3][r] (one partial per warp = 32 columns) and the column sum
+// sum_i K_ij v_i of this thread's 64 rows (returned).
+template <int D, bool PROBE>
+__device__ __forceinline__ double cov_lower_rows(const double* __restrict__ xsp, const double* __restrict__ sqp,
+                                                 const double* __restrict__ e, int N, int Np, int I, int j,
+                                                 const double (*s_xi)[NB], const double* s_sqi, double* __restrict__ out,
+                                                 double (*s_row)[NB], const double* s_pvi) {
     double xj[D];
 #pragma unroll
     for (int dd = 0; dd < D; ++dd) xj[dd] = xsp[(size_t)dd * Np + j];
     const double sqj = sqp[j];
-    for (int r = threadIdx.x >> 7; r < NB; r += 2) {
-        const int i = I * NB + r;
-        double v;
-        if (i < N && j < N) {
-            double dot = __dmul_rn(s_xi[0][r], xj[0]);
+    const double vj = (PROBE && j < N) ? probe_v(j) : 0.0;
+    const int lane = threadIdx.x & 31, wq = (threadIdx.x >> 5) & 3;
+    double colsum = 0.0;
+    double rowv[32];
 #pragma unroll
-            for (int dd = 1; dd < D; ++dd) dot = fma(s_xi[dd][r], xj[dd], dot);
-            v = rbf_from_parts(s_sqi[r], sqj, dot);
-            if (i == j) { const double ee = e[i]; v = __dadd_rn(v, __dmul_rn(ee, ee)); }
-        } else {
-            v = (i == j) ? 1.0 : 0.0;
+    for (int half = 0; half < 2; ++half) {
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+            const int r = (threadIdx.x >> 7) + 2 * (half * 32 + k);
+            const int i = I * NB + r;
+            double v;
+            if (i < N && j < N) {
+                double dot = __dmul_rn(s_xi[0][r], xj[0]);
+#pragma unroll
+                for (int dd = 1; dd < D; ++dd) dot = fma(s_xi[dd][r], xj[dd], dot);
+                v = rbf_from_parts(s_sqi[r], sqj, dot);
+                if (i == j) { const double ee = e[i]; v = __dadd_rn(v, __dmul_rn(ee, ee)); }
+            } else {
+                v = (i == j) ? 1.0 : 0.0;
+            }
+            out[(size_t)i * Np + j] = v;
+            if (PROBE) {
+                rowv[k] = v * vj;
+                colsum = fma(v, s_pvi[r], colsum);
+            }
         }
-        out[(size_t)i * Np + j] = v;
+        if (PROBE) {
+            // 32 rows x 32 lanes (columns) -> lane l holds the warp's sum of row k = l (butterfly, 31 exchanges)
+#pragma unroll
+            for (int step = 16; step >= 1; step >>= 1) {
+                const bool up = (lane & step) != 0;
+#pragma unroll
+                for (int i2 = 0; i2 < step; ++i2) {
+                    const double send = up ? rowv[i2] : rowv[i2 + step];
+                    const double keep = up ? rowv[i2 + step] : rowv[i2];
+                    rowv[i2] = keep + __shfl_xor_sync(0xffffffffu, send, step);
+                }
+            }
+            s_row[wq][(threadIdx.x >> 7) + 2 * (half * 32 + lane)] = rowv[0];
+        }
     }
+    return colsum;
 }
 
 // ---------------------------------------------------------------------------------------------
 // Lower block triangle of K + diag(e^2) for every particle, written straight into the factorisation
 // buffer.  One CTA per 128x128 tile (I >= J); padding rows/cols become the identity.
+// kv != nullptr ([P][T][Np]): slot [B][i] receives the contribution to (K v)_i of the tile that pairs row block of i with
+// block B -- tile (I, J) writes its row sums to [J][rows of I] and, for I > J, its column sums (K is symmetric) to
+// [I][columns of J]: every slot is written exactly once, k_probe_sum adds them in a fixed order.
+template <bool PROBE>
 __global__ void __launch_bounds__(256) k_cov_lower(const double* __restrict__ xs, const double* __restrict__ sq,
                                                    const double* __restrict__ e, int N, int Np, int d,
-                                                   double* __restrict__ mat,
+                                                   double* __restrict__ mat, double* __restrict__ kv,
                                                    const unsigned char* __restrict__ active) {
     const int p = blockIdx.y;
     if (active && !active[p]) return;
@@ -85,13 +121,19 @@ __global__ void __launch_bounds__(256) k_cov_lower(const double* __restrict__ xs
 
     __shared__ double s_xi[MAX_D][NB];
     __shared__ double s_sqi[NB];
+    __shared__ double s_row[PROBE ? 4 : 1][NB];
+    __shared__ double s_col[PROBE ? 2 : 1][NB];
+    __shared__ double s_pvi[PROBE ? NB : 1];
     const double* xsp = xs + (size_t)p * d * Np;
     const double* sqp = sq + (size_t)p * Np;
     for (int k = threadIdx.x; k < d * NB; k += blockDim.x) {
         const int dd = k / NB, r = k % NB;
         s_xi[dd][r] = xsp[(size_t)dd * Np + I * NB + r];
     }
-    if (threadIdx.x < NB) s_sqi[threadIdx.x] = sqp[I * NB + threadIdx.x];
+    if (threadIdx.x < NB) {
+        s_sqi[threadIdx.x] = sqp[I * NB + threadIdx.x];
+        if (PROBE) s_pvi[threadIdx.x] = (I * NB + threadIdx.x < N) ? probe_v(I * NB + threadIdx.x) : 0.0;
+    }
     __syncthreads();
 
     const int c = threadIdx.x & (NB - 1);
@@ -99,23 +141,36 @@ __global__ void __launch_bounds__(256) k_cov_lower(const double* __restrict__ xs
     double* out = mat + (size_t)p * Np * Np;
     // the dimension loop is unrolled for the actual d (a run-time bound costs MAX_D predicated load / FMA pairs per
     // element in issue slots); same operations in the same order for every D
+    double colsum;
     switch (d) {
-        case 1: cov_lower_rows<1>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out); break;
-        case 2: cov_lower_rows<2>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out); break;
-        case 3: cov_lower_rows<3>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out); break;
-        case 4: cov_lower_rows<4>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out); break;
-        case 5: cov_lower_rows<5>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out); break;
-        case 6: cov_lower_rows<6>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out); break;
-        case 7: cov_lower_rows<7>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out); break;
-        default: cov_lower_rows<8>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out); break;
+        case 1: colsum = cov_lower_rows<1, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_row, s_pvi); break;
+        case 2: colsum = cov_lower_rows<2, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_row, s_pvi); break;
+        case 3: colsum = cov_lower_rows<3, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_row, s_pvi); break;
+        case 4: colsum = cov_lower_rows<4, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_row, s_pvi); break;
+        case 5: colsum = cov_lower_rows<5, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_row, s_pvi); break;
+        case 6: colsum = cov_lower_rows<6, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_row, s_pvi); break;
+        case 7: colsum = cov_lower_rows<7, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_row, s_pvi); break;
+        default: colsum = cov_lower_rows<8, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_row, s_pvi); break;
+    }
+    if (PROBE) {
+        s_col[threadIdx.x >> 7][c] = colsum;
+        __syncthreads();
+        if (threadIdx.x < NB) {
+            const int r = threadIdx.x;
+            const int T = Np / NB;
+            double* slot = kv + (size_t)p * T * Np;
+            slot[(size_t)J * Np + I * NB + r] = (s_row[0][r] + s_row[1][r]) + (s_row[2][r] + s_row[3][r]);
+            if (I > J) slot[(size_t)I * Np + J * NB + r] = s_col[0][r] + s_col[1][r];
+        }
     }
 }
 
 int launch_cov_lower(const double* xs, const double* sq, const double* e, int P, int N, int Np, int d,
-                     double* mat, const unsigned char* active, cudaStream_t st) {
+                     double* mat, double* kv, const unsigned char* active, cudaStream_t st) {
     const int T = Np / NB;
     dim3 grid(T * (T + 1) / 2, P);
-    k_cov_lower<<<grid, 256, 0, st>>>(xs, sq, e, N, Np, d, mat, active);
+    if (kv) k_cov_lower<true><<<grid, 256, 0, st>>>(xs, sq, e, N, Np, d, mat, kv, active);
+    else k_cov_lower<false><<<grid, 256, 0, st>>>(xs, sq, e, N, Np, d, mat, kv, active);
     return check_launch("k_cov_lower");
 }
 

@@ -71,6 +71,10 @@ struct SmallSmem {
     static constexpr size_t total = hist + (size_t)(MAX_S + 1) * 4;
 };
 
+// FORM 0: reduced form (above).  FORM 1: the reference's own formulae (GP_func.py:36-40, find_len_scales.py:161-163):
+// mu = K_s^T alpha, v = L^-1 K_s, var = 1 - sum_rows v^2, pull = (mu - y) / max(sd s, 1e-12) -- the cancellations of the
+// reference are reproduced (K_s is rebuilt over the factor in shared memory, L^-1 is applied as the explicit inverse).
+template <int FORM>
 __global__ void __launch_bounds__(256, 1)
 k_small_loss(const double* __restrict__ X, const double* __restrict__ y, const double* __restrict__ e,
              const double* __restrict__ ls, const unsigned char* __restrict__ active,
@@ -145,23 +149,76 @@ k_small_loss(const double* __restrict__ X, const double* __restrict__ y, const d
         zv[k] = acc;
     }
     __syncthreads();
+    double cn = 0.0, al = 0.0;
     if (tid < N) {
         const int i = tid;
-        double cn = 0.0, al = 0.0;
         const double* row = Lm + i * CI_LD + 1;
         for (int k = i; k < N; ++k) {
             const double w = row[k];
             cn = fma(w, w, cn);
             al = fma(w, zv[k], al);
         }
-        double resid, sd;
-        resid_sigma(dv[i], al, cn, resid, sd);
-        av[i] = fabs(resid);
-        sg[i] = sd;
-        if (resid_out) resid_out[(size_t)p * N + i] = resid;
-        if (sig_out) sig_out[(size_t)p * N + i] = sd;
-        const int k0 = first_inside(av[i], sd, sigma_vals, S);
-        atomicAdd(&hist[k0], 1);
+    }
+    if constexpr (FORM == 0) {
+        if (tid < N) {
+            const int i = tid;
+            double resid, sd;
+            resid_sigma(dv[i], al, cn, resid, sd);
+            av[i] = fabs(resid);
+            sg[i] = sd;
+            if (resid_out) resid_out[(size_t)p * N + i] = resid;
+            if (sig_out) sig_out[(size_t)p * N + i] = sd;
+            const int k0 = first_inside(av[i], sd, sigma_vals, S);
+            atomicAdd(&hist[k0], 1);
+        }
+    } else {
+        // K_s = kernel_func(x, x) (GP_func.py:32, no noise term) over the L part of the staging array: lower triangle at
+        // Lm[r][c], c <= r; the inverse W[k][c] = Lm[c][k + 1] (c <= k) stays where it is
+        double* alv = col;                          // scratch of the factorisation, free now
+        double* muv = col + NB;
+        if (tid < N) alv[tid] = al;
+        {
+            const int R0 = (tid >> 4) * 8, C0 = (tid & 15) * 8;
+#pragma unroll
+            for (int rr = 0; rr < 8; ++rr)
+#pragma unroll
+                for (int cc = 0; cc < 8; ++cc) {
+                    const int r = R0 + rr, c = C0 + cc;
+                    if (c <= r && r < N) {
+                        double dot = __dmul_rn(xs[0][r], xs[0][c]);
+                        for (int dd = 1; dd < d; ++dd) dot = fma(xs[dd][r], xs[dd][c], dot);
+                        double sdist = __dsub_rn(__dadd_rn(sq[r], sq[c]), __dmul_rn(2.0, dot));
+                        sdist = fmax(sdist, 0.0);
+                        Lm[r * CI_LD + c] = exp(__dmul_rn(-0.5, sdist));
+                    }
+                }
+        }
+        __syncthreads();
+        if (tid >= NB && tid - NB < N) {            // mu_i = sum_c K_s[c][i] alpha_c                       GP_func.py:36
+            const int i = tid - NB;
+            double m = 0.0;
+            for (int c = 0; c < N; ++c) m = fma((c >= i) ? Lm[c * CI_LD + i] : Lm[i * CI_LD + c], alv[c], m);
+            muv[i] = m;
+        }
+        double ssq = 0.0;
+        if (tid < N) {                              // sum_k (sum_{c<=k} W[k][c] K_s[c][i])^2              GP_func.py:38-39
+            const int i = tid;
+            for (int k = 0; k < N; ++k) {
+                double vk = 0.0;
+                for (int c = 0; c <= k; ++c)
+                    vk = fma(Lm[c * CI_LD + k + 1], (c >= i) ? Lm[c * CI_LD + i] : Lm[i * CI_LD + c], vk);
+                ssq = __dadd_rn(ssq, __dmul_rn(vk, vk));
+            }
+        }
+        __syncthreads();
+        if (tid < N) {
+            const int i = tid;
+            const double resid = __dsub_rn(muv[i], yv[i]);
+            const double sd = sqrt(fmax(__dsub_rn(1.0, ssq), 1e-12));                     // GP_func.py:34,39-40
+            if (resid_out) resid_out[(size_t)p * N + i] = resid;
+            if (sig_out) sig_out[(size_t)p * N + i] = sd;
+            atomicAdd(&hist[first_inside(fabs(resid), sd, sigma_vals, S)], 1);
+        }
     }
     __syncthreads();
     prefix_and_store(hist, S, counts + (size_t)p * S);
@@ -169,23 +226,31 @@ k_small_loss(const double* __restrict__ X, const double* __restrict__ y, const d
 
 int launch_small_loss(const double* X, const double* y, const double* e, const double* ls,
                       const unsigned char* active, const double* sigma_vals, int P, int N, int d, int S,
-                      int* counts, int* info, double* resid_out, double* sig_out, cudaStream_t st) {
+                      int* counts, int* info, double* resid_out, double* sig_out, int form, cudaStream_t st) {
     static bool configured = false;
     if (!configured) {
-        cudaError_t er = cudaFuncSetAttribute(k_small_loss, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t er = cudaFuncSetAttribute(k_small_loss<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               (int)SmallSmem::total);
+        if (er == cudaSuccess)
+            er = cudaFuncSetAttribute(k_small_loss<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SmallSmem::total);
         if (er != cudaSuccess) { set_error("k_small_loss smem attr: %s", cudaGetErrorString(er)); return 1; }
         configured = true;
     }
-    k_small_loss<<<P, 256, SmallSmem::total, st>>>(X, y, e, ls, active, sigma_vals, N, d, S, counts, info,
-                                                   resid_out, sig_out);
-    return check_launch("k_small_loss");
+    if (form)
+        k_small_loss<1><<<P, 256, SmallSmem::total, st>>>(X, y, e, ls, active, sigma_vals, N, d, S, counts, info,
+                                                          resid_out, sig_out);
+    else
+        k_small_loss<0><<<P, 256, SmallSmem::total, st>>>(X, y, e, ls, active, sigma_vals, N, d, S, counts, info,
+                                                          resid_out, sig_out);
+    return check_launch(form ? "k_small_loss_ref_form" : "k_small_loss");
 }
 
 // ---------------------------------------------------------------------------------------------
 // z = W y : one warp per row, W lower block-triangular with zero upper parts in the diagonal blocks.
+// pu / pt (optional, per particle [Np]): the residual probe's second right-hand side, t = W u, in the same pass over W.
 __global__ void __launch_bounds__(256) k_wy(const double* __restrict__ mat, int Np, int N,
                                             const double* __restrict__ y, double* __restrict__ z,
+                                            const double* __restrict__ pu, double* __restrict__ pt,
                                             const unsigned char* __restrict__ active) {
     const int p = blockIdx.y;
     if (active && !active[p]) return;
@@ -195,36 +260,62 @@ __global__ void __launch_bounds__(256) k_wy(const double* __restrict__ mat, int 
     const double* row = mat + (size_t)p * Np * Np + (size_t)k * Np;
     const int cend = min(k, N - 1);
     double acc = 0.0;
-    for (int c = lane; c <= cend; c += 32) acc = fma(row[c], y[c], acc);
+    if (pu == nullptr) {
+        for (int c = lane; c <= cend; c += 32) acc = fma(row[c], y[c], acc);
+    } else {
+        const double* u = pu + (size_t)p * Np;
+        double acc2 = 0.0;
+        for (int c = lane; c <= cend; c += 32) {
+            const double w = row[c];
+            acc = fma(w, y[c], acc);
+            acc2 = fma(w, u[c], acc2);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc2 += __shfl_xor_sync(0xffffffffu, acc2, o);
+        if (lane == 0) pt[(size_t)p * Np + k] = acc2;
+    }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     if (lane == 0) z[(size_t)p * Np + k] = acc;
 }
 
-int launch_wy(const double* mat, int Np, int N, int P, const double* y, double* z, const unsigned char* active,
-              cudaStream_t st) {
-    k_wy<<<dim3(Np / 8, P), 256, 0, st>>>(mat, Np, N, y, z, active);
+int launch_wy(const double* mat, int Np, int N, int P, const double* y, double* z, const double* pu, double* pt,
+              const unsigned char* active, cudaStream_t st) {
+    k_wy<<<dim3(Np / 8, P), 256, 0, st>>>(mat, Np, N, y, z, pu, pt, active);
     return check_launch("k_wy");
 }
 
 // cn_i = sum_{k>=i} W[k][i]^2,  alpha_i = sum_{k>=i} W[k][i] z_k : 32 columns per CTA, 8 warps sweep rows.
+// pt / pw (optional, per particle [Np]): the residual probe, w = W^T t, in the same pass over W.
 __global__ void __launch_bounds__(256) k_colnorm_alpha(const double* __restrict__ mat, int Np,
                                                        const double* __restrict__ z, double* __restrict__ cn,
-                                                       double* __restrict__ alpha,
+                                                       double* __restrict__ alpha, const double* __restrict__ pt,
+                                                       double* __restrict__ pw,
                                                        const unsigned char* __restrict__ active) {
     const int p = blockIdx.y;
     if (active && !active[p]) return;
-    __shared__ double s_cn[8][32], s_al[8][32];
+    __shared__ double s_cn[8][32], s_al[8][32], s_pw[8][32];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int i = blockIdx.x * 32 + lane;
     const int kstart = (blockIdx.x * 32 / NB) * NB;       // first row of the diagonal block
     const double* M = mat + (size_t)p * Np * Np;
     const double* zp = z + (size_t)p * Np;
-    double a = 0.0, b = 0.0;
-    for (int k = kstart + warp; k < Np; k += 8) {
-        const double w = M[(size_t)k * Np + i];
-        a = fma(w, w, a);
-        b = fma(w, zp[k], b);
+    double a = 0.0, b = 0.0, c = 0.0;
+    if (pt == nullptr) {
+        for (int k = kstart + warp; k < Np; k += 8) {
+            const double w = M[(size_t)k * Np + i];
+            a = fma(w, w, a);
+            b = fma(w, zp[k], b);
+        }
+    } else {
+        const double* tp = pt + (size_t)p * Np;
+        for (int k = kstart + warp; k < Np; k += 8) {
+            const double w = M[(size_t)k * Np + i];
+            a = fma(w, w, a);
+            b = fma(w, zp[k], b);
+            c = fma(w, tp[k], c);
+        }
+        s_pw[warp][lane] = c;
     }
     s_cn[warp][lane] = a;
     s_al[warp][lane] = b;
@@ -235,27 +326,85 @@ __global__ void __launch_bounds__(256) k_colnorm_alpha(const double* __restrict_
         for (int w = 0; w < 8; ++w) { ta += s_cn[w][lane]; tb += s_al[w][lane]; }
         cn[(size_t)p * Np + i] = ta;
         alpha[(size_t)p * Np + i] = tb;
+        if (pt != nullptr) {
+            double tc = 0.0;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) tc += s_pw[w][lane];
+            pw[(size_t)p * Np + i] = tc;
+        }
     }
 }
 
 int launch_colnorm_alpha(const double* mat, int Np, int P, const double* z, double* cn, double* alpha,
-                         const unsigned char* active, cudaStream_t st) {
-    k_colnorm_alpha<<<dim3(Np / 32, P), 256, 0, st>>>(mat, Np, z, cn, alpha, active);
+                         const double* pt, double* pw, const unsigned char* active, cudaStream_t st) {
+    k_colnorm_alpha<<<dim3(Np / 32, P), 256, 0, st>>>(mat, Np, z, cn, alpha, pt, pw, active);
     return check_launch("k_colnorm_alpha");
 }
 
+// u[p][i] = sum_B kv[p][B][i]: the probe's K v from the per-tile partial sums k_cov_lower leaves (fixed order)
+__global__ void __launch_bounds__(256) k_probe_sum(const double* __restrict__ kv, int Np, int T, double* __restrict__ u,
+                                                   const unsigned char* __restrict__ active) {
+    const int p = blockIdx.y;
+    if (active && !active[p]) return;
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= Np) return;
+    const double* src = kv + (size_t)p * T * Np + i;
+    double s = 0.0;
+    for (int b = 0; b < T; ++b) s += src[(size_t)b * Np];
+    u[(size_t)p * Np + i] = s;
+}
+
+int launch_probe_sum(const double* kv, int Np, int T, int P, double* u, const unsigned char* active, cudaStream_t st) {
+    k_probe_sum<<<dim3((Np + 255) / 256, P), 256, 0, st>>>(kv, Np, T, u, active);
+    return check_launch("k_probe_sum");
+}
+
 // counts[p][s] from alpha / cn: one CTA per particle.
+// pw != nullptr: also the residual probe rho_p = max_i |w_i - v_i| / max_i |v_i| (w = W^T W K v for the fixed vector
+// probe_v) -> probe[p], and fail[p] = !(rho_p <= tol) (a NaN fails).  zero_inactive = 0: particles outside `active` are
+// left untouched (the FP64 fallback pass recomputes only the failed ones).
 __global__ void __launch_bounds__(256) k_counts(const double* __restrict__ alpha, const double* __restrict__ cn,
                                                 const double* __restrict__ e, const double* __restrict__ sigma_vals,
                                                 int N, int Np, int S, int* __restrict__ counts,
                                                 double* __restrict__ resid_out, double* __restrict__ sig_out,
+                                                const double* __restrict__ pw, double tol, double* __restrict__ probe,
+                                                unsigned char* __restrict__ fail, int zero_inactive,
                                                 const unsigned char* __restrict__ active) {
     __shared__ int hist[MAX_S + 1];
+    __shared__ double s_max[8][2];
     const int p = blockIdx.x;
     const int tid = threadIdx.x;
     if (active && !active[p]) {
-        for (int k = tid; k < S; k += 256) counts[(size_t)p * S + k] = 0;
+        if (zero_inactive) {
+            for (int k = tid; k < S; k += 256) counts[(size_t)p * S + k] = 0;
+            if (pw != nullptr && tid == 0) { probe[p] = 0.0; fail[p] = 0; }
+        }
         return;
+    }
+    if (pw != nullptr) {
+        double dmax = 0.0, vmax = 0.0;
+        bool nan = false;
+        for (int i = tid; i < N; i += 256) {
+            const double v = probe_v(i);
+            const double dlt = fabs(pw[(size_t)p * Np + i] - v);
+            nan |= !(dlt == dlt);
+            dmax = fmax(dmax, dlt);
+            vmax = fmax(vmax, fabs(v));
+        }
+        if (nan) dmax = __longlong_as_double(0x7ff0000000000000LL);        // +inf: fmax would drop a NaN
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            dmax = fmax(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
+            vmax = fmax(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+        }
+        if ((tid & 31) == 0) { s_max[tid >> 5][0] = dmax; s_max[tid >> 5][1] = vmax; }
+        __syncthreads();
+        if (tid == 0) {
+            for (int w = 1; w < 8; ++w) { dmax = fmax(dmax, s_max[w][0]); vmax = fmax(vmax, s_max[w][1]); }
+            const double rho = dmax / vmax;
+            probe[p] = rho;
+            fail[p] = (rho <= tol) ? 0 : 1;
+        }
     }
     for (int k = tid; k <= S; k += 256) hist[k] = 0;
     __syncthreads();
@@ -273,10 +422,60 @@ __global__ void __launch_bounds__(256) k_counts(const double* __restrict__ alpha
 }
 
 int launch_counts(const double* alpha, const double* cn, const double* e, const double* sigma_vals, int P, int N,
-                  int Np, int S, int* counts, double* resid_out, double* sig_out, const unsigned char* active,
-                  cudaStream_t st) {
-    k_counts<<<P, 256, 0, st>>>(alpha, cn, e, sigma_vals, N, Np, S, counts, resid_out, sig_out, active);
+                  int Np, int S, int* counts, double* resid_out, double* sig_out, const double* pw, double tol,
+                  double* probe, unsigned char* fail, int zero_inactive, const unsigned char* active, cudaStream_t st) {
+    k_counts<<<P, 256, 0, st>>>(alpha, cn, e, sigma_vals, N, Np, S, counts, resid_out, sig_out, pw, tol, probe, fail,
+                                zero_inactive, active);
     return check_launch("k_counts");
+}
+
+// rho_p of the residual probe for callers without a count stage (gpk_fit): one CTA per particle
+__global__ void __launch_bounds__(256) k_probe_value(const double* __restrict__ pw, int N, int Np, double* __restrict__ probe,
+                                                     unsigned char* __restrict__ fail, double tol,
+                                                     const unsigned char* __restrict__ active) {
+    __shared__ double s_max[8][2];
+    const int p = blockIdx.x, tid = threadIdx.x;
+    if (active && !active[p]) return;
+    double dmax = 0.0, vmax = 0.0;
+    bool nan = false;
+    for (int i = tid; i < N; i += 256) {
+        const double v = probe_v(i);
+        const double dlt = fabs(pw[(size_t)p * Np + i] - v);
+        nan |= !(dlt == dlt);
+        dmax = fmax(dmax, dlt);
+        vmax = fmax(vmax, fabs(v));
+    }
+    if (nan) dmax = __longlong_as_double(0x7ff0000000000000LL);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        dmax = fmax(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
+        vmax = fmax(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+    }
+    if ((tid & 31) == 0) { s_max[tid >> 5][0] = dmax; s_max[tid >> 5][1] = vmax; }
+    __syncthreads();
+    if (tid == 0) {
+        for (int w = 1; w < 8; ++w) { dmax = fmax(dmax, s_max[w][0]); vmax = fmax(vmax, s_max[w][1]); }
+        const double rho = dmax / vmax;
+        probe[p] = rho;
+        fail[p] = (rho <= tol) ? 0 : 1;
+    }
+}
+
+int launch_probe_value(const double* pw, int N, int Np, int P, double* probe, unsigned char* fail, double tol,
+                       const unsigned char* active, cudaStream_t st) {
+    k_probe_value<<<P, 256, 0, st>>>(pw, N, Np, probe, fail, tol, active);
+    return check_launch("k_probe_value");
+}
+
+// the FP64 fallback pass starts from a clean status for the particles it re-evaluates
+__global__ void k_clear_info(int* __restrict__ info, const unsigned char* __restrict__ mask, int P) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < P && mask[p]) info[p] = 0;
+}
+
+int launch_clear_info(int* info, const unsigned char* mask, int P, cudaStream_t st) {
+    k_clear_info<<<(P + 255) / 256, 256, 0, st>>>(info, mask, P);
+    return check_launch("k_clear_info");
 }
 
 // sigma_b = sqrt(clip(1 - sum_I partial[I][b], 1e-12))     GP_func.py:34,39-40

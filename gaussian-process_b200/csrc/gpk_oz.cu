@@ -222,11 +222,13 @@ constexpr int OZ_QDEPTH = 4;
 template <int EPI, int NG, int TN, class F>
 __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uint8_t* smem) {
     static_assert(TN == 64 || TN == 32, "tile width");
+    static_assert(NG >= 5 && NG <= 8, "digit groups kept");
     static_assert(EPI != OZ_SUMSQ || TN == 64, "the sum-of-squares epilogue is written for 64-column tiles");
     constexpr uint32_t NSETS = (TN == 32) ? 2u : 1u;        // accumulator sets in TMEM
     constexpr uint32_t SET_COLS = NG * TN;
     constexpr uint32_t B_DIGIT = TN * 32;                   // bytes of one B digit of a stage (TN rows x 32 k)
-    constexpr uint32_t STAGE_TX = OZ_CHUNK + OZ_NS * B_DIGIT;
+    constexpr int ND = (NG < OZ_NS) ? NG : OZ_NS;           // leading digits of each operand that meet a partner (s + t < NG)
+    constexpr uint32_t STAGE_TX = ND * OZ_DIGIT + ND * B_DIGIT;
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
     uint8_t* ctrl = smem + (size_t)OZ_STAGES * OZ_STAGE;
@@ -292,9 +294,9 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
                 mbar_wait(empty0 + 8 * s, ph ^ 1u);
                 mbar_expect_tx(full0 + 8 * s, STAGE_TX);
                 const uint32_t dst = stage0 + s * OZ_STAGE;
-                bulk_g2s(dst, t.a + (size_t)k * OZ_CHUNK, OZ_CHUNK, full0 + 8 * s);
+                bulk_g2s(dst, t.a + (size_t)k * OZ_CHUNK, ND * OZ_DIGIT, full0 + 8 * s);      // digit-major record: a prefix
 #pragma unroll
-                for (int d = 0; d < OZ_NS; ++d)       // TN rows of every B digit, stored back to back
+                for (int d = 0; d < ND; ++d)          // TN rows of every B digit, stored back to back
                     bulk_g2s(dst + OZ_CHUNK + d * B_DIGIT, t.b + (size_t)k * OZ_CHUNK + d * OZ_DIGIT, B_DIGIT,
                              full0 + 8 * s);
             }
@@ -408,9 +410,16 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
                 // directly inside the bit pattern of a double (oz_acc3 / oz_acc2) and finished by one FP64 subtraction:
                 // this phase is issue bound (8 warps on 4 schedulers hold TMEM while they convert)
                 const double hi = oz_acc3(a[0][j], a[1][j], a[2][j], magic_hi);
-                const double mid = oz_acc3(a[3][j], a[4][j], a[5][j], magic_hi);
-                const double lo = (NG == 8) ? oz_acc2(a[6][j], a[NG - 1][j], magic_hi) : oz_acc2(a[6][j], 0u, magic_hi);
-                const double x = fma(hi, 0x1p40, fma(mid, 0x1p16, lo));      // units of 2^-56 (rs carries the factor)
+                double x;                                                     // units of 2^-56 (rs carries the factor)
+                if constexpr (NG >= 7) {
+                    const double mid = oz_acc3(a[3][j], a[4][j], a[5][j], magic_hi);
+                    const double lo = (NG == 8) ? oz_acc2(a[6][j], a[NG - 1][j], magic_hi) : oz_acc2(a[6][j], 0u, magic_hi);
+                    x = fma(hi, 0x1p40, fma(mid, 0x1p16, lo));
+                } else if constexpr (NG == 6) {
+                    x = fma(hi, 0x1p40, oz_acc3(a[3][j], a[4][j], a[5][j], magic_hi) * 0x1p16);
+                } else {
+                    x = fma(hi, 0x1p40, oz_acc2(a[3][j], a[4][j], magic_hi) * 0x1p24);
+                }
                 const double v = x * (rs * (sbp ? sbp[cc + j] : 1.0));
                 if (EPI == OZ_SUB) val[cc + j] -= v;
                 else if (EPI == OZ_STORE) val[cc + j] = v;
@@ -444,7 +453,7 @@ __device__ __forceinline__ void oz_run(const F& f, int ntiles, int* counter, uin
                     }
                     uint8_t* d = drow + (cc >> 4) * 128;
 #pragma unroll
-                    for (int s = 0; s < OZ_NS; ++s) {
+                    for (int s = 0; s < ND; ++s) {
                         const int bytepos = 6 - s;
                         const uint32_t* w = (bytepos >= 4) ? hi : lo;
                         uint4 o4;
@@ -992,24 +1001,17 @@ int launch_oz_prep(const double* e, int N, int Np, double* rowsig, double* rowin
     return check_launch("k_oz_prep");
 }
 
-static int g_oz_groups = 8;     // digit groups kept: 8 -> 34 digit products (default), 7 -> 28
-void oz_set_groups(int ng) { g_oz_groups = (ng == 7) ? 7 : 8; }
+// digit groups kept (g = s + t < NG): 8 -> 34 digit products (default), 7 -> 28, 6 -> 21 (6 digits), 5 -> 15 (5 digits).
+// Per calling thread: every C-ABI entry sets it from its own `precision` argument before launching.
+static thread_local int g_oz_groups = 8;
+void oz_set_groups(int ng) { g_oz_groups = (ng >= 5 && ng <= 8) ? ng : 8; }
 int oz_get_groups() { return g_oz_groups; }
 
-// Tile width of the 4-chunk panel contractions (TRSM, phase-2 panel).  64 (default): one accumulator set fills TMEM, MMA and
-// epilogue of a CTA alternate.  GPK_OZ_PANEL_TN=32: two accumulator sets, the epilogue of one tile overlaps the MMAs of the
-// next.  Measured (profiles/r01_ab_panel_tn.log): the hand-off wait drops from 4000 to 900 cycles per tile, but a 32-column
-// tile costs 5700 cycles against 10 000 for a 64-column one (MMAs of N <= 128 are bound by the A operand reads, and the
-// per-tile queue / operand latencies double): 195.9 vs 192.5 ms per step, so 64 stays.  The results do not depend on it
-// (exact integer accumulation, element-wise epilogue): the loss checksum is identical.
-static int oz_panel_tn() {
-    static int v = 0;
-    if (v == 0) {
-        const char* e = getenv("GPK_OZ_PANEL_TN");
-        v = (e && atoi(e) == 32) ? 32 : 64;
-    }
-    return v;
-}
+// Tile width of the 4-chunk panel contractions (TRSM, phase-2 panel): 64, one accumulator set fills TMEM, MMA and epilogue of
+// a CTA alternate.  A 32-column variant with two accumulator sets (k_oz<.., TN = 32>) was measured in round 1
+// (profiles/r01_ab_panel_tn.log): the hand-off wait drops from 4000 to 900 cycles per tile, but a 32-column tile costs 5700
+// cycles against 10 000 for a 64-column one (MMAs of N <= 128 are bound by the A operand reads): 195.9 vs 192.5 ms per step,
+// so it is not instantiated.
 
 static int oz_grid(int ntiles) {
     static int sms = 0;
@@ -1026,15 +1028,20 @@ static int oz_grid(int ntiles) {
 // launches k_oz<EPI, 7 or 8, TN, F> on one persistent CTA per SM (one smem-attribute call per instantiation)
 template <int EPI, int TN = OZ_TILE_N, class F>
 static int oz_launch(const F& f, int ntiles, int* counter, cudaStream_t st) {
-    static bool done7 = false, done8 = false;
+    static bool done[4] = {false, false, false, false};
     if (ntiles <= 0) return 0;
-    if (g_oz_groups == 7) {
-        if (oz_smem_attr(k_oz<EPI, 7, TN, F>, done7)) return 1;
-        k_oz<EPI, 7, TN, F><<<oz_grid(ntiles), OZ_THREADS, OZ_SMEM_BYTES, st>>>(f, ntiles, counter);
-    } else {
-        if (oz_smem_attr(k_oz<EPI, 8, TN, F>, done8)) return 1;
-        k_oz<EPI, 8, TN, F><<<oz_grid(ntiles), OZ_THREADS, OZ_SMEM_BYTES, st>>>(f, ntiles, counter);
+#define GPK_OZ_GO(NG_)                                                                                   \
+    do {                                                                                                  \
+        if (oz_smem_attr(k_oz<EPI, NG_, TN, F>, done[NG_ - 5])) return 1;                                 \
+        k_oz<EPI, NG_, TN, F><<<oz_grid(ntiles), OZ_THREADS, OZ_SMEM_BYTES, st>>>(f, ntiles, counter);    \
+    } while (0)
+    switch (g_oz_groups) {
+        case 5: GPK_OZ_GO(5); break;
+        case 6: GPK_OZ_GO(6); break;
+        case 7: GPK_OZ_GO(7); break;
+        default: GPK_OZ_GO(8); break;
     }
+#undef GPK_OZ_GO
     return 0;
 }
 
@@ -1060,15 +1067,9 @@ int launch_oz_trsm(double* mat, int Np, int T, int J, int P, const uint8_t* sdig
                    const double* rowsig, const double* rowinv, uint8_t* slices, int* counter, const unsigned char* active,
                    cudaStream_t st) {
     if (J >= T - 1) return 0;
-    if (oz_panel_tn() == 32) {
-        const OzTrsmTiles<32> f{mat, Np, T, J, 4 * (T - 1 - J), sdig, oz_panel_bytes(Np), ddig, dsc, rowsig, rowinv, slices,
-                                oz_slice_bytes(Np), active};
-        if (oz_launch<OZ_STORE, 32>(f, f.nx * P, counter, st)) return 1;
-    } else {
-        const OzTrsmTiles<64> f{mat, Np, T, J, 2 * (T - 1 - J), sdig, oz_panel_bytes(Np), ddig, dsc, rowsig, rowinv, slices,
-                                oz_slice_bytes(Np), active};
-        if (oz_launch<OZ_STORE, 64>(f, f.nx * P, counter, st)) return 1;
-    }
+    const OzTrsmTiles<64> f{mat, Np, T, J, 2 * (T - 1 - J), sdig, oz_panel_bytes(Np), ddig, dsc, rowsig, rowinv, slices,
+                            oz_slice_bytes(Np), active};
+    if (oz_launch<OZ_STORE, 64>(f, f.nx * P, counter, st)) return 1;
     return check_launch("k_oz_trsm");
 }
 
@@ -1076,13 +1077,8 @@ int launch_oz_invp(double* mt, int Np, int T, int J, int P, const uint8_t* ddig,
                    const double* rowsig, unsigned long long* mtmax, const double* gaminv, int* counter,
                    const unsigned char* active, cudaStream_t st) {
     if (J >= T - 1) return 0;
-    if (oz_panel_tn() == 32) {
-        const OzInvpTiles<32> f{mt, Np, T, J, 4 * (T - 1 - J), ddig, dsc, slices, oz_slice_bytes(Np), rowsig, mtmax, gaminv, active};
-        if (oz_launch<OZ_STORE, 32>(f, f.nx * P, counter, st)) return 1;
-    } else {
-        const OzInvpTiles<64> f{mt, Np, T, J, 2 * (T - 1 - J), ddig, dsc, slices, oz_slice_bytes(Np), rowsig, mtmax, gaminv, active};
-        if (oz_launch<OZ_STORE, 64>(f, f.nx * P, counter, st)) return 1;
-    }
+    const OzInvpTiles<64> f{mt, Np, T, J, 2 * (T - 1 - J), ddig, dsc, slices, oz_slice_bytes(Np), rowsig, mtmax, gaminv, active};
+    if (oz_launch<OZ_STORE, 64>(f, f.nx * P, counter, st)) return 1;
     return check_launch("k_oz_invp");
 }
 

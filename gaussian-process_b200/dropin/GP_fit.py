@@ -13,6 +13,7 @@ GP_fit.py:20-164), SURVEY 8f row N1.  What changes underneath:
 import _bootstrap  # noqa: F401
 from pathlib import Path
 
+import numpy as np
 import pandas as pd
 
 from find_len_scales import len_scale_opt
@@ -119,11 +120,27 @@ def create_GP():
 
     by_experiment = size > 1 and len(jobs) >= size
     if by_experiment:
+        # a failing experiment (LinAlgError from GP_func.py:22, a library error) must not leave the other ranks waiting in
+        # the gather: the error travels with the results and is raised on every rank, as the reference aborts the run
+        mine, failure = {}, None
         with sharding.local_swarm():
-            mine = {j: run(jobs[j]) for j in range(rank, len(jobs), size)}
+            for j in range(rank, len(jobs), size):
+                try:
+                    mine[j] = run(jobs[j])
+                except Exception as ex:              # noqa: BLE001 -- re-raised below, on every rank
+                    failure = (j, type(ex).__name__, str(ex), ex if isinstance(ex, np.linalg.LinAlgError) else None)
+                    break
         results = {}
-        for part in sharding.gather_objects(mine):
+        first = None
+        for part, fail in sharding.gather_objects((mine, failure)):
             results.update(part)
+            if fail is not None and (first is None or fail[0] < first[0]):
+                first = fail
+        if first is not None:
+            j, kind, text, ex = first
+            if kind == "LinAlgError":
+                raise np.linalg.LinAlgError(text)
+            raise RuntimeError(f"experiment job {j} failed with {kind}: {text}")
         dfs = [results[j] for j in range(len(jobs))]
     else:
         dfs = None                    # fitted inside the loop below, so that stdout reads exactly like the reference's

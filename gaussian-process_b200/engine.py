@@ -15,6 +15,8 @@ import torch
 from . import _lib
 
 NB = 128
+MAX_D = 8                     # include/gpk.h GPK_MAX_D
+MAX_S = 4096                  # include/gpk.h GPK_MAX_S
 DEFAULT_CHUNK = 8192          # grid points per predict pass (2048 measured 17 % slower than 4096: too few CTAs per launch)
 
 
@@ -50,29 +52,63 @@ def to_dev(a, dtype=None):
     return t.to(device(), non_blocking=False)
 
 
-# Arithmetic of the two dense contractions of the blocked path (N > 128), include/gpk.h gpk_set_precision:
+# Arithmetic of the two dense contractions of the blocked path (N > 128), include/gpk.h GPK_PREC_*.  It is a per-call argument
+# of the C ABI (the library keeps no precision state); what lives here is the caller's *policy*:
 #   "fp64"   native FP64 tensor instructions (DMMA)
 #   "emu"    FP64 emulated on the int8 tcgen05 tensor cores (7-digit Ozaki split, 34 digit products): same rounding
 #            level as an FP64 dot product, 1.7x the loss-evaluation throughput at N = 4096; needs e > 0
 #   "emu28"  28 digit products (~2^8 larger truncation error)
+#   "emu21"  6 digits, 21 products;  "emu15"  5 digits, 15 products -- for use under the a-posteriori check below
 #   "auto"   "emu" when every e_i is finite and > 0 and N >= 1024 (below that the native kernels are faster:
 #            profiles/r01_mode_crossover.log), else "fp64"                        (default; env GPK_PRECISION)
-_MODES = {"fp64": 0, "emu": 1, "emu28": 2}
+_MODES = {"fp64": 0, "emu": 1, "emu28": 2, "emu21": 3, "emu15": 4}
+MODE_NAMES = {v: k for k, v in _MODES.items()}
 EMU_MIN_N = 1024
 EMU_MAX_N = 16256             # contraction length below 2^14: the int32 sums of 8 digit products of 2^14 each cannot overflow
 _precision_pref = os.environ.get("GPK_PRECISION", "auto")
 
+# Checked mixed precision: every emulated factorisation is probed a posteriori, rho = |W^T W K v - v|_inf / |v|_inf for one
+# fixed pseudo-random v (include/gpk.h).  rho estimates the relative error the computed inverse puts on alpha = K^-1 y, i.e. on
+# mu - y; a particle (or fit) whose rho exceeds the tolerance is evaluated again by the native FP64 kernels in the same call.
+# 1e-10 leaves a factor 10 to the 1e-9 parity bar.  0 switches the check off.                      (env GPK_CHECK_TOL)
+_check_tol = float(os.environ.get("GPK_CHECK_TOL", "1e-10"))
+
+# Which algebraic form the loss of the one-CTA path (N <= 128) uses: "reduced" (mu - y = -e^2 alpha, var from diag K^-1) or
+# "reference" (GP_func.py:36-40 as written: K_s^T alpha - y, 1 - sum v^2).                         (env GPK_LOSS_FORM)
+_FORMS = {"reduced": 0, "reference": 1}
+_loss_form = os.environ.get("GPK_LOSS_FORM", "reduced")
+
 
 def set_precision(mode):
     global _precision_pref
-    mode = {0: "fp64", 1: "emu", 2: "emu28"}.get(mode, mode)
+    mode = MODE_NAMES.get(mode, mode)
     if mode != "auto" and mode not in _MODES:
-        raise ValueError(f"precision must be one of auto, fp64, emu, emu28 (got {mode!r})")
+        raise ValueError(f"precision must be one of auto, {', '.join(_MODES)} (got {mode!r})")
     _precision_pref = mode
 
 
 def get_precision():
     return _precision_pref
+
+
+def set_check_tol(tol):
+    global _check_tol
+    _check_tol = float(tol)
+
+
+def get_check_tol():
+    return _check_tol
+
+
+def set_loss_form(form):
+    global _loss_form
+    if form not in _FORMS:
+        raise ValueError(f"loss form must be one of {', '.join(_FORMS)} (got {form!r})")
+    _loss_form = form
+
+
+def get_loss_form():
+    return _loss_form
 
 
 def _resolve_precision(e_host, n=None):
@@ -81,15 +117,13 @@ def _resolve_precision(e_host, n=None):
     ok = bool(np.all(np.isfinite(e_host)) and np.all(np.abs(e_host) > 1e-150)) if e_host.size else False
     if pref == "auto":
         return 1 if ok and (n is None or EMU_MIN_N <= n <= EMU_MAX_N) else 0
+    if pref not in _MODES:
+        raise ValueError(f"GPK_PRECISION={pref!r}: expected auto, {', '.join(_MODES)}")
     if pref != "fp64" and not ok:
         raise ValueError("emulated-FP64 mode needs finite, non-zero e_known (use GPK_PRECISION=fp64)")
     if pref != "fp64" and n is not None and n > EMU_MAX_N:
         raise ValueError(f"emulated-FP64 mode supports N <= {EMU_MAX_N} (exact int32 accumulation); use GPK_PRECISION=fp64")
     return _MODES[pref]
-
-
-def _apply_precision(mode):
-    _lib.check(_lib.load().gpk_set_precision(int(mode)), "gpk_set_precision")
 
 
 # CUDA-graph replay of the blocked loss evaluation where launch latency shows (128 < N <= 2048); GPK_GRAPH=0 disables
@@ -213,13 +247,30 @@ def selfpredict_counts(L, alpha, y, e, sigma_vals, active=None):
 # ------------------------------------------------------------------------------------ (b)
 class LossContext:
     """Device-resident training set + sigma grid for repeated swarm evaluations (one per PSO
-    iteration).  Only the (P,d) positions go up and the (P,S) int32 counts come down per call."""
+    iteration).  Only the (P,d) positions go up and the (P,S) int32 counts come down per call.
+
+    After every evaluation `last_fallback` ((P,) uint8 device tensor) marks the particles the a-posteriori check sent to the
+    native FP64 kernels and `last_probe` ((P,) float64 device tensor) holds their probe values; `fallbacks` counts them over
+    the life of the context when the host-returning calls (counts / counts_view) are used."""
 
     def __init__(self, x, y, e, sigma_vals, max_particles=None, mem_fraction=0.85):
         self.lib = _lib.load()
         x, y, e, sigma_vals = _f64(x), _f64(y), _f64(e), _f64(sigma_vals)
         self.d, self.n = x.shape
+        if self.d > MAX_D:
+            raise ValueError(f"x_known has {self.d} dimensions; the kernels support at most {MAX_D} (include/gpk.h GPK_MAX_D)")
         self.s = sigma_vals.shape[0]
+        if self.s > MAX_S:
+            raise ValueError(f"{self.s} sigma scales; the count kernels support at most {MAX_S} (include/gpk.h GPK_MAX_S)")
+        # the count is found by bisection over an ascending grid (the predicate is monotone in s); the reference compares
+        # element-wise and accepts any order (find_len_scales.py:161-163): other grids are sorted here, un-permuted on return
+        self._sig_unsort = None
+        if self.s > 1 and np.any(np.diff(sigma_vals) < 0):
+            order = np.argsort(sigma_vals, kind="stable")
+            sigma_vals = np.ascontiguousarray(sigma_vals[order])
+            unsort = np.empty_like(order)
+            unsort[order] = np.arange(self.s)
+            self._sig_unsort = to_dev(unsort.astype(np.int64))
         self.x, self.y, self.e, self.sig = to_dev(x), to_dev(y), to_dev(e), to_dev(sigma_vals)
         self.mem_fraction = mem_fraction
         self._e_ok = e
@@ -228,68 +279,81 @@ class LossContext:
         self._pin_counts = None
         self._mode_key = None
         self._graphs = {}
+        self.fallbacks = 0
+        self.evaluated = 0
+        self.last_fallback = None
+        self.last_probe = None
 
     def _ws(self, p):
         if self._mode_key != _precision_pref:                 # the e-scan is O(N): once per policy, not per call
             self.mode = _resolve_precision(self._e_ok, self.n)
             self._mode_key = _precision_pref
-        _apply_precision(self.mode)                            # process-wide switch: other contexts may have moved it
-        need = self.lib.gpk_loss_workspace_bytes(p, self.n, self.d)     # sized for the mode just applied
+        need = self.lib.gpk_loss_workspace_bytes(p, self.n, self.d, self.mode)
         have = _ws_cache.get((torch.cuda.current_device(), "loss"))
         if have is not None and have.numel() >= need:
             return have
-        one = self.lib.gpk_loss_workspace_bytes(1, self.n, self.d)
+        one = self.lib.gpk_loss_workspace_bytes(1, self.n, self.d, self.mode)
         budget = int((free_bytes() + (have.numel() if have is not None else 0)) * self.mem_fraction)
         if need > budget:                      # libgpk runs the swarm in waves inside this much memory
             need = max(one, budget // one * one)
         return workspace(need, "loss")
 
-    def _launch(self, positions_dev, active_dev, p, counts, info, resid, sd, ws, stream=None):
+    def _form(self):
+        return _FORMS[_loss_form] if self.n <= NB else 0
+
+    def _launch(self, positions_dev, active_dev, p, counts, info, resid, sd, probe, fallback, ws, stream=None):
         st = self.lib.gpk_loss_batched(
             self.x.data_ptr(), self.y.data_ptr(), self.e.data_ptr(), positions_dev.data_ptr(),
             active_dev.data_ptr() if active_dev is not None else None, self.sig.data_ptr(), p, self.n, self.d,
-            self.s, counts.data_ptr(), info.data_ptr(), resid.data_ptr() if resid is not None else None,
-            sd.data_ptr() if sd is not None else None, ws.data_ptr(), ws.numel(),
+            self.s, self.mode, self._form(), _check_tol if self.mode != 0 else 0.0,
+            counts.data_ptr(), info.data_ptr(), resid.data_ptr() if resid is not None else None,
+            sd.data_ptr() if sd is not None else None, probe.data_ptr() if probe is not None else None,
+            fallback.data_ptr(), ws.data_ptr(), ws.numel(),
             stream if stream is not None else _stream())
         _lib.check(st, "gpk_loss_batched")
 
-    def counts_device(self, positions_dev, active_dev, p, want_detail=False, stream=None):
+    def counts_device(self, positions_dev, active_dev, p, want_detail=False, stream=None, want_probe=False):
         """All inputs already on the device; returns device tensors (counts, info[, resid, sd]).  In the launch-bound
         range of the blocked path the evaluation is replayed from a CUDA graph; the tensors returned then belong to the
         context and are overwritten by its next evaluation."""
         dev = device()
         ws = self._ws(p)
-        if not want_detail and GRAPH_MIN_N < self.n <= GRAPH_MAX_N and _graphs_enabled():
+        if not want_detail and not want_probe and self._sig_unsort is None and GRAPH_MIN_N < self.n <= GRAPH_MAX_N and _graphs_enabled():
             return self._counts_graphed(positions_dev, active_dev, p, ws)
         counts = torch.empty((p, self.s), dtype=torch.int32, device=dev)
         info = torch.empty(p, dtype=torch.int32, device=dev)
         resid = torch.empty((p, self.n), dtype=torch.float64, device=dev) if want_detail else None
         sd = torch.empty((p, self.n), dtype=torch.float64, device=dev) if want_detail else None
-        self._launch(positions_dev, active_dev, p, counts, info, resid, sd, ws, stream)
+        self.last_fallback = torch.empty(p, dtype=torch.uint8, device=dev)
+        self.last_probe = torch.empty(p, dtype=torch.float64, device=dev) if want_probe else None
+        self._launch(positions_dev, active_dev, p, counts, info, resid, sd, self.last_probe, self.last_fallback, ws, stream)
+        if self._sig_unsort is not None:
+            counts = counts.index_select(1, self._sig_unsort)
         return (counts, info, resid, sd) if want_detail else (counts, info)
 
     def _counts_graphed(self, positions_dev, active_dev, p, ws):
         """One swarm evaluation of the blocked path is ~16 launches per block column on up to four streams; for
-        N <= 2048 their launch latency is a visible share of the step.  Captured once per (swarm size, mode,
-        workspace) into a CUDA graph with static input / output tensors, replayed afterwards."""
-        key = (p, self.mode, ws.data_ptr(), ws.numel())
+        N <= 2048 their launch latency is a visible share of the step.  Captured once per (swarm size, mode, check
+        tolerance, workspace) into a CUDA graph with static input / output tensors, replayed afterwards."""
+        key = (p, self.mode, _check_tol, ws.data_ptr(), ws.numel())
         g = self._graphs.get(key)
         if g is None:
             dev = device()
             st = {"pos": torch.empty((p, self.d), dtype=torch.float64, device=dev),
                   "act": torch.ones(p, dtype=torch.uint8, device=dev),
                   "counts": torch.empty((p, self.s), dtype=torch.int32, device=dev),
-                  "info": torch.empty(p, dtype=torch.int32, device=dev)}
+                  "info": torch.empty(p, dtype=torch.int32, device=dev),
+                  "fb": torch.zeros(p, dtype=torch.uint8, device=dev)}
             st["pos"].copy_(positions_dev)
             cur = torch.cuda.current_stream()
             side = torch.cuda.Stream(device=dev)
             side.wait_stream(cur)
             with torch.cuda.stream(side):                  # warm-up outside the capture (attribute calls, streams)
-                self._launch(st["pos"], st["act"], p, st["counts"], st["info"], None, None, ws)
+                self._launch(st["pos"], st["act"], p, st["counts"], st["info"], None, None, None, st["fb"], ws)
             cur.wait_stream(side)
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
-                self._launch(st["pos"], st["act"], p, st["counts"], st["info"], None, None, ws)
+                self._launch(st["pos"], st["act"], p, st["counts"], st["info"], None, None, None, st["fb"], ws)
             self._graphs.clear()                           # one live graph per context (its workspace is shared)
             g = self._graphs[key] = (graph, st)
         graph, st = g
@@ -299,23 +363,27 @@ class LossContext:
         else:
             st["act"].fill_(1)
         graph.replay()
+        self.last_fallback = st["fb"]
+        self.last_probe = None
         return st["counts"], st["info"]
 
-    def counts(self, positions, active=None, want_detail=False):
-        """positions (P,d) host -> counts (P,S) int32 host (+ info, optional resid/sd)."""
-        c, i, extra = self._counts_pinned(positions, active, want_detail)
+    def counts(self, positions, active=None, want_detail=False, want_probe=False):
+        """positions (P,d) host -> counts (P,S) int32 host (+ info, optional resid/sd[, probe])."""
+        c, i, extra = self._counts_pinned(positions, active, want_detail, want_probe)
         res = [c.copy(), i.copy()]
         if want_detail:
             res += [extra[0].cpu().numpy(), extra[1].cpu().numpy()]
+        if want_probe:
+            res.append(self.last_probe.cpu().numpy())
         return tuple(res)
 
     def counts_view(self, positions, active=None):
         """As counts(), but the arrays returned are views of the context's page-locked staging buffers: valid until
         its next evaluation.  The PSO loop finishes the scores from them at once (one 160 KB copy less per iteration)."""
-        c, i, _ = self._counts_pinned(positions, active, False)
+        c, i, _ = self._counts_pinned(positions, active, False, False)
         return c, i
 
-    def _counts_pinned(self, positions, active, want_detail):
+    def _counts_pinned(self, positions, active, want_detail, want_probe):
         positions = np.atleast_2d(_f64(positions))
         p = positions.shape[0]
         dev = device()
@@ -324,8 +392,10 @@ class LossContext:
             self._pin_act = torch.empty(p, dtype=torch.uint8).pin_memory()
             self._pin_counts = torch.empty((p, self.s), dtype=torch.int32).pin_memory()
             self._pin_info = torch.empty(p, dtype=torch.int32).pin_memory()
+            self._pin_fb = torch.empty(p, dtype=torch.uint8).pin_memory()
             self._np_pos, self._np_act = self._pin_pos.numpy(), self._pin_act.numpy()
             self._np_counts, self._np_info = self._pin_counts.numpy(), self._pin_info.numpy()
+            self._np_fb = self._pin_fb.numpy()
             self._dev_pos = torch.empty((p, self.d), dtype=torch.float64, device=dev)
             self._dev_act = torch.empty(p, dtype=torch.uint8, device=dev)
         stream = torch.cuda.current_stream(dev.index)
@@ -333,10 +403,13 @@ class LossContext:
         self._np_act[...] = 1 if active is None else np.asarray(active, dtype=np.uint8)
         self._dev_pos.copy_(self._pin_pos, non_blocking=True)
         self._dev_act.copy_(self._pin_act, non_blocking=True)
-        out = self.counts_device(self._dev_pos, self._dev_act, p, want_detail, stream.cuda_stream)
+        out = self.counts_device(self._dev_pos, self._dev_act, p, want_detail, stream.cuda_stream, want_probe)
         self._pin_counts.copy_(out[0], non_blocking=True)
         self._pin_info.copy_(out[1], non_blocking=True)
+        self._pin_fb.copy_(self.last_fallback, non_blocking=True)
         stream.synchronize()
+        self.evaluated += int(self._np_act.sum())
+        self.fallbacks += int(self._np_fb.sum())
         return self._np_counts, self._np_info, (out[2:] if want_detail else None)
 
 
@@ -358,15 +431,29 @@ class GPFit:
         self.alpha = torch.empty(self.np_, dtype=torch.float64, device=dev)
         self.xs = torch.empty((self.d, self.np_), dtype=torch.float64, device=dev)
         self.sq = torch.empty(self.np_, dtype=torch.float64, device=dev)
+        if self.d > MAX_D:
+            raise ValueError(f"x_known has {self.d} dimensions; the kernels support at most {MAX_D} (include/gpk.h GPK_MAX_D)")
+        status = torch.zeros(2, dtype=torch.float64, device=dev)           # [probe, info] -> one device-to-host read
         info = torch.zeros(1, dtype=torch.int32, device=dev)
         self.mode = _resolve_precision(e, self.n)
-        _apply_precision(self.mode)
-        ws = workspace(lib.gpk_fit_workspace_bytes(self.n, self.d), "fit")
-        st = lib.gpk_fit(dx.data_ptr(), dy.data_ptr(), de.data_ptr(), self.ls.data_ptr(), self.n, self.d,
-                         self.W.data_ptr(), self.alpha.data_ptr(), self.xs.data_ptr(), self.sq.data_ptr(),
-                         info.data_ptr(), ws.data_ptr(), ws.numel(), _stream())
-        _lib.check(st, "gpk_fit")
-        if int(info.item()) != 0:
+        self.fell_back = False
+
+        def run(mode):
+            ws = workspace(lib.gpk_fit_workspace_bytes(self.n, self.d, mode), "fit")
+            st = lib.gpk_fit(dx.data_ptr(), dy.data_ptr(), de.data_ptr(), self.ls.data_ptr(), self.n, self.d, mode,
+                             self.W.data_ptr(), self.alpha.data_ptr(), self.xs.data_ptr(), self.sq.data_ptr(),
+                             info.data_ptr(), status.data_ptr(), ws.data_ptr(), ws.numel(), _stream())
+            _lib.check(st, "gpk_fit")
+            status[1:2].copy_(info)
+            rho, bad = status.tolist()
+            return rho, int(bad)
+
+        self.probe, bad = run(self.mode)
+        if self.mode != 0 and _check_tol > 0 and not (self.probe <= _check_tol):
+            # checked mixed precision: the emulated factor failed its a-posteriori residual probe -> native FP64 (DMMA)
+            self.mode, self.fell_back = 0, True
+            self.probe, bad = run(0)
+        if bad != 0:
             # numpy.linalg.cholesky's behaviour at GP_func.py:22
             raise np.linalg.LinAlgError("Matrix is not positive definite")
         self.state = None
@@ -382,11 +469,10 @@ class GPFit:
         mu = torch.empty(m, dtype=torch.float64, device=dev)
         sd = torch.empty(m, dtype=torch.float64, device=dev)
         chunk = int(max(NB, min(chunk, -(-m // NB) * NB)))
-        _apply_precision(self.mode)                 # process-wide switch: predict in the mode this fit was made in
         if self.state is not None:
             ws = workspace(self.lib.gpk_predict_emu_workspace_bytes(self.n, chunk), "predict")
             st = self.lib.gpk_predict_emu(self.state.data_ptr(), self.alpha.data_ptr(), self.xs.data_ptr(),
-                                          self.sq.data_ptr(), self.ls.data_ptr(), self.n, self.d, xfit_dev.data_ptr(), m,
+                                          self.sq.data_ptr(), self.ls.data_ptr(), self.n, self.d, self.mode, xfit_dev.data_ptr(), m,
                                           mu.data_ptr(), sd.data_ptr(), chunk, ws.data_ptr(), ws.numel(), _stream())
             _lib.check(st, "gpk_predict_emu")
             return mu, sd

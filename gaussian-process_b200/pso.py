@@ -158,8 +158,17 @@ def len_scale_opt(x_known, y_known, e_known, PSO_progress, *, num_particles=40, 
                   distributed=None):
     """Drop-in for find_len_scales.len_scale_opt (:22-150); keyword defaults are the reference's
     hard-coded constants (:24,:49-54).  `trace` (a list) receives (positions, scores) of every swarm
-    evaluation; `swarm_fn` overrides the evaluator (tests); `distributed` shards the swarm over the
-    initialised torch.distributed group (default: automatically when world_size > 1)."""
+    evaluation; `swarm_fn` overrides the evaluator (tests).
+
+    Under an initialised torch.distributed group (world_size > 1) every rank must follow the same trajectory.  The
+    reference is unseeded (SMT's LHS draws from a private RandomState, r1 / r2 / the restart noise from the
+    global np.random stream), so nothing may be assumed identical across ranks: rank 0's initial swarm and rank 0's
+    np.random state are broadcast once, before the first evaluation (every other rank's global np.random state is
+    replaced by it: the run then equals the single-process run of rank 0, seeded or not), and the result is broadcast
+    at the end.  `distributed`: True shards the swarm evaluation over the ranks (each evaluates its slice, one
+    all-gather of the losses per iteration), False keeps it local (every rank evaluates the whole swarm redundantly,
+    no communication per iteration); None (default) shards only when one swarm evaluation is worth more than the
+    exchange (sharding.worth_sharding)."""
     x_known = np.asarray(x_known, dtype=np.float64)
     y_known = np.asarray(y_known, dtype=np.float64)
     e_known = np.asarray(e_known, dtype=np.float64)
@@ -182,11 +191,17 @@ def len_scale_opt(x_known, y_known, e_known, PSO_progress, *, num_particles=40, 
     positions = np.array(sampler(num_particles), dtype=np.float64)
     velocities = np.zeros_like(positions)
 
+    in_group = sharding.world()[1] > 1
+    if in_group:
+        # one exchange per optimisation: the start of the trajectory (initial swarm + RNG stream) is rank 0's
+        positions, rng_state = sharding.broadcast_object((positions, np.random.get_state()))
+        positions = np.array(positions, dtype=np.float64)
+        np.random.set_state(rng_state)
     evaluate = swarm_fn if swarm_fn is not None else SwarmLoss(
         x_known, y_known, e_known, sigma_vals, expected_percents, lower_bounds, upper_bounds)
     if distributed is None:
-        distributed = sharding.world()[1] > 1
-    if distributed:
+        distributed = in_group and sharding.worth_sharding(num_particles, x_known.shape[1])
+    if distributed and in_group:
         evaluate = sharding.ShardedSwarm(evaluate)
 
     def scored(p):
@@ -242,6 +257,8 @@ def len_scale_opt(x_known, y_known, e_known, PSO_progress, *, num_particles=40, 
             stall = 0
             restart_count += 1
 
+    if in_group:
+        gbest_pos, gbest_score = sharding.broadcast_object((gbest_pos, gbest_score))
     print("PSO completed.")
     print("Optimal length scale found:")
     print(gbest_pos)

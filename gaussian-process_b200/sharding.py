@@ -83,9 +83,38 @@ def all_gather_losses(local, n_total, group=None):
     return np.concatenate(parts)
 
 
+# A swarm is sharded only when one evaluation of it is worth more than the exchange: the all-gather of the losses costs a
+# host->device copy, a latency-bound NCCL collective and a device->host copy per PSO iteration (~0.1 ms), the one-CTA path
+# evaluates a 40-particle swarm of 100 points in 0.13 ms, and the blocked path below ~2000 points is bound by its chain of
+# dependent launches, not by the number of particles.  Below the threshold every rank evaluates the whole
+# swarm redundantly from the same (broadcast) RNG state: zero communication per iteration, identical results.
+SHARD_MIN_FLOPS = 3.0e11          # P * 2/3 N^3 of one swarm evaluation (C3: 1.2e13; C2: 4.6e10; default PSO: 2.7e7)
+
+
+def worth_sharding(n_particles, n_points):
+    return n_points > 128 and n_particles * (2.0 / 3.0) * float(n_points) ** 3 >= SHARD_MIN_FLOPS
+
+
+def broadcast_object(obj, src=0, group=None):
+    """`obj` of rank `src` on every rank (pickled; used once per optimisation, not per iteration)."""
+    rank, size = dist_world()
+    if size == 1:
+        return obj
+    box = [obj if rank == src else None]
+    dist.broadcast_object_list(box, src=src, group=group)
+    return box[0]
+
+
 class ShardedSwarm:
     """Wraps a swarm evaluator `fn(positions (p,d)) -> losses (p,)` so that each rank evaluates only
-    its slice and all ranks see all losses."""
+    its slice and all ranks see all losses.
+
+    A failure on one rank (numpy.linalg.LinAlgError from a covariance that is not positive definite, GP_func.py:22, or a
+    library error) must not leave the other ranks waiting in the collective: the local evaluation is caught, the slice
+    travels with a status word, and the same exception type is raised on every rank after the exchange -- the reference
+    aborts the whole run from its pool worker (find_len_scales.py:103)."""
+
+    _OK, _LINALG, _OTHER = 0.0, 1.0, 2.0
 
     def __init__(self, fn, group=None):
         self.fn = fn
@@ -95,8 +124,27 @@ class ShardedSwarm:
         rank, size = world()
         n = positions.shape[0]
         lo, hi = shard_slice(n, rank, size)
-        local = self.fn(positions[lo:hi]) if hi > lo else np.zeros(0)
-        return all_gather_losses(local, n, self.group)
+        status, err = self._OK, None
+        try:
+            local = np.asarray(self.fn(positions[lo:hi]), dtype=np.float64) if hi > lo else np.zeros(0)
+        except np.linalg.LinAlgError as ex:
+            status, err, local = self._LINALG, ex, np.zeros(hi - lo)
+        except Exception as ex:                     # noqa: BLE001 -- re-raised below, on every rank
+            status, err, local = self._OTHER, ex, np.zeros(hi - lo)
+        width = -(-n // size)
+        padded = np.zeros(width + 1)
+        padded[:hi - lo] = local
+        padded[width] = status
+        every = all_gather_losses(padded, size * (width + 1), self.group).reshape(size, width + 1)
+        worst = every[:, width].max()
+        if worst != self._OK:
+            if err is not None:
+                raise err
+            bad = int(np.argmax(every[:, width]))
+            if worst == self._LINALG:
+                raise np.linalg.LinAlgError(f"Matrix is not positive definite (swarm slice of rank {bad})")
+            raise RuntimeError(f"swarm evaluation failed on rank {bad}")
+        return np.concatenate([every[r, :shard_slice(n, r, size)[1] - shard_slice(n, r, size)[0]] for r in range(size)])
 
 
 def gather_rows(local, n_total, group=None):

@@ -25,11 +25,36 @@ extern "C" {
 #define GPK_API
 #endif
 
-#define GPK_VERSION 100
+#define GPK_VERSION 200
 #define GPK_NB 128            /* tile edge; N is padded to a multiple of it internally (Np) */
 #define GPK_SMALL_N_MAX 128   /* N <= this: one-CTA shared-memory path */
-#define GPK_MAX_D 8
-#define GPK_MAX_S 4096
+#define GPK_MAX_D 8            /* kinematic dimensions; more is an error (status 2), not a fallback */
+#define GPK_MAX_S 4096         /* sigma-scale grid points; find_len_scales.py:66 uses 1000 */
+
+/* `precision` argument: arithmetic of the dense contractions of the blocked path (N > 128) -- the Cholesky trailing updates,
+ * GP_func.py:22, and the triangular-inverse updates that replace the N-right-hand-side solve of GP_func.py:38.  It is a
+ * per-call argument: the library keeps no precision state, two host threads may use different modes concurrently.
+ *   GPK_PREC_FP64   native FP64 tensor instructions (DMMA, mma.sync.m8n8k4.f64) -- sm_100a has no FP64 kind of tcgen05.mma;
+ *   GPK_PREC_EMU34  emulated FP64: every operand is split error-free into 7 signed 8-bit digits (Ozaki scheme), the 34 digit
+ *                   products of weight >= 2^-56 run on the int8 tcgen05 tensor cores with exact int32 accumulation in TMEM,
+ *                   the FP64 result is rebuilt in the epilogue.  Rounding level of an FP64 dot product of the same length.
+ *                   Requires e > 0 (the column bound |L^-1[i][k]| <= 1 / e_k is used) and N <= 16256;
+ *   GPK_PREC_EMU28  the 28 digit products of weight >= 2^-48 (7 digits, truncation ~2^8 larger);
+ *   GPK_PREC_EMU21  6 digits, 21 products (operands rounded to 47 bits + sign relative to their row scale);
+ *   GPK_PREC_EMU15  5 digits, 15 products (39 bits + sign).
+ * The reduced modes are meant to be used with the a-posteriori check (check_tol of gpk_loss_batched, probe_out of gpk_fit). */
+#define GPK_PREC_FP64 0
+#define GPK_PREC_EMU34 1
+#define GPK_PREC_EMU28 2
+#define GPK_PREC_EMU21 3
+#define GPK_PREC_EMU15 4
+
+/* `form` argument of gpk_loss_batched: which algebraic form of the self-prediction the loss uses.
+ *   GPK_FORM_REDUCED    mu - y = -e^2 alpha, var = e^2 - e^4 (K^-1)_ii (triangular inverse, 2/3 N^3 flop; every N);
+ *   GPK_FORM_REFERENCE  the reference's own formulae, GP_func.py:36-40: mu = K_s^T alpha, v = L^-1 K_s, var = 1 - sum v^2
+ *                       (4/3 N^3 flop, with the reference's cancellations); one-CTA path only (N <= GPK_SMALL_N_MAX). */
+#define GPK_FORM_REDUCED 0
+#define GPK_FORM_REFERENCE 1
 
 GPK_API int gpk_version(void);
 GPK_API const char* gpk_last_error_string(void);            /* HOST string, valid until the next failing call */
@@ -63,21 +88,32 @@ GPK_API int gpk_selfpredict_counts(const double* L, const double* alpha, const d
 
 /* (b) the PSO hot call: evaluate_loss for a whole swarm, find_len_scales.py:154-163 up to the counts.
  *     counts[p][s] = #{ i : |mu_i - y_i| / max(sd_i * sigma_vals[s], 1e-12) <= 1 } (int32); the host finishes
- *     :163-177 in NumPy.  active[p] == 0 marks an out-of-bounds particle (find_len_scales.py:156): it is not
- *     fitted and its counts are 0.  resid_out / sig_out ([P][N], optional, may be NULL) receive mu - y and sd.
- *     info[p] != 0: covariance not positive definite (the reference raises LinAlgError). */
-GPK_API size_t gpk_loss_workspace_bytes(int P, int N, int d);
+ *     :163-177 in NumPy.  sigma_vals must be ascending (the count is found by bisection: the predicate is monotone in s;
+ *     the Python mirror sorts and un-permutes other grids).  active[p] == 0 marks an out-of-bounds particle
+ *     (find_len_scales.py:156): it is not fitted and its counts are 0.  resid_out / sig_out ([P][N], optional, may be NULL)
+ *     receive mu - y and sd.  info[p] != 0: covariance not positive definite (the reference raises LinAlgError).
+ *
+ *     Checked mixed precision (blocked path): when check_tol > 0 or probe_out != NULL every particle's factor is probed
+ *     with one fixed pseudo-random vector v: rho_p = |W^T (W (K v)) - v|_inf / |v|_inf, W = L^-1 as computed, K as built
+ *     (three N^2 matrix-vector products fused into passes that exist anyway).  rho_p -> probe_out[p] (optional).  With an
+ *     emulated `precision` and check_tol > 0, every particle with rho_p > check_tol (or NaN) is evaluated again by the
+ *     native FP64 kernels inside the same call and fallback_out[p] (optional, [P] bytes) is set to 1.  No host
+ *     synchronisation: the call stays asynchronous and can be captured into a CUDA graph. */
+GPK_API size_t gpk_loss_workspace_bytes(int P, int N, int d, int precision);
 GPK_API int gpk_loss_batched(const double* X, const double* y, const double* e, const double* ls,
                      const unsigned char* active, const double* sigma_vals, int P, int N, int d, int S,
-                     int* counts_out, int* info, double* resid_out, double* sig_out, void* workspace,
+                     int precision, int form, double check_tol, int* counts_out, int* info, double* resid_out,
+                     double* sig_out, double* probe_out, unsigned char* fallback_out, void* workspace,
                      size_t workspace_bytes, void* stream);
 
 /* (b)+(c) GP(): fit part, GP_func.py:21-24.  Produces the cached state used by gpk_predict:
- *     W = L^-1 ([Np][Np], lower block triangle), alpha = K^-1 y ([Np]), xs = X / l ([d][Np]), sq ([Np]). */
-GPK_API size_t gpk_fit_workspace_bytes(int N, int d);
-GPK_API int gpk_fit(const double* X, const double* y, const double* e, const double* ls, int N, int d, double* W_out,
-            double* alpha_out, double* xs_out, double* sq_out, int* info, void* workspace,
-            size_t workspace_bytes, void* stream);
+ *     W = L^-1 ([Np][Np], lower block triangle), alpha = K^-1 y ([Np]), xs = X / l ([d][Np]), sq ([Np]).
+ *     probe_out (optional, one double): the residual probe rho of gpk_loss_batched for this factor; the caller refits with
+ *     GPK_PREC_FP64 when it exceeds its tolerance (engine.GPFit does). */
+GPK_API size_t gpk_fit_workspace_bytes(int N, int d, int precision);
+GPK_API int gpk_fit(const double* X, const double* y, const double* e, const double* ls, int N, int d, int precision,
+            double* W_out, double* alpha_out, double* xs_out, double* sq_out, int* info, double* probe_out,
+            void* workspace, size_t workspace_bytes, void* stream);
 
 /* (c) GP(): predict part, GP_func.py:26-45, for M grid points Xfit (d, M):
  *     mu = K_*^T alpha, sd = sqrt(clip(1 - |W k_*|^2, 1e-12)).  chunk = grid points per internal pass. */
@@ -86,16 +122,16 @@ GPK_API int gpk_predict(const double* W, const double* alpha, const double* xs, 
                 int N, int d, const double* Xfit, long long M, double* mu_out, double* sd_out, int chunk,
                 void* workspace, size_t workspace_bytes, void* stream);
 
-/* (c) the same prediction with |W k_*|^2 on the int8 tcgen05 digit GEMM (emulated FP64, see gpk_set_precision):
+/* (c) the same prediction with |W k_*|^2 on the int8 tcgen05 digit GEMM (emulated FP64, see GPK_PREC_*):
  *     gpk_predict_prepare slices the fitted W once into a caller-owned state buffer (needs e > 0), gpk_predict_emu then
  *     builds the digits of each K_* chunk on the fly (no FP64 K_* in HBM) and reduces the squares in the epilogue.
- *     Results do not depend on `chunk`. */
+ *     Results do not depend on `chunk`.  precision: one of GPK_PREC_EMU* (digit products kept by the GEMM). */
 GPK_API size_t gpk_predict_state_bytes(int N);
 GPK_API int gpk_predict_prepare(const double* W, const double* e, int N, void* state, size_t state_bytes, void* stream);
 GPK_API size_t gpk_predict_emu_workspace_bytes(int N, int chunk);
 GPK_API int gpk_predict_emu(const void* state, const double* alpha, const double* xs, const double* sq, const double* ls,
-                    int N, int d, const double* Xfit, long long M, double* mu_out, double* sd_out, int chunk,
-                    void* workspace, size_t workspace_bytes, void* stream);
+                    int N, int d, int precision, const double* Xfit, long long M, double* mu_out, double* sd_out,
+                    int chunk, void* workspace, size_t workspace_bytes, void* stream);
 
 /* (d) generate_prob_surf row loop, calc_prob_surf.py:67-81 + sum_gaussians :15-30.
  *     table: [R][ncols] payload columns of the merged frame (interleaved mean, std; non-finite = gap).
@@ -108,28 +144,17 @@ GPK_API int gpk_prob_surface(const double* table, long long R, int ncols, int np
 GPK_API int gpk_sum_gaussians(const double* y, int n, const double* gaus, int ng, double half_dy, double* p_out,
                       void* stream);
 
-/* Number of concurrent particle groups (streams) gpk_loss_batched splits a swarm into on the blocked path
- * (default 4, 1..8).  Results do not depend on it. */
-GPK_API int gpk_set_groups(int groups);
+/* Scheduling knob, process-wide, results do not depend on it: gpk_loss_batched splits a swarm on the blocked path into at
+ * most `groups` particle groups on concurrent streams (default 4, 1..8), each of at least `min_particles_per_group`
+ * particles (default 32: smaller groups leave the persistent digit-GEMM launches of late block columns with fewer tiles
+ * than SMs). */
+GPK_API int gpk_set_groups(int groups, int min_particles_per_group);
 
-/* Arithmetic of the two dense contractions of the blocked path (Cholesky trailing updates, GP_func.py:22, and the
- * triangular-inverse updates that replace the N-right-hand-side solve of GP_func.py:38):
- *   0  native FP64 tensor instructions (DMMA, mma.sync.m8n8k4.f64) -- sm_100a has no FP64 kind of tcgen05.mma;
- *   1  emulated FP64: every operand is split error-free into 7 signed 8-bit digits (Ozaki scheme), the 34 digit
- *      products of weight >= 2^-56 run on the int8 tcgen05 tensor cores with exact int32 accumulation in TMEM, and
- *      the FP64 result is rebuilt in the epilogue.  Rounding level: that of an FP64 dot product of the same length
- *      (checked against the reference in tests/test_gpu_parity.py).  Requires e > 0 (the column bound
- *      |L^-1[i][k]| <= 1 / e_k is used) and N <= 16256 (8 products of 2^14 per k stay exact in int32 for K < 2^14);
- *   2  as 1 with the 28 digit products of weight >= 2^-48 only (21 % less tensor work, ~2^8 larger truncation).
- * The mode also sizes gpk_loss_workspace_bytes / gpk_fit_workspace_bytes: set it before querying them. */
-GPK_API int gpk_set_precision(int mode);
-GPK_API int gpk_get_precision(void);
-
-/* Emulated-FP64 primitives (used by the blocked path in mode 1, exposed for tests and measurement).
+/* Emulated-FP64 primitives (used by the blocked path in the GPK_PREC_EMU* modes, exposed for tests and measurement).
  *   gpk_oz_slice: rows x cols FP64 (both multiples of 128, row stride ld) -> digit records; rowinv[r] (optional) is
  *     the reciprocal power-of-two row scale: |src[r][c] * rowinv[r]| <= 1/2 is the caller's contract.
  *   gpk_oz_gemm_tn: C[M][N] = sum_k A[m][k] B[n][k] over sliced operands, scaled by sa[m] * sb[n] (the row scales).
- *     groups = 8 (34 digit products) or 7 (28); dbg (optional) receives the raw int32 accumulators
+ *     groups = 8 (34 digit products), 7 (28), 6 (21) or 5 (15); dbg (optional) receives the raw int32 accumulators
  *     [M/128][N/64][groups][128][64]. */
 GPK_API size_t gpk_oz_slice_bytes(int rows, int cols);
 GPK_API int gpk_oz_slice(const double* src, int ld, int rows, int cols, const double* rowinv, void* dst, void* stream);

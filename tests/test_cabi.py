@@ -21,18 +21,21 @@ def test_library_exports_every_symbol():
     lib = _lib.load()
     for name in declared_symbols():
         assert hasattr(lib, name), name
-    assert lib.gpk_version() == 100
+    assert lib.gpk_version() == 200
     assert lib.gpk_padded_n(1) == 128 and lib.gpk_padded_n(128) == 128 and lib.gpk_padded_n(4097) == 4224
 
 
 def test_workspace_queries():
     lib = _lib.load()
-    assert lib.gpk_loss_workspace_bytes(40, 100, 2) <= 4096            # small path needs no scratch
-    one = lib.gpk_loss_workspace_bytes(1, 4096, 3)
+    assert lib.gpk_loss_workspace_bytes(40, 100, 2, 0) <= 4096         # small path needs no scratch
+    one = lib.gpk_loss_workspace_bytes(1, 4096, 3, 0)
     assert one >= 4096 * 4096 * 8
-    assert lib.gpk_loss_workspace_bytes(256, 4096, 3) >= 256 * 4096 * 4096 * 8
+    # precision is a per-call argument (no library state): the emulated modes add the digit records
+    assert lib.gpk_loss_workspace_bytes(1, 4096, 3, 1) > one + 4096 * 4096 * 7 // 2
+    assert lib.gpk_loss_workspace_bytes(1, 4096, 3, 4) == lib.gpk_loss_workspace_bytes(1, 4096, 3, 1)
+    assert lib.gpk_loss_workspace_bytes(256, 4096, 3, 0) >= 256 * 4096 * 4096 * 8
     assert lib.gpk_predict_workspace_bytes(4096, 4096) >= 4096 * 4096 * 8
-    assert lib.gpk_fit_workspace_bytes(1000, 2) > 0
+    assert 0 < lib.gpk_fit_workspace_bytes(1000, 2, 0) < lib.gpk_fit_workspace_bytes(1000, 2, 1)
     assert lib.gpk_potrf_workspace_bytes(2, 256) == 2 * 2 * 2 * 128 * 128 * 8
 
 

@@ -28,12 +28,33 @@ def _worker(rank, size, port, out_dir):
     # 1) plain gather, ragged split (7 particles over 2 ranks)
     pos = orc.center_lhs(np.column_stack((lo, hi)), 7, np.random.RandomState(1))
     full = sharding.ShardedSwarm(swarm)(pos)
-    # 2) a short seeded PSO: every rank must walk the identical trajectory
-    np.random.seed(11)
+    # 2) a short PSO, sharded: every rank must walk the identical trajectory -- rank 0's -- although the ranks are seeded
+    #    DIFFERENTLY (the reference is unseeded, SURVEY F5: nothing may be assumed identical across ranks)
+    np.random.seed(11 + 100 * rank)
     trace = []
-    best = pso.len_scale_opt(x, y, e, False, num_particles=9, max_iter=12, lhs_random_state=2, swarm_fn=swarm,
-                             trace=trace)
-    np.savez(os.path.join(out_dir, f"r{rank}.npz"), full=full, best=best, calls=np.array(calls),
+    best = pso.len_scale_opt(x, y, e, False, num_particles=9, max_iter=12, lhs_random_state=2 + rank, swarm_fn=swarm,
+                             trace=trace, distributed=True)
+    n_sharded = len(calls)
+    # 3) the default policy keeps a swarm this small local: whole swarm on every rank, no per-iteration exchange
+    np.random.seed(5 + rank)
+    trace_local = []
+    best_local = pso.len_scale_opt(x, y, e, False, num_particles=9, max_iter=6, lhs_random_state=7 + rank,
+                                   swarm_fn=swarm, trace=trace_local)
+    # 4) a failure on ONE rank's slice surfaces on EVERY rank (no hang in the collective)
+
+    def failing(positions):
+        if rank == 1:
+            raise np.linalg.LinAlgError("Matrix is not positive definite")
+        return np.zeros(len(positions))
+
+    raised = ""
+    try:
+        sharding.ShardedSwarm(failing)(pos)
+    except np.linalg.LinAlgError as ex:
+        raised = "LinAlgError:" + str(ex)
+    np.savez(os.path.join(out_dir, f"r{rank}.npz"), full=full, best=best, calls=np.array(calls[:n_sharded]),
+             calls_local=np.array(calls[n_sharded:]), best_local=best_local,
+             pos_local=np.array([t[0] for t in trace_local]), raised=np.array(raised),
              pos=np.array([t[0] for t in trace]), sc=np.array([t[1] for t in trace]))
     dist.barrier()
     dist.destroy_process_group()
@@ -44,8 +65,12 @@ def test_sharded_swarm_world2(tmp_path):
     mp.spawn(_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
     r0 = np.load(tmp_path / "r0.npz")
     r1 = np.load(tmp_path / "r1.npz")
-    for k in ("full", "best", "pos", "sc"):
+    for k in ("full", "best", "pos", "sc", "best_local", "pos_local"):
         assert np.array_equal(r0[k], r1[k]), k
+    assert set(r0["calls_local"]) == {9} and set(r1["calls_local"]) == {9}          # whole swarm, every rank
+    assert str(r0["raised"]).startswith("LinAlgError") and str(r1["raised"]).startswith("LinAlgError")
+    from gaussian_process_b200 import sharding as _sh
+    assert not _sh.worth_sharding(40, 100) and not _sh.worth_sharding(64, 1024) and _sh.worth_sharding(256, 4096)
     # each rank evaluated only its share
     assert r0["calls"][0] == 4 and r1["calls"][0] == 3
     assert set(r0["calls"][1:]) == {5} and set(r1["calls"][1:]) == {4}
