@@ -41,6 +41,7 @@ SIGNATURES = {
     "gpk_csv_surface_bound": (_sz, [_ll, _i, _i]),
     "gpk_csv_format_surface": (_ll, [_vp, _vp, _vp, _ll, _i, _i, _vp, _sz, _i]),
     "gpk_finish_wasserstein": (_i, [_vp, _ll, _i, _vp, _i, _vp, _vp, _vp, _vp]),
+    "gpk_debug_trap": (_i, [_vp]),
     "gpk_timing_begin": (_i, [_vp]),
     "gpk_timing_end": (_i, []),
     "gpk_timing_query": (_i, [_i, C.c_char_p, _i, C.POINTER(C.c_double), C.POINTER(C.c_longlong)]),

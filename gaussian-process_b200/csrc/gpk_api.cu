@@ -649,6 +649,18 @@ int gpk_set_groups(int groups, int min_particles_per_group) {
     return 0;
 }
 
+// test hook: a kernel that traps, to show how a device-side fault (e.g. the pipeline watchdog of the digit GEMM, mbar_wait)
+// reaches the caller: every later entry point returns a non-zero status and gpk_last_error_string() names the CUDA error
+__global__ void k_debug_trap() { __trap(); }
+int gpk_debug_trap(void* stream) {
+    set_stream((cudaStream_t)stream);
+    k_debug_trap<<<1, 32, 0, (cudaStream_t)stream>>>();
+    if (check_launch("k_debug_trap")) return 1;
+    cudaError_t e = cudaStreamSynchronize((cudaStream_t)stream);
+    if (e != cudaSuccess) { set_error("k_debug_trap: %s", cudaGetErrorString(e)); return 1; }
+    return 0;
+}
+
 int gpk_timing_begin(void* stream) {
     g_cur_stream = (cudaStream_t)stream;
     for (auto& r : g_recs) g_pool.push_back(r.ev);

@@ -12,7 +12,10 @@
 
 namespace gpk {
 
-constexpr int SURF_MAX_COLS = 128;   // 2 * (max experiments per row)
+// payload columns per row = 2 * experiments.  The compacted finite entries of a row live in shared memory, 8 rows (warps)
+// per CTA: static up to 128 columns, dynamic (opt-in, up to 200 KB) beyond; 3072 columns = 1536 experiments is the limit.
+constexpr int SURF_STATIC_COLS = 128;
+constexpr int SURF_MAX_COLS = 3072;
 
 __device__ __forceinline__ double ndtr(double a) {
     if (isnan(a)) return a;
@@ -33,12 +36,12 @@ __device__ __forceinline__ double norm_cdf(double x, double loc, double scale) {
 __global__ void __launch_bounds__(256) k_prob_surface(const double* __restrict__ table, long long R, int ncols,
                                                       int npoints, double* __restrict__ y_out,
                                                       double* __restrict__ p_out, int* __restrict__ valid_out) {
-    __shared__ double s_vals[8][SURF_MAX_COLS];
+    extern __shared__ double s_vals[];           // [8][pitch], pitch = ncols rounded up to 32
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const long long r = (long long)blockIdx.x * 8 + warp;
     if (r >= R) return;
     const double* row = table + r * ncols;
-    double* sv = s_vals[warp];
+    double* sv = s_vals + (size_t)warp * ((ncols + 31) & ~31);
 
     int cnt = 0;
     for (int base = 0; base < ncols; base += 32) {
@@ -113,11 +116,23 @@ int launch_sum_gaussians(const double* y, int n, const double* gaus, int ng, dou
 
 int launch_prob_surface(const double* table, long long R, int ncols, int npoints, double* y_out, double* p_out,
                         int* valid_out, cudaStream_t st) {
-    if (ncols > SURF_MAX_COLS || ncols < 0) { set_error("prob_surface: ncols=%d unsupported (max %d)", ncols, SURF_MAX_COLS); return 2; }
+    if (ncols > SURF_MAX_COLS || ncols < 0) {
+        set_error("prob_surface: %d payload columns (%d experiments); at most %d columns (%d experiments) fit the per-row shared-memory staging",
+                  ncols, ncols / 2, SURF_MAX_COLS, SURF_MAX_COLS / 2);
+        return 2;
+    }
     if (R <= 0) return 0;
     const long long blocks = (R + 7) / 8;
     if (blocks > 0x7fffffffLL) { set_error("prob_surface: too many rows"); return 2; }
-    k_prob_surface<<<(unsigned)blocks, 256, 0, st>>>(table, R, ncols, npoints, y_out, p_out, valid_out);
+    const int pitch = (ncols + 31) & ~31;
+    const size_t smem = (size_t)8 * (pitch < SURF_STATIC_COLS ? SURF_STATIC_COLS : pitch) * sizeof(double);
+    static size_t configured = 48 * 1024;
+    if (smem > configured) {
+        cudaError_t er = cudaFuncSetAttribute(k_prob_surface, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (er != cudaSuccess) { set_error("k_prob_surface smem attr: %s", cudaGetErrorString(er)); return 1; }
+        configured = smem;
+    }
+    k_prob_surface<<<(unsigned)blocks, 256, smem, st>>>(table, R, ncols, npoints, y_out, p_out, valid_out);
     return check_launch("k_prob_surface");
 }
 

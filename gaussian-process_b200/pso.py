@@ -155,7 +155,7 @@ def swarm_bounds(x_known):
 
 def len_scale_opt(x_known, y_known, e_known, PSO_progress, *, num_particles=40, max_iter=500, patience=100,
                   max_points=100, inertia_decay=0.002, lhs_random_state=None, swarm_fn=None, trace=None,
-                  distributed=None):
+                  distributed=None, timings=None):
     """Drop-in for find_len_scales.len_scale_opt (:22-150); keyword defaults are the reference's
     hard-coded constants (:24,:49-54).  `trace` (a list) receives (positions, scores) of every swarm
     evaluation; `swarm_fn` overrides the evaluator (tests).
@@ -168,13 +168,17 @@ def len_scale_opt(x_known, y_known, e_known, PSO_progress, *, num_particles=40, 
     at the end.  `distributed`: True shards the swarm evaluation over the ranks (each evaluates its slice, one
     all-gather of the losses per iteration), False keeps it local (every rank evaluates the whole swarm redundantly,
     no communication per iteration); None (default) shards only when one swarm evaluation is worth more than the
-    exchange (sharding.worth_sharding)."""
+    exchange (sharding.worth_sharding).  `timings` (a dict) accumulates the seconds of the KMeans subsample and of the
+    swarm loop under "kmeans" / "pso"."""
+    import time as _time
     x_known = np.asarray(x_known, dtype=np.float64)
     y_known = np.asarray(y_known, dtype=np.float64)
     e_known = np.asarray(e_known, dtype=np.float64)
+    _t0 = _time.perf_counter()
     if x_known.shape[1] > max_points:
         print(f"Dataset too large ({x_known.shape[1]} points). Subsampling to {max_points} for hyperparameter optimisation.")
         x_known, y_known, e_known = kmeans_subsample(x_known, y_known, e_known, max_points)
+    _t1 = _time.perf_counter()
 
     ndim = len(x_known)
     restart_count = 0
@@ -259,6 +263,9 @@ def len_scale_opt(x_known, y_known, e_known, PSO_progress, *, num_particles=40, 
 
     if in_group:
         gbest_pos, gbest_score = sharding.broadcast_object((gbest_pos, gbest_score))
+    if timings is not None:
+        timings["kmeans"] = timings.get("kmeans", 0.0) + (_t1 - _t0)
+        timings["pso"] = timings.get("pso", 0.0) + (_time.perf_counter() - _t1)
     print("PSO completed.")
     print("Optimal length scale found:")
     print(gbest_pos)

@@ -37,3 +37,22 @@ def surface_table(r, n_exp, seed=0, p_gap=0.25):
     t[:, 0::2] = mu
     t[:, 1::2] = sd
     return t
+
+
+def c4_experiments(rows=8192, n_exp=8, seed=4):
+    """BASELINE config C4: one 2-D file of `rows` points, `n_exp` experiments with inf-masked gaps (a row is finite in an
+    experiment with probability 0.5 -> ~rows / 2 points each; the 4 box corners are always present so every hull is the
+    unit box).  Returns (x_list, [(y, e), ...]) in the layout read_in.read_data hands to GP_fit (read_in.py:204-254)."""
+    rng = np.random.default_rng(seed)
+    x = rng.random((2, rows))
+    x[:, :4] = np.array([[0, 0, 1, 1], [0, 1, 0, 1]], dtype=np.float64)
+    x_list, pairs = [], []
+    for k in range(n_exp):
+        keep = rng.random(rows) < 0.5
+        keep[:4] = True
+        xk = np.ascontiguousarray(x[:, keep])
+        yk = np.sin(2 * np.pi * xk[0]) + np.sin(2 * np.pi * xk[1]) + 0.3 * k + 0.1 * rng.standard_normal(xk.shape[1])
+        ek = rng.uniform(0.05, 0.15, xk.shape[1])
+        x_list.append(xk)
+        pairs.append((yk, ek))
+    return x_list, pairs

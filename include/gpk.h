@@ -184,6 +184,11 @@ GPK_API long long gpk_csv_format_surface(const double* coords, const double* y, 
 GPK_API int gpk_finish_wasserstein(const int* counts, long long P, int S, const double* measured_of, int n_points,
                            const double* expected, const double* d_sigma, double* scratch, double* out);
 
+/* Test hook: launches a kernel that executes a trap and waits for it.  Returns non-zero with gpk_last_error_string() set; the
+ * CUDA context of the process is unusable afterwards (every later entry point fails the same way) -- run it in a child
+ * process (tests/test_gpu_faults.py).  It shows how the watchdog trap of the digit-GEMM pipeline would surface. */
+GPK_API int gpk_debug_trap(void* stream);
+
 /* Measurement aid (bench.py roofline): per-kernel-class device time by events recorded after every launch
  * on `stream` between begin and end.  Not thread-safe; name_out is a HOST buffer. */
 GPK_API int gpk_timing_begin(void* stream);

@@ -50,7 +50,7 @@ def _operands(m, n, k, seed):
     return a, b
 
 
-@pytest.mark.parametrize("groups", [7, 8])
+@pytest.mark.parametrize("groups", [5, 6, 7, 8])
 def test_digit_gemm_exact(env, groups):
     torch, lib, _lib, engine = env
     m, n, k = 256, 128, 384
@@ -90,8 +90,9 @@ def test_digit_gemm_exact(env, groups):
     np.testing.assert_array_equal(got, acc)                                   # integer work: exact
     ref = (a.astype(np.longdouble) @ b.astype(np.longdouble).T).astype(np.float64)
     err = np.abs(c.cpu().numpy() - ref) / (sa[:, None] * sb[None, :])
-    # groups = 8: FP64 rounding of the result only; groups = 7: + the dropped weight-2^-56 products
-    assert err.max() < (4e-15 if groups == 8 else 4e-14)
+    # groups = 8: FP64 rounding of the result only; fewer groups: + the dropped digit products, each of weight
+    # <= 2^(-8 g) of the scale product per contraction index (worst case, k = 384)
+    assert err.max() < {8: 4e-15, 7: 4e-14, 6: 1e-11, 5: 3e-9}[groups]
 
 
 def test_emulated_loss_matches_native_and_oracle(env):
@@ -157,35 +158,9 @@ def test_graph_replay_equals_direct_launches(env, mode, monkeypatch):
         engine.set_precision("auto")
 
 
-def test_panel_tile_width_does_not_change_results(env, tmp_path):
-    """The 32-column double-buffered panel tiles (GPK_OZ_PANEL_TN=32, read once per process) give the counts, residuals and
-    standard deviations of the default 64-column tiles bit for bit; emu mode N <= 16256 guard."""
-    import os
-    import subprocess
-    import sys
+def test_emulated_mode_size_guard(env):
+    """Exact int32 accumulation needs contraction lengths below 2^14: N <= 16256 for every emulated mode."""
     torch, lib, _lib, engine = env
-    code = r"""
-import sys, numpy as np
-sys.path.insert(0, sys.argv[1])
-from oracle import gp_oracle as orc
-from gaussian_process_b200 import engine
-x, y, e = orc.synthetic_problem(700, 3, 9)
-pos, lo, hi = orc.synthetic_particles(x, 9, 2)
-s, ex = orc.sigma_grid()
-engine.set_precision("emu")
-c, i, r, sd = engine.LossContext(x, y, e, s).counts(pos, want_detail=True)
-np.savez(sys.argv[2], c=c, i=i, r=r, sd=sd)
-"""
-    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    outs = []
-    for tn in ("64", "32"):
-        out = str(tmp_path / f"tn{tn}.npz")
-        env_vars = dict(os.environ, GPK_OZ_PANEL_TN=tn)
-        subprocess.run([sys.executable, "-c", code, root, out], check=True, env=env_vars, timeout=300)
-        outs.append(np.load(out))
-    for k in ("c", "i", "r", "sd"):
-        assert np.array_equal(outs[0][k], outs[1][k]), k
-    assert not outs[0]["i"].any()
     prev = engine.get_precision()
     engine.set_precision("emu")
     try:
@@ -194,3 +169,9 @@ np.savez(sys.argv[2], c=c, i=i, r=r, sd=sd)
     finally:
         engine.set_precision(prev)
     assert engine._resolve_precision(np.full(4, 0.1), 20000) in (0, 1) and (prev != "auto" or engine._resolve_precision(np.full(4, 0.1), 20000) == 0)
+    assert lib.gpk_loss_workspace_bytes(1, 20000, 2, 0) > 0
+    dummy = torch.zeros(64, dtype=torch.float64, device="cuda")
+    st = lib.gpk_loss_batched(dummy.data_ptr(), dummy.data_ptr(), dummy.data_ptr(), dummy.data_ptr(), None, dummy.data_ptr(),
+                              1, 20000, 2, 10, 1, 0, 0.0, dummy.data_ptr(), dummy.data_ptr(), None, None, None, None,
+                              dummy.data_ptr(), 64, None)
+    assert st == 2 and b"16256" in lib.gpk_last_error_string()

@@ -1,0 +1,162 @@
+"""Parity AT THE SIZES bench.py REPORTS, against outputs of the unmodified reference (tests/golden/*_large.npz, generated
+by oracle/make_golden.py `large` in the build container): the C3 bench problem itself (N=4096, d=3, particles 0 / 85 / 170 /
+255 of the 256-particle bench swarm + one on-bound particle), a C4-sized GP() (N=8192, d=2, 2000 grid points), and an
+adversarial case for the emulated arithmetic (e over six decades, isolated points).  Both arithmetic modes.
+Run on the B200 box: pytest -m gpu."""
+import numpy as np
+import pytest
+
+from conftest import load_golden, case
+from oracle import gp_oracle as orc, truth80
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def eng():
+    from gaussian_process_b200 import engine, pso
+    return engine, pso
+
+
+@pytest.fixture(params=["fp64", "emu"])
+def precision(request, eng):
+    eng[0].set_precision(request.param)
+    yield request.param
+    eng[0].set_precision("auto")
+
+
+def _regenerated(n, d, seed, digest):
+    x, y, e = orc.synthetic_problem(n, d, seed)
+    np.testing.assert_array_equal(np.array([x.sum(), y.sum(), e.sum()]), digest)      # the very arrays the golden was made from
+    return x, y, e
+
+
+def test_loss_golden_c3_n4096(eng, precision):
+    """The bench workload: counts exact, mu - y and sd at 1e-9, loss at 1e-12, no fallback, probe far below the bar."""
+    engine, pso = eng
+    c = case(load_golden("loss_cases_large.npz"), "c3_n4096")
+    x, y, e = _regenerated(4096, 3, 0, c["xye_sum"])
+    s, ex = orc.sigma_grid()
+    oob = pso.out_of_bounds_mask(c["pos"], c["lower"], c["upper"])
+    assert list(oob) == [False, False, False, False, True]
+    ctx = engine.LossContext(x, y, e, s)
+    counts, info, resid, sd, probe = ctx.counts(c["pos"], active=~oob, want_detail=True, want_probe=True)
+    act = ~oob
+    assert not info.any()
+    np.testing.assert_allclose(resid[act] + y, c["resid"][act] + y, rtol=1e-9, atol=1e-12)      # predictive mean
+    np.testing.assert_allclose(resid[act], c["resid"][act], rtol=1e-9, atol=1e-9 * np.abs(c["resid"][act]).max())
+    np.testing.assert_allclose(sd[act], c["sd"][act], rtol=1e-9)
+    assert c["margin"][act].min() > 1e-8                       # no pull of the reference sits on a rounding tie
+    np.testing.assert_array_equal(counts[act], c["counts"][act])                                # integer work: exact
+    assert not counts[oob].any()
+    loss = pso.finish_losses(counts, 4096, c["pos"], s, ex, c["lower"], c["upper"], oob)
+    np.testing.assert_allclose(loss, c["loss"], rtol=1e-12)
+    assert ctx.fallbacks == 0 and probe[act].max() < 1e-11, probe
+    # and through the public call, as part of the whole 256-particle bench swarm (position in the swarm does not matter)
+    pos_all, lo, hi = orc.synthetic_particles(x, 256, 0)
+    idx = c["swarm_index"][:4]
+    losses = pso.evaluate_loss_batch(pos_all[:96], x, y, e, s, ex, lo, hi)
+    np.testing.assert_allclose(losses[[0, 85]], c["loss"][:2], rtol=1e-12)
+    assert list(idx) == [0, 85, 170, 255]
+
+
+def test_gp_golden_large(eng, precision):
+    """GP() of the reference at N=8192 (C4 size) and N=4096 (C3 size): mean and sd at 1e-9."""
+    engine, _ = eng
+    g = load_golden("gp_cases_large.npz")
+    for name, n, d, seed in (("c4_n8192", 8192, 2, 3), ("c3_n4096", 4096, 3, 0)):
+        c = case(g, name)
+        x, y, e = _regenerated(n, d, seed, c["xye_sum"])
+        fit = engine.GPFit(x, y, e, c["ls"])
+        mu, sd = fit.predict(c["grid"].T)
+        np.testing.assert_allclose(mu, c["mu"], rtol=1e-9, atol=1e-9 * np.abs(c["mu"]).max(), err_msg=name)
+        np.testing.assert_allclose(sd, c["sd"], rtol=1e-9, err_msg=name)
+        assert not fit.fell_back and fit.probe < 1e-10, (name, fit.probe)
+
+
+def test_adversarial_uncertainties_trigger_the_fallback(eng):
+    """e log-uniform over 1e-6 .. 1 with isolated points carrying the smallest e: cond(K) ~ 1e12.  The a-priori scales of the
+    emulated arithmetic are loose here; the a-posteriori probe must notice, every particle must be re-evaluated by the native
+    FP64 kernels inside the same call (bit-identical to the fp64 mode), and the result must be as close to an 80-bit
+    evaluation as the reference's own LAPACK path is (a 1e-9 agreement between two FP64 evaluations does not exist at this
+    conditioning: the tolerance is the reference's own distance from the truth)."""
+    engine, pso = eng
+    c = case(load_golden("loss_cases_large.npz"), "adv_n1024")
+    x, y, e, pos = c["x"], c["y"], c["e"], c["pos"]
+    s, ex = orc.sigma_grid()
+    out = {}
+    for mode, tol in (("fp64", 1e-10), ("emu", 1e-10), ("emu", 0.0)):
+        engine.set_precision(mode)
+        engine.set_check_tol(tol)
+        try:
+            ctx = engine.LossContext(x, y, e, s)
+            out[(mode, tol)] = ctx.counts(pos, want_detail=True, want_probe=True) + (ctx.fallbacks,)
+        finally:
+            engine.set_precision("auto")
+            engine.set_check_tol(1e-10)
+    c64, i64, r64, sd64, p64, fb64 = out[("fp64", 1e-10)]
+    cck, ick, rck, sdck, pck, fbck = out[("emu", 1e-10)]
+    assert not i64.any() and not ick.any()
+    assert fb64 == 0                                            # nothing to fall back to in the native mode
+    assert fbck == len(pos) and np.all(pck > 1e-10), pck       # every particle failed the probe ...
+    np.testing.assert_array_equal(cck, c64)                     # ... and was recomputed by the native kernels, in the same call
+    np.testing.assert_array_equal(rck, r64)
+    np.testing.assert_array_equal(sdck, sd64)
+    # which side is off?  80-bit truth for two particles
+    for k in (0, 3):
+        r_t, sd_t = truth80.selfpredict_ld(x, y, e, pos[k])
+        ref_r, ref_sd = truth80.rel_err(c["resid"][k], r_t), truth80.rel_err_pointwise(c["sd"][k], sd_t)
+        got_r, got_sd = truth80.rel_err(rck[k], r_t), truth80.rel_err_pointwise(sdck[k], sd_t)
+        raw = out[("emu", 0.0)]
+        raw_r, raw_sd = truth80.rel_err(raw[2][k], r_t), truth80.rel_err_pointwise(raw[3][k], sd_t)
+        print(f"adversarial particle {k}: error vs 80-bit truth  reference {ref_r:.2e} / {ref_sd:.2e}   checked "
+              f"{got_r:.2e} / {got_sd:.2e}   unchecked emulation {raw_r:.2e} / {raw_sd:.2e}   probe {pck[k]:.2e}")
+        assert got_r <= max(1e-9, 4 * ref_r) and got_sd <= max(1e-9, 4 * ref_sd)
+
+
+@pytest.mark.parametrize("mode", ["emu28", "emu21", "emu15"])
+def test_reduced_digit_modes_are_checked(eng, mode):
+    """Fewer digit products (28 / 21 / 15) under the a-posteriori check: whatever the mode, the result that comes back is
+    either within the bar (probe <= 1e-10) or the native FP64 one."""
+    engine, pso = eng
+    x, y, e = orc.synthetic_problem(1024, 2, 5)
+    pos, lo, hi = orc.synthetic_particles(x, 6, 5)
+    s, ex = orc.sigma_grid()
+    engine.set_precision("fp64")
+    try:
+        c64, i64, r64, sd64 = engine.LossContext(x, y, e, s).counts(pos, want_detail=True)
+        engine.set_precision(mode)
+        ctx = engine.LossContext(x, y, e, s)
+        c, i, r, sd, probe = ctx.counts(pos, want_detail=True, want_probe=True)
+        fb = ctx.last_fallback.cpu().numpy().astype(bool)
+    finally:
+        engine.set_precision("auto")
+    assert not i.any()
+    np.testing.assert_array_equal(fb, ~(probe <= 1e-10))
+    np.testing.assert_array_equal(c[fb], c64[fb])               # fallen back: the native result, bit for bit
+    np.testing.assert_array_equal(sd[fb], sd64[fb])
+    ok = ~fb
+    if ok.any():
+        np.testing.assert_allclose(r[ok], r64[ok], rtol=0, atol=1e-9 * np.abs(r64).max())
+        np.testing.assert_allclose(sd[ok], sd64[ok], rtol=1e-9)
+    print(f"{mode}: probe {probe.min():.2e} .. {probe.max():.2e}, fallbacks {int(fb.sum())}/{len(pos)}")
+
+
+def test_unsorted_sigma_grid(eng):
+    """The reference compares element-wise and accepts any order of sigma_vals (find_len_scales.py:161-163); the kernels
+    bisect an ascending grid, so the host side sorts and un-permutes."""
+    engine, pso = eng
+    x, y, e = orc.synthetic_problem(300, 2, 1)
+    pos, lo, hi = orc.synthetic_particles(x, 3, 1)
+    s, ex = orc.sigma_grid()
+    perm = np.random.default_rng(0).permutation(len(s))
+    c_sorted, _ = engine.LossContext(x, y, e, s).counts(pos)
+    c_perm, _ = engine.LossContext(x, y, e, s[perm]).counts(pos)
+    np.testing.assert_array_equal(c_perm, c_sorted[:, perm])
+    x1, y1, e1 = orc.synthetic_problem(60, 2, 1)
+    pos1, _, _ = orc.synthetic_particles(x1, 3, 1)
+    np.testing.assert_array_equal(engine.LossContext(x1, y1, e1, s[perm]).counts(pos1)[0],
+                                  engine.LossContext(x1, y1, e1, s).counts(pos1)[0][:, perm])
+    for k in range(3):
+        want, _, _, _ = orc.calibration_counts(pos1[k], x1, y1, e1, s[perm])
+        np.testing.assert_array_equal(engine.LossContext(x1, y1, e1, s[perm]).counts(pos1)[0][k], want)

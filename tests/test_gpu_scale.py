@@ -51,15 +51,18 @@ def test_loss_n4096_two_routes_agree(eng):
     import torch
     lib = _lib.load()
     ctx = engine.LossContext(x, y, e, s)
-    small = torch.empty(lib.gpk_loss_workspace_bytes(2, n, d), dtype=torch.uint8, device="cuda")
+    mode = engine._resolve_precision(e, n)
+    small = torch.empty(lib.gpk_loss_workspace_bytes(2, n, d, mode), dtype=torch.uint8, device="cuda")
     dpos = engine.to_dev(pos)
     c2 = torch.empty((6, 1000), dtype=torch.int32, device="cuda")
     inf2 = torch.empty(6, dtype=torch.int32, device="cuda")
+    fb = torch.empty(6, dtype=torch.uint8, device="cuda")
     st = lib.gpk_loss_batched(ctx.x.data_ptr(), ctx.y.data_ptr(), ctx.e.data_ptr(), dpos.data_ptr(), None,
-                              ctx.sig.data_ptr(), 6, n, d, 1000, c2.data_ptr(), inf2.data_ptr(), None, None,
-                              small.data_ptr(), small.numel(), torch.cuda.current_stream().cuda_stream)
+                              ctx.sig.data_ptr(), 6, n, d, 1000, mode, 0, 1e-10, c2.data_ptr(), inf2.data_ptr(), None, None,
+                              None, fb.data_ptr(), small.data_ptr(), small.numel(), torch.cuda.current_stream().cuda_stream)
     assert st == 0
     np.testing.assert_array_equal(c2.cpu().numpy(), counts)
+    assert not fb.cpu().numpy().any()                 # the a-posteriori check passes on the bench workload: no fallback
 
 
 def test_potrf_n4096_round_trip(eng):

@@ -14,7 +14,7 @@ for mode in ("fp64", "emu"):
     for graph in ("1", "0"):
         os.environ["GPK_GRAPH"] = graph
         for G in (1, 2, 4, 8):
-            _lib.check(lib.gpk_set_groups(G), "groups")
+            _lib.check(lib.gpk_set_groups(G, 1), "groups")
             engine.set_precision(mode)
             ctx = engine.LossContext(x, y, e, s)
             for _ in range(3): ctx.counts_device(dpos, dact, P)

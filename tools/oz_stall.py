@@ -18,7 +18,7 @@ lib = _lib.load()
 assert hasattr(lib, "gpk_debug_oz_prof"), "not the instrumented build: set GPK_LIB=tools/libgpk_prof.so"
 lib.gpk_debug_oz_prof.restype = C.c_int
 lib.gpk_debug_oz_prof.argtypes = [C.POINTER(C.c_ulonglong), C.c_int]
-_lib.check(lib.gpk_set_groups(G), "gpk_set_groups")
+_lib.check(lib.gpk_set_groups(G, 1), "gpk_set_groups")
 x, y, e = bench.make_problem(0)
 pos, lo, hi = bench.make_particles(x, P, 0)
 s, ex = pso.sigma_grid()

@@ -9,7 +9,7 @@ import time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import numpy as np
-from oracle import gp_oracle as orc
+from oracle import gp_oracle as orc, truth80
 from gaussian_process_b200 import engine
 
 SIZES = [3, 64, 127, 128, 129, 130, 200, 255, 256, 257, 383, 385, 511, 513, 640, 777, 1000, 1023, 1025, 1300, 1537, 2047]
@@ -55,7 +55,18 @@ def _predict_case(rng, sizes, worst):
         es = np.abs(sd / sd_r - 1).max()
         worst["pred_mu"] = max(worst.get("pred_mu", 0.0), em)
         worst["pred_sd"] = max(worst.get("pred_sd", 0.0), es)
-        if not (mu.shape == (m,) and em < 1e-8 and es < 1e-7):
+        if mu.shape == (m,) and not (em < 1e-9 and es < 1e-9) and n <= 2100:
+            # two FP64 evaluations differ by more than the bar: an 80-bit evaluation decides (on a sample of the grid)
+            pick = np.unique(np.concatenate([np.argsort(-np.abs(mu - mu_r))[:20], np.argsort(-np.abs(sd / sd_r - 1))[:20]]))
+            mu_t, sd_t = truth80.predict_ld(x, y, e, grid[:, pick], ls)
+            sc = max(np.abs(mu_r).max(), 1e-300)
+            g_mu, r_mu = np.abs(mu[pick] - mu_t).max() / sc, np.abs(mu_r[pick] - mu_t).max() / sc
+            g_sd, r_sd = np.abs(sd[pick] / sd_t - 1).max(), np.abs(sd_r[pick] / sd_t - 1).max()
+            print(f"  80-bit truth decides predict n={n} d={d} m={m} {mode}: vs checker {em:.2e} / {es:.2e}; vs truth gpu "
+                  f"{g_mu:.2e} / {g_sd:.2e}, checker {r_mu:.2e} / {r_sd:.2e}", flush=True)
+            if g_mu <= max(1e-9, 2 * r_mu) and g_sd <= max(1e-9, 2 * r_sd):
+                em, es = min(em, 1e-10), min(es, 1e-10)
+        if not (mu.shape == (m,) and em < 1e-9 and es < 1e-9):
             bad += 1
             print(f"FAIL predict n={n} d={d} m={m} {mode}: mean err {em:.2e} sd err {es:.2e}", flush=True)
     return bad
@@ -102,14 +113,22 @@ def _case(rng, sizes, s, worst):
                         pass
                     continue
                 c_ref, r_ref, sd_ref, pulls = orc.calibration_counts(pos[k], x, y, e, s)
-                scale = max(np.abs(r_ref).max(), 1e-300)
-                er = np.abs(resid[k] - r_ref).max() / scale
-                es = np.abs(sd[k] / sd_ref - 1).max()
+                try:
+                    er, es, detail = truth80.check_selfpredict(resid[k], sd[k], r_ref, sd_ref, x, y, e, pos[k])
+                    within = True
+                except AssertionError as exc:
+                    er, es, detail = truth80.rel_err(resid[k], r_ref), truth80.rel_err_pointwise(sd[k], sd_ref), str(exc)
+                    within = False
+                if detail is not None and within:
+                    worst["decided_by_truth"] = worst.get("decided_by_truth", 0) + 1
+                    print(f"  80-bit truth decides n={n} d={d} {kind} {mode} particle {k}: vs checker {er:.2e} / {es:.2e}; vs truth "
+                          f"gpu {detail['gpu_resid']:.2e} / {detail['gpu_sd']:.2e}, checker {detail['ref_resid']:.2e} / {detail['ref_sd']:.2e}",
+                          flush=True)
                 worst["resid"] = max(worst["resid"], er)
                 worst["sd"] = max(worst["sd"], es)
                 tie = np.min(np.abs(np.abs(pulls) - 1))
                 dc = int(np.abs(counts[k] - c_ref).max())
-                ok = er < 1e-7 and es < 1e-7 and (dc == 0 or (tie < 1e-7 and dc <= 2))
+                ok = within and (dc == 0 or (tie < 1e-7 and dc <= 2))
                 if not ok:
                     bad += 1
                     print(f"FAIL n={n} d={d} p={p} {kind} {mode} particle {k}: resid err {er:.2e} sd err {es:.2e} count diff {dc} (closest pull to 1: {tie:.1e})", flush=True)

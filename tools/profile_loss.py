@@ -12,7 +12,7 @@ pos, lo, hi = bench.make_particles(x, P, 0)
 s, ex = pso.sigma_grid()
 if os.environ.get("GPK_GROUPS"):
     from gaussian_process_b200 import _lib
-    _lib.check(_lib.load().gpk_set_groups(int(os.environ["GPK_GROUPS"])), "gpk_set_groups")
+    _lib.check(_lib.load().gpk_set_groups(int(os.environ["GPK_GROUPS"]), 1), "gpk_set_groups")
 ctx = engine.LossContext(x, y, e, s)
 dpos = engine.to_dev(pos); dact = torch.ones(P, dtype=torch.uint8, device="cuda")
 counts, info = ctx.counts_device(dpos, dact, P)

@@ -7,7 +7,7 @@ x, y, e = bench.make_problem(0); pos, lo, hi = bench.make_particles(x, P, 0); s,
 ctx = engine.LossContext(x, y, e, s); dpos = engine.to_dev(pos); dact = torch.ones(P, dtype=torch.uint8, device="cuda")
 ref = None
 for G in (1, 2, 4, 8):
-    _lib.load().gpk_set_groups(G)
+    _lib.load().gpk_set_groups(G, 1)
     for _ in range(2): c, info = ctx.counts_device(dpos, dact, P)
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
