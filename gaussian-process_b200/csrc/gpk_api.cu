@@ -216,7 +216,8 @@ static int inverse_phase(double* mat, int Np, int T, int P, const double* dinvT,
 
 // ---- concurrent particle groups ------------------------------------------------------------------
 static int g_groups = 4;
-static int g_min_group = 32;       // particles per group below which a swarm is not split further (gpk_set_groups)
+static bool g_groups_explicit = false;     // gpk_set_groups was called: the small-swarm cap of 2 groups no longer applies
+static int g_min_group = 16;       // particles per group below which a swarm is not split further (gpk_set_groups)
 static cudaStream_t g_group_streams[MAX_GROUPS] = {};
 static cudaEvent_t g_join[MAX_GROUPS] = {};
 static cudaEvent_t g_fork = nullptr;
@@ -399,19 +400,29 @@ static int blocked_pass(const double* X, const double* y, const double* e, const
 
 int gpk_loss_batched(const double* X, const double* y, const double* e, const double* ls,
                      const unsigned char* active, const double* sigma_vals, int P, int N, int d, int S,
-                     int precision, int form, double check_tol, int* counts_out, int* info, double* resid_out,
+                     int precision, int flags, double check_tol, int* counts_out, int* info, double* resid_out,
                      double* sig_out, double* probe_out, unsigned char* fallback_out, void* workspace,
                      size_t workspace_bytes, void* stream) {
     if (bad_dims("gpk_loss_batched", N, d, S) || P < 1) return 2;
     if (bad_precision("gpk_loss_batched", precision, N)) return 2;
-    if (form != GPK_FORM_REDUCED && form != GPK_FORM_REFERENCE) { set_error("gpk_loss_batched: form %d", form); return 2; }
-    if (form == GPK_FORM_REFERENCE && N > SMALL_N_MAX) {
+    if (flags & ~(GPK_FLAG_REFERENCE_FORM | GPK_FLAG_KEEP_INACTIVE)) { set_error("gpk_loss_batched: flags 0x%x", flags); return 2; }
+    const int form = (flags & GPK_FLAG_REFERENCE_FORM) ? 1 : 0;
+    const int zero_inactive = (flags & GPK_FLAG_KEEP_INACTIVE) ? 0 : 1;
+    if (form && N > SMALL_N_MAX) {
         set_error("gpk_loss_batched: the reference-formula form (N^3 solve) exists on the one-CTA path only, N <= %d", SMALL_N_MAX);
+        return 2;
+    }
+    if (!zero_inactive && (active == nullptr || N <= SMALL_N_MAX)) {
+        set_error("gpk_loss_batched: GPK_FLAG_KEEP_INACTIVE needs an active mask and the blocked path (N > %d)", SMALL_N_MAX);
         return 2;
     }
     cudaStream_t st = (cudaStream_t)stream;
     set_stream(st);
-    if (cudaMemsetAsync(info, 0, (size_t)P * sizeof(int), st) != cudaSuccess) { set_error("memset info failed"); return 1; }
+    if (zero_inactive) {
+        if (cudaMemsetAsync(info, 0, (size_t)P * sizeof(int), st) != cudaSuccess) { set_error("memset info failed"); return 1; }
+    } else if (launch_clear_info(info, active, P, st)) {
+        return 1;
+    }
     if (N <= SMALL_N_MAX) {
         // native FP64 in one CTA per particle: nothing is emulated, nothing to check
         if (probe_out && cudaMemsetAsync(probe_out, 0, (size_t)P * 8, st) != cudaSuccess) { set_error("memset probe failed"); return 1; }
@@ -424,13 +435,18 @@ int gpk_loss_batched(const double* X, const double* y, const double* e, const do
     // other groups fill its wave tails and hide the latency-bound diagonal kernel)
     const int emu = precision != GPK_PREC_FP64;
     if (emu) oz_set_groups(groups_of(precision));
-    const bool probe = check_tol > 0.0 || probe_out != nullptr;
-    const bool fallback = emu && check_tol > 0.0;
-    const double tol = check_tol > 0.0 ? check_tol : 1e300;
+    const bool probe = check_tol != 0.0 || probe_out != nullptr;
+    const bool fallback = emu && check_tol > 0.0;              // check_tol < 0: flags only, the caller re-evaluates
+    const double tol = check_tol != 0.0 ? (check_tol > 0.0 ? check_tol : -check_tol) : 1e300;
     const size_t per1 = blocked_layout(1, N, d, emu).total;
     if (workspace == nullptr || workspace_bytes < per1) { set_error("gpk_loss_batched: workspace too small (%zu < %zu)", workspace_bytes, per1); return 3; }
+    // particle groups: measured on one B200 at N = 4096 (profiles/r02_bench_v1.json, strong_scaling_slices_1gpu): 4 groups
+    // of 64 for the full 256-particle swarm, 2 groups for the slices of a sharded swarm (128 / 64 / 32 particles: 2 groups
+    // beat 1 by 1-8 % and 4 by 1-3 %): one group's latency-bound diagonal-block kernel overlaps the other's digit GEMMs,
+    // while each persistent GEMM launch still has enough tiles for the 148 SMs
     int G = g_timing ? 1 : g_groups;
     if (G > P / g_min_group) G = P / g_min_group;
+    if (!g_groups_explicit && G > 2 && P < 256) G = 2;
     if (G < 1) G = 1;
     if (G > 1 && ensure_group_streams(G)) return 1;
     auto fits = [&](int pw) { const int pg = (pw + G - 1) / G; return (size_t)G * blocked_layout(pg, N, d, emu).total <= workspace_bytes; };
@@ -455,7 +471,7 @@ int gpk_loss_batched(const double* X, const double* y, const double* e, const do
             int* cnt = counts_out + (size_t)q0 * S;
             double* rs = resid_out ? resid_out + (size_t)q0 * N : nullptr;
             double* sg = sig_out ? sig_out + (size_t)q0 * N : nullptr;
-            if (blocked_pass(X, y, e, lsp, act, sigma_vals, Pc, N, d, S, cnt, info + q0, rs, sg, ws, L, emu, probe, tol, 1, gs)) return 1;
+            if (blocked_pass(X, y, e, lsp, act, sigma_vals, Pc, N, d, S, cnt, info + q0, rs, sg, ws, L, emu, probe, tol, zero_inactive, gs)) return 1;
             if (probe_out && cudaMemcpyAsync(probe_out + q0, ws + L.probe, (size_t)Pc * 8, cudaMemcpyDeviceToDevice, gs) != cudaSuccess) { set_error("copy of the probe values failed"); return 1; }
             if (fallback_out) {
                 cudaError_t ce = probe ? cudaMemcpyAsync(fallback_out + q0, ws + L.fail, (size_t)Pc, cudaMemcpyDeviceToDevice, gs)
@@ -619,6 +635,19 @@ int gpk_prob_surface(const double* table, long long R, int ncols, int npoints, d
     return launch_prob_surface(table, R, ncols, npoints, y_out, p_out, valid_out, (cudaStream_t)stream);
 }
 
+int gpk_surface_scan(const int* valid, long long R, long long* dst_out, long long* count_out, void* stream) {
+    if (R < 0) { set_error("gpk_surface_scan: R=%lld", R); return 2; }
+    set_stream((cudaStream_t)stream);
+    return launch_surface_scan(valid, R, dst_out, count_out, (cudaStream_t)stream);
+}
+
+int gpk_surface_gather(const int* valid, const long long* dst, long long R, int npoints, const double* y, const double* p,
+                       double* y_compact, double* p_compact, long long* row_index_out, void* stream) {
+    if (npoints < 1) { set_error("gpk_surface_gather: npoints=%d", npoints); return 2; }
+    set_stream((cudaStream_t)stream);
+    return launch_surface_gather(valid, dst, R, npoints, y, p, y_compact, p_compact, row_index_out, (cudaStream_t)stream);
+}
+
 int gpk_sum_gaussians(const double* y, int n, const double* gaus, int ng, double half_dy, double* p_out,
                       void* stream) {
     set_stream((cudaStream_t)stream);
@@ -646,6 +675,7 @@ int gpk_set_groups(int groups, int min_particles_per_group) {
     if (groups < 1 || groups > MAX_GROUPS || min_particles_per_group < 1) { set_error("gpk_set_groups: groups 1..%d, at least 1 particle per group", MAX_GROUPS); return 2; }
     g_groups = groups;
     g_min_group = min_particles_per_group;
+    g_groups_explicit = true;
     return 0;
 }
 

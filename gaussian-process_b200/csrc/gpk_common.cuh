@@ -156,6 +156,9 @@ int launch_predict_finalize(const double* partial, int T, int Bp, int B, double*
 int launch_prob_surface(const double* table, long long R, int ncols, int npoints,
                         double* y_out, double* p_out, int* valid_out, cudaStream_t st);
 
+int launch_surface_scan(const int* valid, long long R, long long* dst, long long* count, cudaStream_t st);
+int launch_surface_gather(const int* valid, const long long* dst, long long R, int npoints, const double* y, const double* p,
+                          double* yc, double* pc, long long* idx, cudaStream_t st);
 int launch_sum_gaussians(const double* y, int n, const double* gaus, int ng, double half_dy, double* p_out,
                          cudaStream_t st);
 

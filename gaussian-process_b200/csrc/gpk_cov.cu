@@ -44,26 +44,29 @@ int launch_scale_points(const double* X, const double* ls, int P, int N, int Np,
 
 // rows r = (threadIdx.x >> 7), +2, ... of tile (I, .) for column j: K_ij + delta_ij e_i^2, identity in the padding.
 // PROBE: the tile's contributions to u = K v (v = probe_v, the residual probe of include/gpk.h) are formed on the way:
-// row sums sum_j K_ij v_j into s_row[warp & 3][r] (one partial per warp = 32 columns) and the column sum
-// sum_i K_ij v_i of this thread's 64 rows (returned).
+// the column sum sum_i K_ij v_i of this thread's 64 rows stays in a register (returned); the row sums sum_j K_ij v_j need
+// all 128 columns = threads of a row and go through shared memory in batches of 16 rows (s_prod, then 16 threads per row
+// add 8 columns each and finish with 4 shuffle steps) -> s_rowsum[r].  Keeping the 64 products of a thread in registers
+// for a warp butterfly instead costs 66 registers and halves the occupancy of this FP64-pipe-bound kernel (measured: 2x time).
+constexpr int CP_ROWS = 16;              // rows per batch
+constexpr int CP_PITCH = NB + 1;
 template <int D, bool PROBE>
 __device__ __forceinline__ double cov_lower_rows(const double* __restrict__ xsp, const double* __restrict__ sqp,
                                                  const double* __restrict__ e, int N, int Np, int I, int j,
                                                  const double (*s_xi)[NB], const double* s_sqi, double* __restrict__ out,
-                                                 double (*s_row)[NB], const double* s_pvi) {
+                                                 double* s_prod, double* s_rowsum, const double* s_pvi) {
     double xj[D];
 #pragma unroll
     for (int dd = 0; dd < D; ++dd) xj[dd] = xsp[(size_t)dd * Np + j];
     const double sqj = sqp[j];
     const double vj = (PROBE && j < N) ? probe_v(j) : 0.0;
-    const int lane = threadIdx.x & 31, wq = (threadIdx.x >> 5) & 3;
+    const int h = threadIdx.x >> 7, c = threadIdx.x & (NB - 1);
     double colsum = 0.0;
-    double rowv[32];
+    for (int b = 0; b < NB / CP_ROWS; ++b) {
 #pragma unroll
-    for (int half = 0; half < 2; ++half) {
-#pragma unroll
-        for (int k = 0; k < 32; ++k) {
-            const int r = (threadIdx.x >> 7) + 2 * (half * 32 + k);
+        for (int k = 0; k < CP_ROWS / 2; ++k) {
+            const int lr = h + 2 * k;
+            const int r = b * CP_ROWS + lr;
             const int i = I * NB + r;
             double v;
             if (i < N && j < N) {
@@ -77,23 +80,20 @@ __device__ __forceinline__ double cov_lower_rows(const double* __restrict__ xsp,
             }
             out[(size_t)i * Np + j] = v;
             if (PROBE) {
-                rowv[k] = v * vj;
+                s_prod[lr * CP_PITCH + c] = v * vj;
                 colsum = fma(v, s_pvi[r], colsum);
             }
         }
         if (PROBE) {
-            // 32 rows x 32 lanes (columns) -> lane l holds the warp's sum of row k = l (butterfly, 31 exchanges)
+            __syncthreads();
+            const int rr = threadIdx.x >> 4, q = threadIdx.x & 15;          // 16 threads per row of the batch
+            double a = 0.0;
 #pragma unroll
-            for (int step = 16; step >= 1; step >>= 1) {
-                const bool up = (lane & step) != 0;
+            for (int m = 0; m < NB / 16; ++m) a += s_prod[rr * CP_PITCH + q + 16 * m];
 #pragma unroll
-                for (int i2 = 0; i2 < step; ++i2) {
-                    const double send = up ? rowv[i2] : rowv[i2 + step];
-                    const double keep = up ? rowv[i2 + step] : rowv[i2];
-                    rowv[i2] = keep + __shfl_xor_sync(0xffffffffu, send, step);
-                }
-            }
-            s_row[wq][(threadIdx.x >> 7) + 2 * (half * 32 + lane)] = rowv[0];
+            for (int o = 8; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+            if (q == 0) s_rowsum[b * CP_ROWS + rr] = a;
+            __syncthreads();
         }
     }
     return colsum;
@@ -121,7 +121,8 @@ __global__ void __launch_bounds__(256) k_cov_lower(const double* __restrict__ xs
 
     __shared__ double s_xi[MAX_D][NB];
     __shared__ double s_sqi[NB];
-    __shared__ double s_row[PROBE ? 4 : 1][NB];
+    __shared__ double s_prod[PROBE ? CP_ROWS * CP_PITCH : 1];
+    __shared__ double s_rowsum[PROBE ? NB : 1];
     __shared__ double s_col[PROBE ? 2 : 1][NB];
     __shared__ double s_pvi[PROBE ? NB : 1];
     const double* xsp = xs + (size_t)p * d * Np;
@@ -143,14 +144,14 @@ __global__ void __launch_bounds__(256) k_cov_lower(const double* __restrict__ xs
     // element in issue slots); same operations in the same order for every D
     double colsum;
     switch (d) {
-        case 1: colsum = cov_lower_rows<1, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_row, s_pvi); break;
-        case 2: colsum = cov_lower_rows<2, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_row, s_pvi); break;
-        case 3: colsum = cov_lower_rows<3, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_row, s_pvi); break;
-        case 4: colsum = cov_lower_rows<4, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_row, s_pvi); break;
-        case 5: colsum = cov_lower_rows<5, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_row, s_pvi); break;
-        case 6: colsum = cov_lower_rows<6, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_row, s_pvi); break;
-        case 7: colsum = cov_lower_rows<7, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_row, s_pvi); break;
-        default: colsum = cov_lower_rows<8, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_row, s_pvi); break;
+        case 1: colsum = cov_lower_rows<1, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_prod, s_rowsum, s_pvi); break;
+        case 2: colsum = cov_lower_rows<2, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_prod, s_rowsum, s_pvi); break;
+        case 3: colsum = cov_lower_rows<3, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_prod, s_rowsum, s_pvi); break;
+        case 4: colsum = cov_lower_rows<4, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_prod, s_rowsum, s_pvi); break;
+        case 5: colsum = cov_lower_rows<5, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_prod, s_rowsum, s_pvi); break;
+        case 6: colsum = cov_lower_rows<6, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_prod, s_rowsum, s_pvi); break;
+        case 7: colsum = cov_lower_rows<7, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_prod, s_rowsum, s_pvi); break;
+        default: colsum = cov_lower_rows<8, PROBE>(xsp, sqp, e, N, Np, I, j, s_xi, s_sqi, out, s_prod, s_rowsum, s_pvi); break;
     }
     if (PROBE) {
         s_col[threadIdx.x >> 7][c] = colsum;
@@ -159,7 +160,7 @@ __global__ void __launch_bounds__(256) k_cov_lower(const double* __restrict__ xs
             const int r = threadIdx.x;
             const int T = Np / NB;
             double* slot = kv + (size_t)p * T * Np;
-            slot[(size_t)J * Np + I * NB + r] = (s_row[0][r] + s_row[1][r]) + (s_row[2][r] + s_row[3][r]);
+            slot[(size_t)J * Np + I * NB + r] = s_rowsum[r];
             if (I > J) slot[(size_t)I * Np + J * NB + r] = s_col[0][r] + s_col[1][r];
         }
     }

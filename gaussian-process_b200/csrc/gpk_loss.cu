@@ -287,6 +287,9 @@ int launch_wy(const double* mat, int Np, int N, int P, const double* y, double* 
 
 // cn_i = sum_{k>=i} W[k][i]^2,  alpha_i = sum_{k>=i} W[k][i] z_k : 32 columns per CTA, 8 warps sweep rows.
 // pt / pw (optional, per particle [Np]): the residual probe, w = W^T t, in the same pass over W.
+// One CTA per 128-column strip (= one block column: the strip starts at its diagonal block), 8 warps sweep the rows, a lane
+// owns 4 consecutive columns: every load is one full 32-byte sector per lane, 1 KB contiguous per warp and row.
+template <bool PROBE>
 __global__ void __launch_bounds__(256) k_colnorm_alpha(const double* __restrict__ mat, int Np,
                                                        const double* __restrict__ z, double* __restrict__ cn,
                                                        double* __restrict__ alpha, const double* __restrict__ pt,
@@ -294,50 +297,55 @@ __global__ void __launch_bounds__(256) k_colnorm_alpha(const double* __restrict_
                                                        const unsigned char* __restrict__ active) {
     const int p = blockIdx.y;
     if (active && !active[p]) return;
-    __shared__ double s_cn[8][32], s_al[8][32], s_pw[8][32];
+    __shared__ double s_red[8][3][NB];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int i = blockIdx.x * 32 + lane;
-    const int kstart = (blockIdx.x * 32 / NB) * NB;       // first row of the diagonal block
-    const double* M = mat + (size_t)p * Np * Np;
+    const int c0 = blockIdx.x * NB + 4 * lane;
+    const int kstart = blockIdx.x * NB;                    // first row of the diagonal block
+    const double* M = mat + (size_t)p * Np * Np + c0;
     const double* zp = z + (size_t)p * Np;
-    double a = 0.0, b = 0.0, c = 0.0;
-    if (pt == nullptr) {
-        for (int k = kstart + warp; k < Np; k += 8) {
-            const double w = M[(size_t)k * Np + i];
-            a = fma(w, w, a);
-            b = fma(w, zp[k], b);
+    const double* tp = PROBE ? pt + (size_t)p * Np : nullptr;
+    double a[4] = {0.0, 0.0, 0.0, 0.0}, b[4] = {0.0, 0.0, 0.0, 0.0}, c[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll 2
+    for (int k = kstart + warp; k < Np; k += 8) {
+        double w[4];
+        asm volatile("ld.global.nc.v4.f64 {%0, %1, %2, %3}, [%4];\n"
+                     : "=d"(w[0]), "=d"(w[1]), "=d"(w[2]), "=d"(w[3]) : "l"(M + (size_t)k * Np));
+        const double zk = zp[k];
+        const double tk = PROBE ? tp[k] : 0.0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            a[q] = fma(w[q], w[q], a[q]);
+            b[q] = fma(w[q], zk, b[q]);
+            if (PROBE) c[q] = fma(w[q], tk, c[q]);
         }
-    } else {
-        const double* tp = pt + (size_t)p * Np;
-        for (int k = kstart + warp; k < Np; k += 8) {
-            const double w = M[(size_t)k * Np + i];
-            a = fma(w, w, a);
-            b = fma(w, zp[k], b);
-            c = fma(w, tp[k], c);
-        }
-        s_pw[warp][lane] = c;
     }
-    s_cn[warp][lane] = a;
-    s_al[warp][lane] = b;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        s_red[warp][0][4 * lane + q] = a[q];
+        s_red[warp][1][4 * lane + q] = b[q];
+        if (PROBE) s_red[warp][2][4 * lane + q] = c[q];
+    }
     __syncthreads();
-    if (warp == 0) {
-        double ta = 0.0, tb = 0.0;
+    if (threadIdx.x < NB) {
+        const int i = threadIdx.x;
+        double ta = 0.0, tb = 0.0, tc = 0.0;
 #pragma unroll
-        for (int w = 0; w < 8; ++w) { ta += s_cn[w][lane]; tb += s_al[w][lane]; }
-        cn[(size_t)p * Np + i] = ta;
-        alpha[(size_t)p * Np + i] = tb;
-        if (pt != nullptr) {
-            double tc = 0.0;
-#pragma unroll
-            for (int w = 0; w < 8; ++w) tc += s_pw[w][lane];
-            pw[(size_t)p * Np + i] = tc;
+        for (int w = 0; w < 8; ++w) {
+            ta += s_red[w][0][i];
+            tb += s_red[w][1][i];
+            if (PROBE) tc += s_red[w][2][i];
         }
+        const size_t o = (size_t)p * Np + blockIdx.x * NB + i;
+        cn[o] = ta;
+        alpha[o] = tb;
+        if (PROBE) pw[o] = tc;
     }
 }
 
 int launch_colnorm_alpha(const double* mat, int Np, int P, const double* z, double* cn, double* alpha,
                          const double* pt, double* pw, const unsigned char* active, cudaStream_t st) {
-    k_colnorm_alpha<<<dim3(Np / 32, P), 256, 0, st>>>(mat, Np, z, cn, alpha, pt, pw, active);
+    if (pt) k_colnorm_alpha<true><<<dim3(Np / NB, P), 256, 0, st>>>(mat, Np, z, cn, alpha, pt, pw, active);
+    else k_colnorm_alpha<false><<<dim3(Np / NB, P), 256, 0, st>>>(mat, Np, z, cn, alpha, pt, pw, active);
     return check_launch("k_colnorm_alpha");
 }
 

@@ -114,6 +114,76 @@ int launch_sum_gaussians(const double* y, int n, const double* gaus, int ng, dou
     return check_launch("k_sum_gaussians");
 }
 
+// ---- compaction of the emitting rows (calc_prob_surf.py:71 drops rows; the output is compacted) ----------------
+// dst[r] = number of emitting rows before r (exclusive prefix sum of valid), count[0] = their total.  One CTA: a pass of the
+// surface reduction holds at most a few 10^5 rows.
+__global__ void __launch_bounds__(1024) k_surface_scan(const int* __restrict__ valid, long long R, long long* __restrict__ dst,
+                                                       long long* __restrict__ count) {
+    __shared__ long long s_warp[32];
+    __shared__ long long s_base;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_base = 0;
+    __syncthreads();
+    for (long long r0 = 0; r0 < R; r0 += 1024) {
+        const long long r = r0 + tid;
+        const int v = (r < R && valid[r]) ? 1 : 0;
+        int incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            long long w = s_warp[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const long long t = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += t;
+            }
+            s_warp[lane] = w;                 // inclusive over warps
+        }
+        __syncthreads();
+        const long long before = s_base + (warp ? s_warp[warp - 1] : 0) + (incl - v);
+        if (r < R) dst[r] = before;
+        __syncthreads();
+        if (tid == 0) s_base += s_warp[31];
+        __syncthreads();
+    }
+    if (tid == 0) count[0] = s_base;
+}
+
+// emitting row r -> row dst[r] of the compacted outputs; one warp per row
+__global__ void __launch_bounds__(256) k_surface_gather(const int* __restrict__ valid, const long long* __restrict__ dst,
+                                                        long long R, int npoints, const double* __restrict__ y,
+                                                        const double* __restrict__ p, double* __restrict__ yc,
+                                                        double* __restrict__ pc, long long* __restrict__ idx) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const long long r = (long long)blockIdx.x * 8 + warp;
+    if (r >= R || !valid[r]) return;
+    const long long q = dst[r];
+    for (int i = lane; i < npoints; i += 32) {
+        yc[q * npoints + i] = y[r * npoints + i];
+        pc[q * npoints + i] = p[r * npoints + i];
+    }
+    if (lane == 0) idx[q] = r;
+}
+
+int launch_surface_scan(const int* valid, long long R, long long* dst, long long* count, cudaStream_t st) {
+    k_surface_scan<<<1, 1024, 0, st>>>(valid, R, dst, count);
+    return check_launch("k_surface_scan");
+}
+
+int launch_surface_gather(const int* valid, const long long* dst, long long R, int npoints, const double* y, const double* p,
+                          double* yc, double* pc, long long* idx, cudaStream_t st) {
+    if (R <= 0) return 0;
+    const long long blocks = (R + 7) / 8;
+    if (blocks > 0x7fffffffLL) { set_error("surface_gather: too many rows"); return 2; }
+    k_surface_gather<<<(unsigned)blocks, 256, 0, st>>>(valid, dst, R, npoints, y, p, yc, pc, idx);
+    return check_launch("k_surface_gather");
+}
+
 int launch_prob_surface(const double* table, long long R, int ncols, int npoints, double* y_out, double* p_out,
                         int* valid_out, cudaStream_t st) {
     if (ncols > SURF_MAX_COLS || ncols < 0) {

@@ -301,11 +301,14 @@ class LossContext:
     def _form(self):
         return _FORMS[_loss_form] if self.n <= NB else 0
 
-    def _launch(self, positions_dev, active_dev, p, counts, info, resid, sd, probe, fallback, ws, stream=None):
+    def _launch(self, positions_dev, active_dev, p, counts, info, resid, sd, probe, fallback, ws, stream=None, mode=None,
+                flags=None, tol=None):
+        mode = self.mode if mode is None else mode
         st = self.lib.gpk_loss_batched(
             self.x.data_ptr(), self.y.data_ptr(), self.e.data_ptr(), positions_dev.data_ptr(),
             active_dev.data_ptr() if active_dev is not None else None, self.sig.data_ptr(), p, self.n, self.d,
-            self.s, self.mode, self._form(), _check_tol if self.mode != 0 else 0.0,
+            self.s, mode, self._form() if flags is None else flags,
+            (_check_tol if mode != 0 else 0.0) if tol is None else tol,
             counts.data_ptr(), info.data_ptr(), resid.data_ptr() if resid is not None else None,
             sd.data_ptr() if sd is not None else None, probe.data_ptr() if probe is not None else None,
             fallback.data_ptr(), ws.data_ptr(), ws.numel(),
@@ -343,17 +346,21 @@ class LossContext:
                   "act": torch.ones(p, dtype=torch.uint8, device=dev),
                   "counts": torch.empty((p, self.s), dtype=torch.int32, device=dev),
                   "info": torch.empty(p, dtype=torch.int32, device=dev),
-                  "fb": torch.zeros(p, dtype=torch.uint8, device=dev)}
+                  "fb": torch.zeros(p, dtype=torch.uint8, device=dev),
+                  "fb2": torch.zeros(p, dtype=torch.uint8, device=dev)}
             st["pos"].copy_(positions_dev)
             cur = torch.cuda.current_stream()
             side = torch.cuda.Stream(device=dev)
             side.wait_stream(cur)
+            # the a-posteriori check runs inside the graph in its flags-only form (negative tolerance): the ~6 T launches of
+            # an in-call second pass, empty when nothing failed, would be a visible share of these launch-bound sizes
+            gtol = -_check_tol if self.mode != 0 else 0.0
             with torch.cuda.stream(side):                  # warm-up outside the capture (attribute calls, streams)
-                self._launch(st["pos"], st["act"], p, st["counts"], st["info"], None, None, None, st["fb"], ws)
+                self._launch(st["pos"], st["act"], p, st["counts"], st["info"], None, None, None, st["fb"], ws, tol=gtol)
             cur.wait_stream(side)
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
-                self._launch(st["pos"], st["act"], p, st["counts"], st["info"], None, None, None, st["fb"], ws)
+                self._launch(st["pos"], st["act"], p, st["counts"], st["info"], None, None, None, st["fb"], ws, tol=gtol)
             self._graphs.clear()                           # one live graph per context (its workspace is shared)
             g = self._graphs[key] = (graph, st)
         graph, st = g
@@ -363,6 +370,10 @@ class LossContext:
         else:
             st["act"].fill_(1)
         graph.replay()
+        if self.mode != 0 and _check_tol > 0 and bool(st["fb"].any().item()):
+            # checked mixed precision: the failed particles again, by the native FP64 kernels, in place
+            self._launch(st["pos"], st["fb"], p, st["counts"], st["info"], None, None, None, st["fb2"], ws, mode=0,
+                         flags=2, tol=0.0)
         self.last_fallback = st["fb"]
         self.last_probe = None
         return st["counts"], st["info"]
@@ -560,15 +571,26 @@ def prob_surface_passes(table, points=100, rows_per_pass=None):
                                       streams[slot].cuda_stream)
             _lib.check(st, "gpk_prob_surface")
             # rows that do not emit are rare: ship everything when all rows are valid, else compact on the device first
-            keep = torch.nonzero(valid, as_tuple=False).reshape(-1)
-            k = keep.numel()                                              # (synchronises this stream only)
+            # (exclusive prefix sum of the valid flags + row gather, libgpk kernels)
+            dst = torch.empty(rc, dtype=torch.int64, device=dev)
+            cnt = torch.empty(1, dtype=torch.int64, device=dev)
+            st = lib.gpk_surface_scan(valid.data_ptr(), rc, dst.data_ptr(), cnt.data_ptr(), streams[slot].cuda_stream)
+            _lib.check(st, "gpk_surface_scan")
+            k = int(cnt.item())                                           # (synchronises this stream only)
             if k == rc:
                 ys.copy_(y, non_blocking=True)
                 ps.copy_(p, non_blocking=True)
+                keep = torch.arange(rc, dtype=torch.int64, device=dev)
             else:
-                ys[:k].copy_(y.index_select(0, keep), non_blocking=True)
-                ps[:k].copy_(p.index_select(0, keep), non_blocking=True)
-            ids[:k].copy_(keep, non_blocking=True)
+                yc = torch.empty((max(k, 1), points), dtype=torch.float64, device=dev)
+                pc = torch.empty((max(k, 1), points), dtype=torch.float64, device=dev)
+                keep = torch.empty(max(k, 1), dtype=torch.int64, device=dev)
+                st = lib.gpk_surface_gather(valid.data_ptr(), dst.data_ptr(), rc, points, y.data_ptr(), p.data_ptr(),
+                                            yc.data_ptr(), pc.data_ptr(), keep.data_ptr(), streams[slot].cuda_stream)
+                _lib.check(st, "gpk_surface_gather")
+                ys[:k].copy_(yc[:k], non_blocking=True)
+                ps[:k].copy_(pc[:k], non_blocking=True)
+            ids[:k].copy_(keep[:k], non_blocking=True)
             done = torch.cuda.Event()
             done.record(streams[slot])
         pending.append((k, ys, ps, ids, r0, done))

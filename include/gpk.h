@@ -49,12 +49,15 @@ extern "C" {
 #define GPK_PREC_EMU21 3
 #define GPK_PREC_EMU15 4
 
-/* `form` argument of gpk_loss_batched: which algebraic form of the self-prediction the loss uses.
- *   GPK_FORM_REDUCED    mu - y = -e^2 alpha, var = e^2 - e^4 (K^-1)_ii (triangular inverse, 2/3 N^3 flop; every N);
- *   GPK_FORM_REFERENCE  the reference's own formulae, GP_func.py:36-40: mu = K_s^T alpha, v = L^-1 K_s, var = 1 - sum v^2
- *                       (4/3 N^3 flop, with the reference's cancellations); one-CTA path only (N <= GPK_SMALL_N_MAX). */
-#define GPK_FORM_REDUCED 0
-#define GPK_FORM_REFERENCE 1
+/* `flags` argument of gpk_loss_batched (bit mask).
+ *   GPK_FLAG_REFERENCE_FORM  which algebraic form of the self-prediction the loss uses.  Clear: the reduced form,
+ *                       mu - y = -e^2 alpha, var = e^2 - e^4 (K^-1)_ii (triangular inverse, 2/3 N^3 flop; every N).  Set:
+ *                       the reference's own formulae, GP_func.py:36-40: mu = K_s^T alpha, v = L^-1 K_s, var = 1 - sum v^2
+ *                       (4/3 N^3 flop, with the reference's cancellations); one-CTA path only (N <= GPK_SMALL_N_MAX).
+ *   GPK_FLAG_KEEP_INACTIVE   particles with active[p] == 0 keep their previous counts / info / resid / sd instead of being
+ *                       zeroed: re-evaluation of a subset of a swarm in place (blocked path, active != NULL). */
+#define GPK_FLAG_REFERENCE_FORM 1
+#define GPK_FLAG_KEEP_INACTIVE 2
 
 GPK_API int gpk_version(void);
 GPK_API const char* gpk_last_error_string(void);            /* HOST string, valid until the next failing call */
@@ -98,11 +101,15 @@ GPK_API int gpk_selfpredict_counts(const double* L, const double* alpha, const d
  *     (three N^2 matrix-vector products fused into passes that exist anyway).  rho_p -> probe_out[p] (optional).  With an
  *     emulated `precision` and check_tol > 0, every particle with rho_p > check_tol (or NaN) is evaluated again by the
  *     native FP64 kernels inside the same call and fallback_out[p] (optional, [P] bytes) is set to 1.  No host
- *     synchronisation: the call stays asynchronous and can be captured into a CUDA graph. */
+ *     synchronisation: the call stays asynchronous and can be captured into a CUDA graph (when nothing failed, the kernels
+ *     of the second pass exit at their first instruction).  check_tol < 0: the probe runs with tolerance -check_tol and
+ *     fallback_out is set, but nothing is re-evaluated: the caller reads the flags and calls again with GPK_PREC_FP64,
+ *     active = the flags and GPK_FLAG_KEEP_INACTIVE (what the Python mirror does where the second pass' ~6 T empty
+ *     launches would show: CUDA-graph replay of launch-bound sizes). */
 GPK_API size_t gpk_loss_workspace_bytes(int P, int N, int d, int precision);
 GPK_API int gpk_loss_batched(const double* X, const double* y, const double* e, const double* ls,
                      const unsigned char* active, const double* sigma_vals, int P, int N, int d, int S,
-                     int precision, int form, double check_tol, int* counts_out, int* info, double* resid_out,
+                     int precision, int flags, double check_tol, int* counts_out, int* info, double* resid_out,
                      double* sig_out, double* probe_out, unsigned char* fallback_out, void* workspace,
                      size_t workspace_bytes, void* stream);
 
@@ -139,6 +146,15 @@ GPK_API int gpk_predict_emu(const void* state, const double* alpha, const double
 GPK_API int gpk_prob_surface(const double* table, long long R, int ncols, int npoints, double* y_out, double* p_out,
                      int* valid_out, void* stream);
 
+/* (d) compaction of the emitting rows (the reference appends output only for rows that pass calc_prob_surf.py:71):
+ *     gpk_surface_scan: dst_out[r] = number of emitting rows before r ([R] int64), count_out[0] = their total (device int64);
+ *     gpk_surface_gather: copies the y / p rows of the emitting rows to rows dst[r] of y_compact / p_compact and writes
+ *     row_index_out[dst[r]] = r.  The caller reads count_out between the two (it sizes the device-to-host copy) and skips
+ *     the gather when every row emits. */
+GPK_API int gpk_surface_scan(const int* valid, long long R, long long* dst_out, long long* count_out, void* stream);
+GPK_API int gpk_surface_gather(const int* valid, const long long* dst, long long R, int npoints, const double* y,
+                               const double* p, double* y_compact, double* p_compact, long long* row_index_out, void* stream);
+
 /* (d) sum_gaussians(temp_y, temp_gaus), calc_prob_surf.py:15-30, at n caller-supplied points y; gaus holds
  *     ng interleaved (mean, std) values; half_dy = (|max(y)-min(y)| / n) / 2 as formed at :23,:26-27. */
 GPK_API int gpk_sum_gaussians(const double* y, int n, const double* gaus, int ng, double half_dy, double* p_out,
@@ -146,8 +162,8 @@ GPK_API int gpk_sum_gaussians(const double* y, int n, const double* gaus, int ng
 
 /* Scheduling knob, process-wide, results do not depend on it: gpk_loss_batched splits a swarm on the blocked path into at
  * most `groups` particle groups on concurrent streams (default 4, 1..8), each of at least `min_particles_per_group`
- * particles (default 32: smaller groups leave the persistent digit-GEMM launches of late block columns with fewer tiles
- * than SMs). */
+ * particles (default 16: smaller groups leave the persistent digit-GEMM launches of late block columns with fewer tiles
+ * than SMs); swarms of fewer than 256 particles use at most 2 groups. */
 GPK_API int gpk_set_groups(int groups, int min_particles_per_group);
 
 /* Emulated-FP64 primitives (used by the blocked path in the GPK_PREC_EMU* modes, exposed for tests and measurement).

@@ -224,6 +224,22 @@ def gen_large(ref):
     np.savez_compressed(os.path.join(OUT, "gp_cases_large.npz"), **g)
 
 
+def gen_adv(ref):
+    """Milder adversarial cases for the emulated arithmetic (same generator as adv_n1024 in gen_large): e log-uniform over
+    1e-3 .. 1 and 1e-4 .. 1 with isolated points carrying the smallest e: cond(K) ~ 1e9 and ~ 1e11, where FP64 still delivers
+    digits and the a-priori scales of the digit split are already loose by 10 and 13 bits."""
+    d = {}
+    for name, e_lo in (("adv3_n1024", 1e-3), ("adv4_n1024", 1e-4)):
+        x, y, e = orc.adversarial_problem(1024, 2, 0, e_lo=e_lo)
+        lower, upper = orc.pso_bounds(x)
+        pos = orc.center_lhs(np.column_stack((lower, upper)), 4, np.random.RandomState(1))
+        c = loss_case(ref, x, y, e, pos, lower, upper)
+        for k, v in c.items():
+            d[f"{name}__{k}"] = v
+        print(name, "min margin", c["margin"].min(), "loss", c["loss"], flush=True)
+    np.savez_compressed(os.path.join(OUT, "loss_cases_adv.npz"), **d)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ref = ref_shim.load()

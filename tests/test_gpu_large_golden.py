@@ -43,15 +43,17 @@ def test_loss_golden_c3_n4096(eng, precision):
     counts, info, resid, sd, probe = ctx.counts(c["pos"], active=~oob, want_detail=True, want_probe=True)
     act = ~oob
     assert not info.any()
-    np.testing.assert_allclose(resid[act] + y, c["resid"][act] + y, rtol=1e-9, atol=1e-12)      # predictive mean
-    np.testing.assert_allclose(resid[act], c["resid"][act], rtol=1e-9, atol=1e-9 * np.abs(c["resid"][act]).max())
+    # 1e-9 relative to the largest entry of each vector: the reference forms mu = K_s^T alpha by summing 4096 terms of size
+    # ~1, so where mu (or mu - y) passes through zero its own last digits are absolute, not relative
+    np.testing.assert_allclose(resid[act] + y, c["resid"][act] + y, rtol=0, atol=1e-9 * np.abs(y).max())       # predictive mean
+    np.testing.assert_allclose(resid[act], c["resid"][act], rtol=0, atol=1e-9 * np.abs(c["resid"][act]).max())
     np.testing.assert_allclose(sd[act], c["sd"][act], rtol=1e-9)
     assert c["margin"][act].min() > 1e-8                       # no pull of the reference sits on a rounding tie
     np.testing.assert_array_equal(counts[act], c["counts"][act])                                # integer work: exact
     assert not counts[oob].any()
     loss = pso.finish_losses(counts, 4096, c["pos"], s, ex, c["lower"], c["upper"], oob)
     np.testing.assert_allclose(loss, c["loss"], rtol=1e-12)
-    assert ctx.fallbacks == 0 and probe[act].max() < 1e-11, probe
+    assert ctx.fallbacks == 0 and probe[act].max() < 0.5 * engine.get_check_tol(), probe
     # and through the public call, as part of the whole 256-particle bench swarm (position in the swarm does not matter)
     pos_all, lo, hi = orc.synthetic_particles(x, 256, 0)
     idx = c["swarm_index"][:4]
@@ -64,9 +66,10 @@ def test_gp_golden_large(eng, precision):
     """GP() of the reference at N=8192 (C4 size) and N=4096 (C3 size): mean and sd at 1e-9."""
     engine, _ = eng
     g = load_golden("gp_cases_large.npz")
+    digest_c3 = case(load_golden("loss_cases_large.npz"), "c3_n4096")["xye_sum"]
     for name, n, d, seed in (("c4_n8192", 8192, 2, 3), ("c3_n4096", 4096, 3, 0)):
         c = case(g, name)
-        x, y, e = _regenerated(n, d, seed, c["xye_sum"])
+        x, y, e = _regenerated(n, d, seed, c["xye_sum"] if "xye_sum" in c else digest_c3)
         fit = engine.GPFit(x, y, e, c["ls"])
         mu, sd = fit.predict(c["grid"].T)
         np.testing.assert_allclose(mu, c["mu"], rtol=1e-9, atol=1e-9 * np.abs(c["mu"]).max(), err_msg=name)
@@ -74,44 +77,78 @@ def test_gp_golden_large(eng, precision):
         assert not fit.fell_back and fit.probe < 1e-10, (name, fit.probe)
 
 
-def test_adversarial_uncertainties_trigger_the_fallback(eng):
-    """e log-uniform over 1e-6 .. 1 with isolated points carrying the smallest e: cond(K) ~ 1e12.  The a-priori scales of the
-    emulated arithmetic are loose here; the a-posteriori probe must notice, every particle must be re-evaluated by the native
-    FP64 kernels inside the same call (bit-identical to the fp64 mode), and the result must be as close to an 80-bit
-    evaluation as the reference's own LAPACK path is (a 1e-9 agreement between two FP64 evaluations does not exist at this
-    conditioning: the tolerance is the reference's own distance from the truth)."""
-    engine, pso = eng
-    c = case(load_golden("loss_cases_large.npz"), "adv_n1024")
-    x, y, e, pos = c["x"], c["y"], c["e"], c["pos"]
-    s, ex = orc.sigma_grid()
+def _three_ways(engine, x, y, e, pos, s):
+    """(counts, info, resid, sd, probe, fallbacks) in native FP64, checked emulation and unchecked emulation."""
     out = {}
-    for mode, tol in (("fp64", 1e-10), ("emu", 1e-10), ("emu", 0.0)):
+    for key, mode, tol in (("fp64", "fp64", 1e-10), ("checked", "emu", 1e-10), ("raw", "emu", 0.0)):
         engine.set_precision(mode)
         engine.set_check_tol(tol)
         try:
             ctx = engine.LossContext(x, y, e, s)
-            out[(mode, tol)] = ctx.counts(pos, want_detail=True, want_probe=True) + (ctx.fallbacks,)
+            out[key] = ctx.counts(pos, want_detail=True, want_probe=True) + (ctx.fallbacks,)
         finally:
             engine.set_precision("auto")
             engine.set_check_tol(1e-10)
-    c64, i64, r64, sd64, p64, fb64 = out[("fp64", 1e-10)]
-    cck, ick, rck, sdck, pck, fbck = out[("emu", 1e-10)]
+    return out
+
+
+def test_adversarial_uncertainties_trigger_the_fallback(eng):
+    """e log-uniform over 1e-6 .. 1 with isolated points carrying the smallest e: cond_2(K) = 8.8e14, so cond * 2^-53 ~ 0.1
+    and NO FP64 evaluation has guaranteed digits -- the reference's own LAPACK path is 1e-3 away from an 80-bit evaluation.
+    What must hold here: the a-posteriori probe notices (it is O(1), not O(1e-11)), every particle is re-evaluated by the
+    native FP64 kernels inside the same call, bit-identical to the fp64 mode, and the result is wrong by no more than the
+    conditioning allows (cond * eps), like the reference's."""
+    engine, pso = eng
+    c = case(load_golden("loss_cases_large.npz"), "adv_n1024")
+    x, y, e, pos = c["x"], c["y"], c["e"], c["pos"]
+    s, ex = orc.sigma_grid()
+    out = _three_ways(engine, x, y, e, pos, s)
+    c64, i64, r64, sd64, p64, fb64 = out["fp64"]
+    cck, ick, rck, sdck, pck, fbck = out["checked"]
     assert not i64.any() and not ick.any()
     assert fb64 == 0                                            # nothing to fall back to in the native mode
     assert fbck == len(pos) and np.all(pck > 1e-10), pck       # every particle failed the probe ...
     np.testing.assert_array_equal(cck, c64)                     # ... and was recomputed by the native kernels, in the same call
     np.testing.assert_array_equal(rck, r64)
     np.testing.assert_array_equal(sdck, sd64)
-    # which side is off?  80-bit truth for two particles
+    cond_eps = 8.8e14 * 2.0 ** -53
     for k in (0, 3):
         r_t, sd_t = truth80.selfpredict_ld(x, y, e, pos[k])
         ref_r, ref_sd = truth80.rel_err(c["resid"][k], r_t), truth80.rel_err_pointwise(c["sd"][k], sd_t)
         got_r, got_sd = truth80.rel_err(rck[k], r_t), truth80.rel_err_pointwise(sdck[k], sd_t)
-        raw = out[("emu", 0.0)]
-        raw_r, raw_sd = truth80.rel_err(raw[2][k], r_t), truth80.rel_err_pointwise(raw[3][k], sd_t)
-        print(f"adversarial particle {k}: error vs 80-bit truth  reference {ref_r:.2e} / {ref_sd:.2e}   checked "
+        raw_r, raw_sd = truth80.rel_err(out["raw"][2][k], r_t), truth80.rel_err_pointwise(out["raw"][3][k], sd_t)
+        print(f"adversarial 1e-6 particle {k}: error vs 80-bit truth  reference {ref_r:.2e} / {ref_sd:.2e}   checked "
               f"{got_r:.2e} / {got_sd:.2e}   unchecked emulation {raw_r:.2e} / {raw_sd:.2e}   probe {pck[k]:.2e}")
+        assert got_r <= cond_eps and got_sd <= cond_eps and ref_r <= cond_eps and ref_sd <= cond_eps
+
+
+@pytest.mark.parametrize("name,cond", [("adv3_n1024", 9.7e8), ("adv4_n1024", 9.4e10)])
+def test_adversarial_milder_cases_meet_the_reference(eng, name, cond):
+    """The same generator with e >= 1e-3 (cond 1e9) and e >= 1e-4 (cond 1e11): FP64 still delivers digits here, the a-priori
+    scales of the digit split are loose by 10 / 13 bits.  Whatever the check decides (pass or FP64 fallback), what comes back
+    must be within 1e-9 of the 80-bit evaluation or as close to it as the reference itself (factor 4), and the counts must
+    equal the reference's wherever no pull of the reference sits within the reference's own error of a threshold."""
+    engine, pso = eng
+    c = case(load_golden("loss_cases_adv.npz"), name)
+    x, y, e, pos = c["x"], c["y"], c["e"], c["pos"]
+    s, ex = orc.sigma_grid()
+    out = _three_ways(engine, x, y, e, pos, s)
+    cck, ick, rck, sdck, pck, fbck = out["checked"]
+    assert not ick.any()
+    for k in range(len(pos)):
+        r_t, sd_t = truth80.selfpredict_ld(x, y, e, pos[k])
+        ref_r, ref_sd = truth80.rel_err(c["resid"][k], r_t), truth80.rel_err_pointwise(c["sd"][k], sd_t)
+        got_r, got_sd = truth80.rel_err(rck[k], r_t), truth80.rel_err_pointwise(sdck[k], sd_t)
+        raw_r, raw_sd = truth80.rel_err(out["raw"][2][k], r_t), truth80.rel_err_pointwise(out["raw"][3][k], sd_t)
+        n64_r, n64_sd = truth80.rel_err(out["fp64"][2][k], r_t), truth80.rel_err_pointwise(out["fp64"][3][k], sd_t)
+        fell = bool(pck[k] > 1e-10)
+        print(f"{name} particle {k}: error vs 80-bit truth  reference {ref_r:.2e} / {ref_sd:.2e}   checked {got_r:.2e} / "
+              f"{got_sd:.2e}   native {n64_r:.2e} / {n64_sd:.2e}   unchecked emulation {raw_r:.2e} / {raw_sd:.2e}   probe "
+              f"{pck[k]:.2e} ({'fallback' if fell else 'pass'})   cond*eps {cond * 2.0 ** -53:.1e}")
         assert got_r <= max(1e-9, 4 * ref_r) and got_sd <= max(1e-9, 4 * ref_sd)
+        if c["margin"][k] > 4 * max(ref_r, ref_sd, got_r, got_sd, 1e-9):
+            np.testing.assert_array_equal(cck[k], c["counts"][k])
+    assert fbck == int(np.sum(pck > 1e-10))
 
 
 @pytest.mark.parametrize("mode", ["emu28", "emu21", "emu15"])
@@ -140,6 +177,20 @@ def test_reduced_digit_modes_are_checked(eng, mode):
         np.testing.assert_allclose(r[ok], r64[ok], rtol=0, atol=1e-9 * np.abs(r64).max())
         np.testing.assert_allclose(sd[ok], sd64[ok], rtol=1e-9)
     print(f"{mode}: probe {probe.min():.2e} .. {probe.max():.2e}, fallbacks {int(fb.sum())}/{len(pos)}")
+
+
+def test_surface_many_experiments(eng):
+    """More than 64 experiments per row (the reference handles any number): 100 and 700 experiments."""
+    engine, _ = eng
+    for n_exp, rows in ((100, 40), (700, 12)):
+        t = orc.synthetic_surface_table(rows, n_exp, seed=n_exp, p_gap=0.4)
+        idx, yv, p = engine.prob_surface(t)
+        i_r, y_r, p_r = orc.prob_surface_rows(t)
+        np.testing.assert_array_equal(idx, i_r)
+        np.testing.assert_array_equal(yv, y_r)
+        np.testing.assert_allclose(p, p_r, rtol=1e-9, atol=1e-15)
+    with pytest.raises(Exception, match="experiments"):
+        engine.prob_surface(np.zeros((2, 2 * 1600)))
 
 
 def test_unsorted_sigma_grid(eng):
