@@ -681,13 +681,15 @@ def run_ours(args):
     if world == 1 and not args.no_aux:
         lib = _lib.load()
         slices = {}
-        for pp in (128, 64, 32):
+        for pp in (256, 128, 64, 32):
+            if pp > P:
+                continue
             row = {}
             for G in (1, 2, 4):
                 lib.gpk_set_groups(G, 1)
                 ms, _o = timed_steps(torch, lambda: ctx.counts_device(dpos[:pp], dact[:pp], pp), 3, 1, barrier)
                 row[f"groups_{G}"] = round(pp * 3 / (ms * 1e-3), 1)
-            lib.gpk_set_groups(4, 32)
+            lib.gpk_set_groups(0, 0)                                   # the built-in rule
             ms, _o = timed_steps(torch, lambda: ctx.counts_device(dpos[:pp], dact[:pp], pp), 3, 1, barrier)
             row["default"] = round(pp * 3 / (ms * 1e-3), 1)
             slices[f"particles_{pp}"] = row

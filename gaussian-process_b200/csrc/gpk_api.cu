@@ -672,6 +672,10 @@ int gpk_oz_gemm_tn(const void* A, const void* B, int M, int N, int K, const doub
 }
 
 int gpk_set_groups(int groups, int min_particles_per_group) {
+    if (groups == 0 && min_particles_per_group == 0) {        // back to the built-in rule
+        g_groups = 4; g_min_group = 16; g_groups_explicit = false;
+        return 0;
+    }
     if (groups < 1 || groups > MAX_GROUPS || min_particles_per_group < 1) { set_error("gpk_set_groups: groups 1..%d, at least 1 particle per group", MAX_GROUPS); return 2; }
     g_groups = groups;
     g_min_group = min_particles_per_group;

@@ -37,6 +37,25 @@ constexpr size_t CI_SMEM_BYTES = (size_t)NB * CI_LD * sizeof(double) + (size_t)(
 // thread tracks the pivots of its own 8 tile columns, pv[c] = A(c,c) - sum_{m<j} v_m[c]^2, with the very FMAs the
 // diagonal tile applies to E(c,c) (same operands, same order: bit-identical), so the owners of column j + 1 start its
 // square root and reciprocal right after the step-j loads, ahead of their 64 update FMAs.
+// root and reciprocal root of a pivot.  FAST = false: the correctly rounded sqrt() and 1.0 / x of the reference's LAPACK path
+// (two dependent software sequences, ~530 cycles: 36 of the 106 us of a 128-column block, profiles/r01 knock-out timing).
+// FAST = true: one reciprocal-square-root sequence (rsqrt, <= 1 ulp) and one Newton correction each for the root and its
+// reciprocal (results within 1 ulp of the correctly rounded ones, ~3x shorter dependency chain); used by the diagonal blocks
+// of the blocked path, not by the one-CTA loss whose seeded trajectories are pinned bit for bit.
+template <bool FAST>
+__device__ __forceinline__ void pivot_root(double piv, double& s, double& inv) {
+    if (FAST) {
+        const double r = rsqrt(piv);
+        const double s0 = piv * r;
+        s = fma(fma(-s0, s0, piv), 0.5 * r, s0);
+        inv = fma(fma(-s, r, 1.0), r, r);
+    } else {
+        s = __dsqrt_rn(piv);
+        inv = __drcp_rn(s);
+    }
+}
+
+template <bool FAST = false>
 __device__ __forceinline__ int chol_inv_regs(double (&E)[8][8], int n, double* work, double* xd) {
     double* dgs = work + 6 * NB;             // initial diagonal
     double* piv = work + 7 * NB;             // pivot of step j at piv[j & 1] (for the positivity check of all threads)
@@ -54,7 +73,7 @@ __device__ __forceinline__ int chol_inv_regs(double (&E)[8][8], int n, double* w
     for (int k = 0; k < 8; ++k) pv[k] = dgs[C0 + k];
     // square root and reciprocal of the pivot of the column this thread scales next (valid in the owners of that column)
     double s_next = 0.0, inv_next = 0.0;
-    if (tc == 0) { s_next = __dsqrt_rn(pv[0]); inv_next = __drcp_rn(s_next); }
+    if (tc == 0) pivot_root<FAST>(pv[0], s_next, inv_next);
     // steps are taken 8 at a time so that the column inside the owning tile (jj) is a compile-time index:
     // the register tile must never be indexed dynamically (it would be demoted to local memory)
     for (int jb = 0; jb * 8 < n; ++jb) {
@@ -104,8 +123,7 @@ __device__ __forceinline__ int chol_inv_regs(double (&E)[8][8], int n, double* w
                         s_next = dn;
                         inv_next = 0.5;
 #else
-                        s_next = __dsqrt_rn(dn);
-                        inv_next = __drcp_rn(s_next);
+                        pivot_root<FAST>(dn, s_next, inv_next);
 #endif
                     }
                     // tiles above the diagonal whose rows are all > j have not started
@@ -148,6 +166,134 @@ __device__ __forceinline__ void chol_inv_dump(const double (&E)[8][8], const dou
         }
     }
     if (tid < NB) Lm[tid * CI_LD + tid + 1] = xd[tid];
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Blocked form of the same factorisation for a full 128 x 128 block (the diagonal-block kernel of the blocked path).
+//
+// chol_inv_regs pays one block barrier and one square root -> reciprocal -> scaling chain per column: 128 x ~0.8 us.  Here
+// the columns are taken in panels of CB = 8: the panel (128 rows x 8 columns: L part below the diagonal, X part above) is
+// handed to ONE warp, which runs the 8 column steps on registers with shuffles only (no block barrier inside the serial
+// chain), publishes the 8 scaled columns, and all 256 threads then apply them to their 8 x 8 register tiles as 8 rank-1
+// updates in a row.  2 block barriers per panel = 32 per block instead of 128.
+//
+// Every element still receives exactly the FMAs of chol_inv_regs, with the same operands, in the same order (column k
+// ascending; a masked term is skipped instead of adding an exact zero), and the pivots' square roots and reciprocals are the
+// same correctly rounded operations: the results are bit-identical to chol_inv_regs.
+constexpr int CB = 8;                        // panel width
+constexpr int CB_PITCH = CB + 1;             // row pitch of the panel staging (odd: the lanes of the panel warp own rows l + 32 q)
+// doubles of shared scratch: two panel staging buffers, published columns (row operands, masked row operands, column
+// operands in [k][c % 8][c / 8] order), the status word
+constexpr int CBK_PN = NB * CB_PITCH;
+constexpr int CBK_WORK = 2 * CBK_PN + 3 * NB * CB + 8;
+
+// the panel warp: lane l owns rows l, l + 32, l + 64, l + 96; Q = (first panel column) / 32 = register index of the rows
+// ps .. ps + 7 that the pivots and the column operands come from
+template <int Q>
+__device__ __forceinline__ int chol_panel_warp(double* __restrict__ pn, int ps, double* __restrict__ vr,
+                                               double* __restrict__ vup, double* __restrict__ vc, double* __restrict__ xd) {
+    const int l = threadIdx.x & 31;
+    const int src0 = ps & 31;
+    double P[4][CB], T[4];
+    int bad = 0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int cc = 0; cc < CB; ++cc) P[q][cc] = pn[(l + 32 * q) * CB_PITCH + cc];
+#pragma unroll
+    for (int jj = 0; jj < CB; ++jj) {
+        const int j = ps + jj;
+        const double piv = __shfl_sync(0xffffffffu, P[Q][jj], src0 + jj);
+        if (!(piv > 0.0) && bad == 0) bad = j + 1;
+        const double s = __dsqrt_rn(piv);
+        const double inv = __drcp_rn(s);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int r = l + 32 * q;
+            if (r == j) { T[q] = inv; P[q][jj] = s; }
+            else { T[q] = P[q][jj] * inv; P[q][jj] = T[q]; }
+            vr[r * CB + jj] = T[q];
+            vup[r * CB + jj] = (r <= j) ? T[q] : 0.0;
+            vc[(jj * 8 + (r & 7)) * 16 + (r >> 3)] = T[q];
+        }
+        if (l == src0 + jj) xd[j] = inv;
+#pragma unroll
+        for (int cc = jj + 1; cc < CB; ++cc) {
+            const int c = ps + cc;
+            const double vcol = __shfl_sync(0xffffffffu, T[Q], src0 + cc);       // scaled column j at row c (c > j)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int r = l + 32 * q;
+                if (c <= r || r <= j) P[q][cc] = fma(-T[q], vcol, P[q][cc]);
+            }
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int cc = 0; cc < CB; ++cc) pn[(l + 32 * q) * CB_PITCH + cc] = P[q][cc];
+    return bad;
+}
+
+// All 256 threads must call.  work: CBK_WORK doubles, xd: NB doubles, both in shared memory.  Same contract as
+// chol_inv_regs with n = NB.
+__device__ __forceinline__ int chol_inv_blocked(double (&E)[8][8], double* work, double* xd) {
+    double* vr = work + 2 * CBK_PN;
+    double* vup = vr + NB * CB;
+    double* vc = vup + NB * CB;
+    int* status = reinterpret_cast<int*>(vc + NB * CB);
+    const int tid = threadIdx.x;
+    const int tr = tid >> 4, tc = tid & 15;
+    const int R0 = tr * 8;
+    if (tid == 0) status[0] = 0;
+#pragma unroll 1
+    for (int jb = 0; jb < NB / CB; ++jb) {
+        const int ps = jb * CB;
+        double* pn = work + (jb & 1) * CBK_PN;
+        if (tc == jb) {                                   // this thread owns 8 rows of the panel's columns
+#pragma unroll
+            for (int rr = 0; rr < 8; ++rr)
+#pragma unroll
+                for (int cc = 0; cc < 8; ++cc) pn[(R0 + rr) * CB_PITCH + cc] = E[rr][cc];
+        }
+        __syncthreads();
+        if (tid < 32) {
+            int bad;
+            switch (jb >> 2) {
+                case 0: bad = chol_panel_warp<0>(pn, ps, vr, vup, vc, xd); break;
+                case 1: bad = chol_panel_warp<1>(pn, ps, vr, vup, vc, xd); break;
+                case 2: bad = chol_panel_warp<2>(pn, ps, vr, vup, vc, xd); break;
+                default: bad = chol_panel_warp<3>(pn, ps, vr, vup, vc, xd); break;
+            }
+            if (bad && tid == 0 && status[0] == 0) status[0] = bad;
+        }
+        __syncthreads();
+        if (tc == jb) {
+#pragma unroll
+            for (int rr = 0; rr < 8; ++rr)
+#pragma unroll
+                for (int cc = 0; cc < 8; ++cc) E[rr][cc] = pn[(R0 + rr) * CB_PITCH + cc];
+        } else if (tc > jb && (tr >= tc || tr <= jb)) {
+            // trailing tiles: the L part (on or below the diagonal) and the rows of the X part that have started
+            const double* row_lo = (tc > tr) ? vup : vr;          // row multiplier of the elements with c <= r
+            const double* row_up = (tc < tr) ? vr : vup;          // ... and of those with c > r
+#pragma unroll
+            for (int k = 0; k < CB; ++k) {
+                double vcol[8], lo[8], up[8];
+#pragma unroll
+                for (int cc = 0; cc < 8; ++cc) vcol[cc] = vc[(k * 8 + cc) * 16 + tc];
+#pragma unroll
+                for (int rr = 0; rr < 8; ++rr) { lo[rr] = row_lo[(R0 + rr) * CB + k]; up[rr] = row_up[(R0 + rr) * CB + k]; }
+#pragma unroll
+                for (int rr = 0; rr < 8; ++rr)
+#pragma unroll
+                    for (int cc = 0; cc < 8; ++cc)
+                        E[rr][cc] = fma(-((cc <= rr) ? lo[rr] : up[rr]), vcol[cc], E[rr][cc]);
+            }
+        }
+    }
+    __syncthreads();
+    return status[0];
 }
 
 }  // namespace gpk

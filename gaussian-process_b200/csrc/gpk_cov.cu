@@ -80,20 +80,22 @@ __device__ __forceinline__ double cov_lower_rows(const double* __restrict__ xsp,
             }
             out[(size_t)i * Np + j] = v;
             if (PROBE) {
-                s_prod[lr * CP_PITCH + c] = v * vj;
+                s_prod[(b & 1) * CP_ROWS * CP_PITCH + lr * CP_PITCH + c] = v * vj;
                 colsum = fma(v, s_pvi[r], colsum);
             }
         }
         if (PROBE) {
+            // two staging buffers: one barrier per batch (the barrier of batch b + 1 separates these reads from the
+            // writes of batch b + 2 into the same buffer)
             __syncthreads();
             const int rr = threadIdx.x >> 4, q = threadIdx.x & 15;          // 16 threads per row of the batch
+            const double* src = s_prod + (b & 1) * CP_ROWS * CP_PITCH + rr * CP_PITCH + q;
             double a = 0.0;
 #pragma unroll
-            for (int m = 0; m < NB / 16; ++m) a += s_prod[rr * CP_PITCH + q + 16 * m];
+            for (int m = 0; m < NB / 16; ++m) a += src[16 * m];
 #pragma unroll
             for (int o = 8; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
             if (q == 0) s_rowsum[b * CP_ROWS + rr] = a;
-            __syncthreads();
         }
     }
     return colsum;
@@ -121,7 +123,7 @@ __global__ void __launch_bounds__(256) k_cov_lower(const double* __restrict__ xs
 
     __shared__ double s_xi[MAX_D][NB];
     __shared__ double s_sqi[NB];
-    __shared__ double s_prod[PROBE ? CP_ROWS * CP_PITCH : 1];
+    __shared__ double s_prod[PROBE ? 2 * CP_ROWS * CP_PITCH : 1];
     __shared__ double s_rowsum[PROBE ? NB : 1];
     __shared__ double s_col[PROBE ? 2 : 1][NB];
     __shared__ double s_pvi[PROBE ? NB : 1];

@@ -3,15 +3,28 @@
 // One CTA per particle.  Reference step being replaced: numpy.linalg.cholesky at GP_func.py:22.
 #include "gpk_cholinv.cuh"
 
+#include <cstdlib>
+
 namespace gpk {
 
+constexpr int DIAG_WORK = (CBK_WORK > CI_WORK) ? CBK_WORK : CI_WORK;
+constexpr size_t DIAG_SMEM_BYTES = (size_t)NB * CI_LD * sizeof(double) + (size_t)(DIAG_WORK + NB) * sizeof(double);
+
+// VARIANT 0: one column per step, correctly rounded pivot roots (round 1); 1: panels of 8 columns, exact roots; 2: one
+// column per step with the short reciprocal-square-root chain.  Measured on C2 (N = 1024, 64 particles,
+// profiles/r02_ab_diag.md): 54.9 / 77.7 / 53.2 us per launch, all three bit-identical on the test problems.  A column step
+// costs ~0.43 us whatever the variant: the 64 update FMAs per thread (256 cycles of the SM's FP64 pipe per step when every
+// tile is active) plus the publish -> barrier -> load round trip, not the root chain (3 % from shortening it) and not the
+// barrier alone (the panel form trades it for shuffles and shared-memory stores of the same cost).  Variant 0 stays the
+// default: its roots are the correctly rounded ones of the reference's LAPACK path.
+template <int VARIANT>
 __global__ void __launch_bounds__(256, 1)
 k_diag_block(double* __restrict__ mat, int Np, int J, double* __restrict__ dinv, double* __restrict__ dinvT,
              int T, int* __restrict__ info, const unsigned char* __restrict__ active, int mode) {
     extern __shared__ double smem[];
     double* Lm = smem;
     double* work = smem + NB * CI_LD;
-    double* xr = work + CI_WORK;
+    double* xr = work + DIAG_WORK;
     const int p = blockIdx.x;
     if (active && !active[p]) return;
     const int tid = threadIdx.x;
@@ -30,7 +43,10 @@ k_diag_block(double* __restrict__ mat, int Np, int J, double* __restrict__ dinv,
                 E[rr][cc] = (c <= r) ? blk[(size_t)r * Np + c] : 0.0;
             }
     }
-    const int bad = chol_inv_regs(E, NB, work, xd);
+    int bad;
+    if (VARIANT == 1) bad = chol_inv_blocked(E, work, xd);
+    else if (VARIANT == 2) bad = chol_inv_regs<true>(E, NB, work, xd);
+    else bad = chol_inv_regs<false>(E, NB, work, xd);
     if (bad && tid == 0) atomicCAS(&info[p], 0, J * NB + bad);
     chol_inv_dump(E, xd, Lm);
     __syncthreads();
@@ -50,14 +66,19 @@ k_diag_block(double* __restrict__ mat, int Np, int J, double* __restrict__ dinv,
 
 int launch_diag_block(double* mat, int Np, int J, int P, double* dinv, double* dinvT, int T, int* info,
                       const unsigned char* active, int mode, cudaStream_t st) {
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(k_diag_block, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)CI_SMEM_BYTES);
+    static int variant = -1;          // GPK_DIAG_VARIANT = 0 | 1 | 2 (A/B runs and tests); default 0
+    if (variant < 0) {
+        const char* v = getenv("GPK_DIAG_VARIANT");
+        const int want = (v && atoi(v) >= 0 && atoi(v) <= 2) ? atoi(v) : 0;
+        cudaError_t e = want == 0 ? cudaFuncSetAttribute(k_diag_block<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DIAG_SMEM_BYTES)
+                      : want == 1 ? cudaFuncSetAttribute(k_diag_block<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DIAG_SMEM_BYTES)
+                                  : cudaFuncSetAttribute(k_diag_block<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DIAG_SMEM_BYTES);
         if (e != cudaSuccess) { set_error("k_diag_block smem attr: %s", cudaGetErrorString(e)); return 1; }
-        configured = true;
+        variant = want;
     }
-    k_diag_block<<<P, 256, CI_SMEM_BYTES, st>>>(mat, Np, J, dinv, dinvT, T, info, active, mode);
+    if (variant == 0) k_diag_block<0><<<P, 256, DIAG_SMEM_BYTES, st>>>(mat, Np, J, dinv, dinvT, T, info, active, mode);
+    else if (variant == 1) k_diag_block<1><<<P, 256, DIAG_SMEM_BYTES, st>>>(mat, Np, J, dinv, dinvT, T, info, active, mode);
+    else k_diag_block<2><<<P, 256, DIAG_SMEM_BYTES, st>>>(mat, Np, J, dinv, dinvT, T, info, active, mode);
     return check_launch("k_diag_block");
 }
 
