@@ -144,8 +144,9 @@ struct OzBuffers {
     int* cnt = nullptr;          // tile counters; next() hands out one per digit-GEMM launch
     mutable int cnt_used = 0;
     int* next() const { return cnt + cnt_used++; }
-    double *rowsig = nullptr, *rowinv = nullptr, *gam = nullptr, *gaminv = nullptr, *mtsig = nullptr, *mtinv = nullptr;
-    unsigned long long* mtmax = nullptr;      // row maxima of the phase-2 panel (bit patterns of non-negative doubles)
+    double *rowsig = nullptr, *rowinv = nullptr, *gam = nullptr, *gaminv = nullptr, *mtsig = nullptr;
+    unsigned long long* mtmax = nullptr;      // row maxima of the phase-2 panel (bit patterns of non-negative doubles),
+    size_t mtmax_stride = 0;                  // two buffers (parity of the block column) of mtmax_stride entries each
     size_t mtmax_bytes = 0;
 };
 
@@ -157,9 +158,10 @@ static OzBuffers oz_buffers(char* ws, const BlockedLayout& L) {
     double* r = (double*)(ws + L.oz_rows);
     o.rowsig = r; o.rowinv = r + L.Np; o.gam = r + 2 * (size_t)L.Np; o.gaminv = r + 3 * (size_t)L.Np;
     double* m = (double*)(ws + L.oz_mtsc);
-    o.mtsig = m; o.mtinv = m + (size_t)L.P * NB;
-    o.mtmax = (unsigned long long*)(m + 2 * (size_t)L.P * NB);
-    o.mtmax_bytes = (size_t)L.P * NB * 8;
+    o.mtsig = m;
+    o.mtmax = (unsigned long long*)(m + (size_t)L.P * NB);
+    o.mtmax_stride = (size_t)L.P * NB;
+    o.mtmax_bytes = 2 * (size_t)L.P * NB * 8;
     o.sdig = (uint8_t*)(ws + L.oz_sdig);
     o.ddig = (uint8_t*)(ws + L.oz_ddig);
     o.dsc = (double*)(ws + L.oz_dsc);
@@ -173,7 +175,7 @@ static int factor_phase(double* mat, int Np, int T, int P, double* dinv, double*
     for (int J = 0; J < T; ++J) {
         if (!oz.slices) {
             if (launch_syrk_update(mat, Np, T, J, P, active, st)) return 1;
-            if (launch_diag_block(mat, Np, J, P, dinv, dinvT, T, info, active, mode, st)) return 1;
+            if (launch_diag_block(mat, Np, J, P, dinv, dinvT, T, info, active, mode, nullptr, nullptr, nullptr, st)) return 1;
             if (launch_trsm_panel(mat, Np, T, J, P, dinv, active, st)) return 1;
             continue;
         }
@@ -182,8 +184,8 @@ static int factor_phase(double* mat, int Np, int T, int P, double* dinv, double*
         if (J > 0) {
             if (launch_oz_syrk(mat, Np, T, J, P, oz.slices, oz.rowsig, oz.rowinv, oz.sdig, oz.next(), active, st)) return 1;
         }
-        if (launch_diag_block(mat, Np, J, P, dinv, dinvT, T, info, active, mode, st)) return 1;
-        if (launch_oz_slice_d(dinv, dinvT, T, J, P, oz.rowsig, oz.ddig, oz.dsc, active, st)) return 1;
+        // the diagonal kernel also leaves the digits of D_J rowsig and D_J^T (the B / A operands of the two panel contractions)
+        if (launch_diag_block(mat, Np, J, P, dinv, dinvT, T, info, active, mode, oz.rowsig, oz.ddig, oz.dsc, st)) return 1;
         if (J == 0) {        // no SYRK ran: the first block column is still the raw covariance, no digits of it exist
             if (launch_trsm_panel(mat, Np, T, J, P, dinv, active, st)) return 1;
             if (launch_oz_slice_l(mat, Np, T, J, P, oz.rowinv, oz.slices, active, st)) return 1;
@@ -203,8 +205,9 @@ static int inverse_phase(double* mat, int Np, int T, int P, const double* dinvT,
     }
     for (int J = T - 2; J >= 0; --J) {
         if (oz.slices) {
-            if (launch_oz_invp(mt, Np, T, J, P, oz.ddig, oz.dsc, oz.slices, oz.rowsig, oz.mtmax, oz.gaminv, oz.next(), active, st)) return 1;
-            if (launch_oz_mt(mt, Np, T, J, P, oz.gaminv, oz.mtmax, oz.mtsig, oz.mtinv, oz.mtslices, active, st)) return 1;
+            if (launch_oz_invp(mt, Np, T, J, P, oz.ddig, oz.dsc, oz.slices, oz.rowsig, oz.mtmax + (size_t)(J & 1) * oz.mtmax_stride,
+                               oz.gaminv, oz.next(), active, st)) return 1;
+            if (launch_oz_mt(mt, Np, T, J, P, oz.gaminv, oz.mtmax, oz.mtmax_stride, oz.mtsig, oz.mtslices, active, st)) return 1;
             if (launch_oz_invu(mat, Np, T, J, P, oz.slices, oz.mtslices, oz.mtsig, oz.gam, 1, oz.next(), active, st)) return 1;
         } else {
             if (launch_inv_panel(mat, Np, T, J, P, dinvT, mt, active, st)) return 1;
@@ -539,8 +542,8 @@ int gpk_fit(const double* X, const double* y, const double* e, const double* ls,
         oz.mtslices = (uint8_t*)(ws + off); off += align256(oz_mt_bytes(Np));
         double* r = (double*)(ws + off); off += align256((size_t)4 * Np * 8);
         oz.rowsig = r; oz.rowinv = r + Np; oz.gam = r + 2 * (size_t)Np; oz.gaminv = r + 3 * (size_t)Np;
-        oz.mtsig = (double*)(ws + off); oz.mtinv = oz.mtsig + NB; oz.mtmax = (unsigned long long*)(oz.mtsig + 2 * NB);
-        oz.mtmax_bytes = (size_t)NB * 8; off += align256((size_t)3 * NB * 8);
+        oz.mtsig = (double*)(ws + off); oz.mtmax = (unsigned long long*)(oz.mtsig + NB); oz.mtmax_stride = NB;
+        oz.mtmax_bytes = (size_t)2 * NB * 8; off += align256((size_t)3 * NB * 8);
         oz.sdig = (uint8_t*)(ws + off); off += align256(oz_panel_bytes(Np));
         oz.ddig = (uint8_t*)(ws + off); off += align256(oz_ddig_bytes(Np));
         oz.dsc = (double*)(ws + off); off += align256((size_t)T * 2 * NB * 8);

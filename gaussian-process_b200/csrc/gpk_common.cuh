@@ -78,8 +78,10 @@ int launch_cross_cov(const double* xs, const double* sq, const double* ls, const
 
 // gpk_diag.cu
 enum DiagMode { DIAG_WRITE_INVERSE = 0, DIAG_WRITE_FACTOR = 1 };
+// ddig != nullptr (emulated mode): the kernel also emits the digit records and row scales of D_J rowsig and D_J^T
 int launch_diag_block(double* mat, int Np, int J, int P, double* dinv, double* dinvT, int T,
-                      int* info, const unsigned char* active, int mode, cudaStream_t st);
+                      int* info, const unsigned char* active, int mode, const double* rowsig, uint8_t* ddig, double* dsc,
+                      cudaStream_t st);
 
 int launch_tri_inv_diag(const double* Lsrc, double* dst, int Np, int T, int P, double* dinv, double* dinvT, int* info,
                         const unsigned char* active, cudaStream_t st);
@@ -104,8 +106,6 @@ size_t oz_panel_bytes(int Np);
 size_t oz_ddig_bytes(int Np);
 int launch_oz_syrk(double* mat, int Np, int T, int J, int P, const uint8_t* slices, const double* rowsig,
                    const double* rowinv, uint8_t* sdig, int* counter, const unsigned char* active, cudaStream_t st);
-int launch_oz_slice_d(const double* dinv, const double* dinvT, int T, int J, int P, const double* rowsig, uint8_t* ddig,
-                      double* dsc, const unsigned char* active, cudaStream_t st);
 int launch_oz_trsm(double* mat, int Np, int T, int J, int P, const uint8_t* sdig, const uint8_t* ddig, const double* dsc,
                    const double* rowsig, const double* rowinv, uint8_t* slices, int* counter, const unsigned char* active,
                    cudaStream_t st);
@@ -117,7 +117,7 @@ int launch_oz_slice_l(const double* mat, int Np, int T, int J, int P, const doub
 int launch_oz_slice_w(const double* mat, int Np, int T, int J, int diag, int P, const double* gam, uint8_t* slices,
                       const unsigned char* active, cudaStream_t st);
 int launch_oz_mt(const double* mt, int Np, int T, int J, int P, const double* gaminv, unsigned long long* mtmax,
-                 double* mtsig, double* mtinv, uint8_t* mtslices, const unsigned char* active, cudaStream_t st);
+                 size_t mtmax_stride, double* mtsig, uint8_t* mtslices, const unsigned char* active, cudaStream_t st);
 int launch_oz_invu(double* mat, int Np, int T, int J, int P, uint8_t* slices, const uint8_t* mtslices,
                    const double* mtsig, const double* gam, int emit, int* counter, const unsigned char* active,
                    cudaStream_t st);

@@ -45,10 +45,10 @@ int launch_scale_points(const double* X, const double* ls, int P, int N, int Np,
 // rows r = (threadIdx.x >> 7), +2, ... of tile (I, .) for column j: K_ij + delta_ij e_i^2, identity in the padding.
 // PROBE: the tile's contributions to u = K v (v = probe_v, the residual probe of include/gpk.h) are formed on the way:
 // the column sum sum_i K_ij v_i of this thread's 64 rows stays in a register (returned); the row sums sum_j K_ij v_j need
-// all 128 columns = threads of a row and go through shared memory in batches of 16 rows (s_prod, then 16 threads per row
-// add 8 columns each and finish with 4 shuffle steps) -> s_rowsum[r].  Keeping the 64 products of a thread in registers
+// all 128 columns = threads of a row and go through shared memory in batches of 8 rows (s_prod, then one warp per row
+// adds 4 columns per lane and finishes with 5 shuffle steps) -> s_rowsum[r].  Keeping the 64 products of a thread in registers
 // for a warp butterfly instead costs 66 registers and halves the occupancy of this FP64-pipe-bound kernel (measured: 2x time).
-constexpr int CP_ROWS = 16;              // rows per batch
+constexpr int CP_ROWS = 8;               // rows per batch (two staging buffers of CP_ROWS x 129 doubles: 16.5 KB, 5 CTAs per SM)
 constexpr int CP_PITCH = NB + 1;
 template <int D, bool PROBE>
 __device__ __forceinline__ double cov_lower_rows(const double* __restrict__ xsp, const double* __restrict__ sqp,
@@ -88,13 +88,13 @@ __device__ __forceinline__ double cov_lower_rows(const double* __restrict__ xsp,
             // two staging buffers: one barrier per batch (the barrier of batch b + 1 separates these reads from the
             // writes of batch b + 2 into the same buffer)
             __syncthreads();
-            const int rr = threadIdx.x >> 4, q = threadIdx.x & 15;          // 16 threads per row of the batch
+            const int rr = threadIdx.x >> 5, q = threadIdx.x & 31;          // one warp per row of the batch
             const double* src = s_prod + (b & 1) * CP_ROWS * CP_PITCH + rr * CP_PITCH + q;
             double a = 0.0;
 #pragma unroll
-            for (int m = 0; m < NB / 16; ++m) a += src[16 * m];
+            for (int m = 0; m < NB / 32; ++m) a += src[32 * m];
 #pragma unroll
-            for (int o = 8; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+            for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
             if (q == 0) s_rowsum[b * CP_ROWS + rr] = a;
         }
     }
@@ -108,7 +108,7 @@ __device__ __forceinline__ double cov_lower_rows(const double* __restrict__ xsp,
 // block B -- tile (I, J) writes its row sums to [J][rows of I] and, for I > J, its column sums (K is symmetric) to
 // [I][columns of J]: every slot is written exactly once, k_probe_sum adds them in a fixed order.
 template <bool PROBE>
-__global__ void __launch_bounds__(256) k_cov_lower(const double* __restrict__ xs, const double* __restrict__ sq,
+__global__ void __launch_bounds__(256, 5) k_cov_lower(const double* __restrict__ xs, const double* __restrict__ sq,
                                                    const double* __restrict__ e, int N, int Np, int d,
                                                    double* __restrict__ mat, double* __restrict__ kv,
                                                    const unsigned char* __restrict__ active) {

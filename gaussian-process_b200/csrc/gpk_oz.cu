@@ -26,18 +26,12 @@
 // instruction with N = 64 * count multiplies the A digit s with `count` consecutive B digits and lands in the
 // accumulators of the groups s + t0 .. s + t0 + count - 1, which are adjacent TMEM columns: 10-11 instructions of
 // N <= 256 per K chunk instead of 28-34 of N = 64.
-#include "gpk_common.cuh"
+#include "gpk_ozdig.cuh"
 
 #include <cstdlib>
 
 namespace gpk {
 
-constexpr int OZ_NS = 7;                        // int8 digits per FP64 value
-constexpr int OZ_DIGIT = 4096;                  // one digit of a 128-row block x 32 k: [16 row groups][256 B]
-constexpr int OZ_DIGIT_HALF = 2048;             // 64 rows
-constexpr int OZ_CHUNK = OZ_NS * OZ_DIGIT;      // 128 rows x 32 k x 7 digits = 28672 B
-constexpr int OZ_HALF = OZ_NS * OZ_DIGIT_HALF;  // 64 rows, digits back to back (shared-memory image of B)
-constexpr int OZ_STAGE = OZ_CHUNK + OZ_HALF;    // A (128 rows) + B (64 rows)
 constexpr int OZ_STAGES = 5;
 #ifndef OZ_PREFETCH_CHUNKS
 #define OZ_PREFETCH_CHUNKS 0
@@ -47,7 +41,6 @@ constexpr int OZ_THREADS = 320;                 // warp 0 producer, warp 1 MMA i
 constexpr int OZ_TMEM_COLS = 512;
 constexpr int OZ_TILE_N = 64;
 constexpr size_t OZ_SMEM_BYTES = (size_t)OZ_STAGES * OZ_STAGE + 256;
-constexpr long long OZ_BIAS = 0x0000808080808080LL;
 // kind::i8, D = S32, A = B = signed 8 bit, both K-major, M = 128; the N field (bits 17..22, N >> 3) is added per MMA
 constexpr uint32_t OZ_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((128u >> 4) << 24);
 // no-swizzle K-major shared-memory descriptor without the start address: LBO = 128 B, SBO = 256 B, version 1
@@ -113,14 +106,6 @@ __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory"); }
 
-// 256-bit global accesses (32-byte aligned): one full sector per lane
-__device__ __forceinline__ void stg_f64x4(double* p, double a, double b, double c, double d) {
-    asm volatile("st.global.v4.f64 [%0], {%1, %2, %3, %4};\n" ::"l"(p), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
-}
-__device__ __forceinline__ void ldg_f64x4(const double* p, double& a, double& b, double& c, double& d) {
-    asm volatile("ld.global.v4.f64 {%0, %1, %2, %3}, [%4];\n" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p) : "memory");
-}
-
 // exact int64 -> double for |v| < 2^51 without the slow I2F path
 __device__ __forceinline__ double ll2d_exact(long long v) {
     return __longlong_as_double(0x4338000000000000LL + v) - 6755399441055744.0;
@@ -141,14 +126,6 @@ __device__ __forceinline__ double oz_acc2(uint32_t a0, uint32_t a1, uint32_t mag
     long long w = (long long)(((unsigned long long)magic_hi << 32) | (unsigned long long)(a1 ^ 0x80000000u));
     w += (long long)(int)a0 * 256;
     return __longlong_as_double(w) - 6755401588539392.0;
-}
-
-// byte b of four 32-bit words -> one word (digit b of four consecutive k)
-__device__ __forceinline__ uint32_t pack_digit(const uint32_t* w, int b) {
-    const uint32_t sel = (uint32_t)b | ((uint32_t)(4 + b) << 4);
-    const uint32_t t0 = __byte_perm(w[0], w[1], sel);
-    const uint32_t t1 = __byte_perm(w[2], w[3], sel);
-    return __byte_perm(t0, t1, 0x5410);
 }
 
 enum OzEpi { OZ_SUB = 0, OZ_STORE = 1, OZ_STORE_NEG = 2, OZ_SUMSQ = 3 };
@@ -591,54 +568,6 @@ struct OzGemmTiles {
     }
 };
 
-// ---- slicers: FP64 128 x 128 tile -> 4 chunk records ----------------------------------------------------------
-
-// u = x * rs[row] * rconst * cs[col];  |u| <= 0.98 is the caller's contract (a-priori bounds / measured maxima)
-__device__ __forceinline__ void oz_slice_tile(const double* __restrict__ src, int ld, const double* __restrict__ rs,
-                                              double rconst, const double* __restrict__ cs, uint8_t* __restrict__ dst) {
-    for (int unit = threadIdx.x; unit < 1024; unit += blockDim.x) {
-        const int kcl = unit >> 8, rg = (unit >> 4) & 15, kg = (unit >> 3) & 1, r8 = unit & 7;
-        const int row = rg * 8 + r8, col0 = kcl * 32 + kg * 16;
-        const double* sp = src + (size_t)row * ld + col0;
-        const double rsv = (rs ? rs[row] : 1.0) * rconst * 0x1p55;
-        uint32_t lo[16], hi[16];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            double x[4];
-            ldg_f64x4(sp + 4 * j, x[0], x[1], x[2], x[3]);          // one full 32-byte sector per lane
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                double u = x[i] * rsv;
-                if (cs) u *= cs[col0 + 4 * j + i];
-                const long long v = (__double2ll_rn(u) + OZ_BIAS) ^ OZ_BIAS;
-                lo[4 * j + i] = (uint32_t)v;
-                hi[4 * j + i] = (uint32_t)(v >> 32);
-            }
-        }
-        uint8_t* d = dst + (size_t)kcl * OZ_CHUNK + rg * 256 + kg * 128 + r8 * 16;
-#pragma unroll
-        for (int s = 0; s < OZ_NS; ++s) {
-            const int bytepos = 6 - s;                 // digit s = byte (6 - s) of the biased fixed-point word
-            const uint32_t* w = (bytepos >= 4) ? hi : lo;
-            const int b = bytepos & 3;
-            uint4 o;
-            o.x = pack_digit(w + 0, b);
-            o.y = pack_digit(w + 4, b);
-            o.z = pack_digit(w + 8, b);
-            o.w = pack_digit(w + 12, b);
-            *reinterpret_cast<uint4*>(d + s * OZ_DIGIT) = o;
-        }
-    }
-}
-
-// smallest power of two sigma with bound / sigma <= 0.98 (the top digit then stays inside [-126, 126])
-__device__ __forceinline__ double oz_scale_for(double bound) {
-    if (!(bound > 0.0) || !(bound < 1e300)) return 1.0;
-    double sig = scalbn(1.0, ilogb(bound) + 1);
-    if (bound > 0.98 * sig) sig *= 2.0;
-    return sig;
-}
-
 // particle-independent scales: row bound of L (|L_ik| <= sqrt(K_ii) = sqrt(1 + e_i^2)) and the column scaling
 // gamma_k = 2^floor(log2 e_k) of W = L^-1 (|W_ik| <= 1 / e_k because K >= diag(e^2))
 __global__ void k_oz_prep(const double* __restrict__ e, int N, int Np, double* __restrict__ rowsig,
@@ -682,29 +611,29 @@ k_oz_slice_w(const double* __restrict__ mat, int Np, int J, int diag, const doub
                   slices + (size_t)p * slice_stride + ((size_t)I * kch + 4 * Jc) * OZ_CHUNK);
 }
 
-// row scales of the phase-2 panel from the row maxima max_k |Mt[n][k] / gamma_k| the panel GEMM's epilogue collected;
-// the maxima are reset for the next block column
-__global__ void __launch_bounds__(NB)
-k_oz_mt_scale(unsigned long long* __restrict__ mtmax, double* __restrict__ mtsig, double* __restrict__ mtinv,
-              const unsigned char* __restrict__ active) {
-    const int p = blockIdx.x;
-    if (active && !active[p]) return;
-    const size_t i = (size_t)p * NB + threadIdx.x;
-    const double sig = oz_scale_for(__longlong_as_double((long long)mtmax[i]));
-    mtmax[i] = 0ull;
-    mtsig[i] = sig;
-    mtinv[i] = 1.0 / sig;
-}
-
-// digits of Mt / gamma: blockIdx.x -> R = J + 1 + bx (128 columns of the panel)
+// digits of Mt / gamma: blockIdx.x -> R = J + 1 + bx (128 columns of the panel).  The row scales come from the row maxima
+// max_k |Mt[n][k] / gamma_k| the panel GEMM's epilogue collected (mtmax, one buffer per parity of J): every CTA derives the
+// 128 scales it needs itself; the first CTA of a particle also publishes them for the inverse update (mtsig) and clears the
+// other parity's maxima for the next block column (its last reader, the slicing of column J + 1, has finished).
 __global__ void __launch_bounds__(256)
 k_oz_slice_mt(const double* __restrict__ mt, int Np, int J, const double* __restrict__ gaminv,
-              const double* __restrict__ mtinv, uint8_t* __restrict__ mtslices, size_t mt_stride,
-              const unsigned char* __restrict__ active) {
+              unsigned long long* __restrict__ mtmax, size_t mtmax_stride, double* __restrict__ mtsig,
+              uint8_t* __restrict__ mtslices, size_t mt_stride, const unsigned char* __restrict__ active) {
+    __shared__ double s_inv[NB];
     const int p = blockIdx.y;
     if (active && !active[p]) return;
+    unsigned long long* cur = mtmax + (size_t)(J & 1) * mtmax_stride + (size_t)p * NB;
+    if (threadIdx.x < NB) {
+        const double sig = oz_scale_for(__longlong_as_double((long long)cur[threadIdx.x]));
+        s_inv[threadIdx.x] = 1.0 / sig;
+        if (blockIdx.x == 0) {
+            mtsig[(size_t)p * NB + threadIdx.x] = sig;
+            mtmax[(size_t)((J + 1) & 1) * mtmax_stride + (size_t)p * NB + threadIdx.x] = 0ull;
+        }
+    }
+    __syncthreads();
     const int R = J + 1 + blockIdx.x;
-    oz_slice_tile(mt + (size_t)p * NB * Np + (size_t)R * NB, Np, mtinv + (size_t)p * NB, 1.0, gaminv + R * NB,
+    oz_slice_tile(mt + (size_t)p * NB * Np + (size_t)R * NB, Np, s_inv, 1.0, gaminv + R * NB,
                   mtslices + (size_t)p * mt_stride + (size_t)(4 * R) * OZ_CHUNK);
 }
 
@@ -715,39 +644,6 @@ k_oz_slice_generic(const double* __restrict__ src, int ld, int kch, const double
     const int cb = blockIdx.x, rb = blockIdx.y;
     oz_slice_tile(src + (size_t)rb * NB * ld + (size_t)cb * NB, ld, rowinv ? rowinv + rb * NB : nullptr, 1.0, nullptr,
                   dst + ((size_t)rb * kch + 4 * cb) * OZ_CHUNK);
-}
-
-// Digits of the inverse diagonal block D_J = L_JJ^-1 for the two panel contractions, with measured row scales:
-//   blockIdx.x = 0: D_J[n][j] * rowsig_j   (B operand of the TRSM  L_IJ = S_IJ D_J^T, whose A digits carry 1/rowsig_j)
-//   blockIdx.x = 1: D_J^T[n][j]            (A operand of the phase-2 panel  Mt = D_J^T L_RJ^T)
-// dig: [P][T][2][4 chunks], dsc: [P][T][2][NB] row scales sigma_n.
-__global__ void __launch_bounds__(256)
-k_oz_slice_d(const double* __restrict__ dinv, const double* __restrict__ dinvT, int T, int J,
-             const double* __restrict__ rowsig, uint8_t* __restrict__ dig, double* __restrict__ dsc,
-             const unsigned char* __restrict__ active) {
-    __shared__ double inv[NB];
-    const int p = blockIdx.y, which = blockIdx.x;
-    if (active && !active[p]) return;
-    const double* src = (which ? dinvT : dinv) + ((size_t)p * T + J) * NB * NB;
-    const double* cs = which ? nullptr : rowsig + J * NB;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int n = warp; n < NB; n += 8) {
-        double m = 0.0;
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            const int j = lane + 32 * q;
-            m = fmax(m, fabs(src[n * NB + j] * (cs ? cs[j] : 1.0)));
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
-        if (lane == 0) {
-            const double sig = oz_scale_for(m);
-            inv[n] = 1.0 / sig;
-            dsc[(((size_t)p * T + J) * 2 + which) * NB + n] = sig;
-        }
-    }
-    __syncthreads();
-    oz_slice_tile(src, NB, inv, 1.0, cs, dig + (((size_t)p * T + J) * 2 + which) * (4 * (size_t)OZ_CHUNK));
 }
 
 // Panel solve on the digit GEMM: L_IJ = S_IJ D_J^T, tile = p * nx + (128 / TN) * (I - J - 1) + column part.  A = digits of
@@ -1057,12 +953,6 @@ int launch_oz_syrk(double* mat, int Np, int T, int J, int P, const uint8_t* slic
     return check_launch("k_oz_syrk");
 }
 
-int launch_oz_slice_d(const double* dinv, const double* dinvT, int T, int J, int P, const double* rowsig, uint8_t* ddig,
-                      double* dsc, const unsigned char* active, cudaStream_t st) {
-    k_oz_slice_d<<<dim3(2, P), 256, 0, st>>>(dinv, dinvT, T, J, rowsig, ddig, dsc, active);
-    return check_launch("k_oz_slice_d");
-}
-
 int launch_oz_trsm(double* mat, int Np, int T, int J, int P, const uint8_t* sdig, const uint8_t* ddig, const double* dsc,
                    const double* rowsig, const double* rowinv, uint8_t* slices, int* counter, const unsigned char* active,
                    cudaStream_t st) {
@@ -1098,11 +988,9 @@ int launch_oz_slice_w(const double* mat, int Np, int T, int J, int diag, int P, 
 }
 
 int launch_oz_mt(const double* mt, int Np, int T, int J, int P, const double* gaminv, unsigned long long* mtmax,
-                 double* mtsig, double* mtinv, uint8_t* mtslices, const unsigned char* active, cudaStream_t st) {
+                 size_t mtmax_stride, double* mtsig, uint8_t* mtslices, const unsigned char* active, cudaStream_t st) {
     if (J >= T - 1) return 0;
-    k_oz_mt_scale<<<P, NB, 0, st>>>(mtmax, mtsig, mtinv, active);
-    if (check_launch("k_oz_mt_scale")) return 1;
-    k_oz_slice_mt<<<dim3(T - 1 - J, P), 256, 0, st>>>(mt, Np, J, gaminv, mtinv, mtslices, oz_mt_bytes(Np), active);
+    k_oz_slice_mt<<<dim3(T - 1 - J, P), 256, 0, st>>>(mt, Np, J, gaminv, mtmax, mtmax_stride, mtsig, mtslices, oz_mt_bytes(Np), active);
     return check_launch("k_oz_slice_mt");
 }
 
