@@ -175,7 +175,7 @@ static int factor_phase(double* mat, int Np, int T, int P, double* dinv, double*
     for (int J = 0; J < T; ++J) {
         if (!oz.slices) {
             if (launch_syrk_update(mat, Np, T, J, P, active, st)) return 1;
-            if (launch_diag_block(mat, Np, J, P, dinv, dinvT, T, info, active, mode, nullptr, nullptr, nullptr, st)) return 1;
+            if (launch_diag_block(mat, Np, J, P, dinv, dinvT, T, info, active, mode, st)) return 1;
             if (launch_trsm_panel(mat, Np, T, J, P, dinv, active, st)) return 1;
             continue;
         }
@@ -184,8 +184,10 @@ static int factor_phase(double* mat, int Np, int T, int P, double* dinv, double*
         if (J > 0) {
             if (launch_oz_syrk(mat, Np, T, J, P, oz.slices, oz.rowsig, oz.rowinv, oz.sdig, oz.next(), active, st)) return 1;
         }
-        // the diagonal kernel also leaves the digits of D_J rowsig and D_J^T (the B / A operands of the two panel contractions)
-        if (launch_diag_block(mat, Np, J, P, dinv, dinvT, T, info, active, mode, oz.rowsig, oz.ddig, oz.dsc, st)) return 1;
+        if (launch_diag_block(mat, Np, J, P, dinv, dinvT, T, info, active, mode, st)) return 1;
+        // (fusing this slicer into the diagonal kernel was measured in round 2: one CTA per particle slices the two operand
+        // sets in 14 us where the separate launch spreads them over 2 P CTAs; C2 2.65 -> 2.70 ms per swarm: kept separate)
+        if (launch_oz_slice_d(dinv, dinvT, T, J, P, oz.rowsig, oz.ddig, oz.dsc, active, st)) return 1;
         if (J == 0) {        // no SYRK ran: the first block column is still the raw covariance, no digits of it exist
             if (launch_trsm_panel(mat, Np, T, J, P, dinv, active, st)) return 1;
             if (launch_oz_slice_l(mat, Np, T, J, P, oz.rowinv, oz.slices, active, st)) return 1;

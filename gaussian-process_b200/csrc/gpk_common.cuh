@@ -78,10 +78,8 @@ int launch_cross_cov(const double* xs, const double* sq, const double* ls, const
 
 // gpk_diag.cu
 enum DiagMode { DIAG_WRITE_INVERSE = 0, DIAG_WRITE_FACTOR = 1 };
-// ddig != nullptr (emulated mode): the kernel also emits the digit records and row scales of D_J rowsig and D_J^T
 int launch_diag_block(double* mat, int Np, int J, int P, double* dinv, double* dinvT, int T,
-                      int* info, const unsigned char* active, int mode, const double* rowsig, uint8_t* ddig, double* dsc,
-                      cudaStream_t st);
+                      int* info, const unsigned char* active, int mode, cudaStream_t st);
 
 int launch_tri_inv_diag(const double* Lsrc, double* dst, int Np, int T, int P, double* dinv, double* dinvT, int* info,
                         const unsigned char* active, cudaStream_t st);
@@ -106,6 +104,8 @@ size_t oz_panel_bytes(int Np);
 size_t oz_ddig_bytes(int Np);
 int launch_oz_syrk(double* mat, int Np, int T, int J, int P, const uint8_t* slices, const double* rowsig,
                    const double* rowinv, uint8_t* sdig, int* counter, const unsigned char* active, cudaStream_t st);
+int launch_oz_slice_d(const double* dinv, const double* dinvT, int T, int J, int P, const double* rowsig, uint8_t* ddig,
+                      double* dsc, const unsigned char* active, cudaStream_t st);
 int launch_oz_trsm(double* mat, int Np, int T, int J, int P, const uint8_t* sdig, const uint8_t* ddig, const double* dsc,
                    const double* rowsig, const double* rowinv, uint8_t* slices, int* counter, const unsigned char* active,
                    cudaStream_t st);

@@ -2,7 +2,6 @@
 // factor the 128x128 block A_JJ (already updated by the left-looking SYRK) and invert the factor.
 // One CTA per particle.  Reference step being replaced: numpy.linalg.cholesky at GP_func.py:22.
 #include "gpk_cholinv.cuh"
-#include "gpk_ozdig.cuh"
 
 #include <cstdlib>
 
@@ -21,8 +20,7 @@ constexpr size_t DIAG_SMEM_BYTES = (size_t)NB * CI_LD * sizeof(double) + (size_t
 template <int VARIANT>
 __global__ void __launch_bounds__(256, 1)
 k_diag_block(double* __restrict__ mat, int Np, int J, double* __restrict__ dinv, double* __restrict__ dinvT,
-             int T, int* __restrict__ info, const unsigned char* __restrict__ active, int mode,
-             const double* __restrict__ rowsig, uint8_t* __restrict__ ddig, double* __restrict__ dsc) {
+             int T, int* __restrict__ info, const unsigned char* __restrict__ active, int mode) {
     extern __shared__ double smem[];
     double* Lm = smem;
     double* work = smem + NB * CI_LD;
@@ -64,19 +62,10 @@ k_diag_block(double* __restrict__ mat, int Np, int J, double* __restrict__ dinv,
         if (mode == DIAG_WRITE_INVERSE) blk[(size_t)r * Np + c] = x_rc;
         else blk[(size_t)r * Np + c] = (c <= r) ? Lm[r * CI_LD + c] : 0.0;
     }
-    if (ddig != nullptr) {
-        // emulated mode: the digits of D_J rowsig (B operand of the panel solve) and of D_J^T (A operand of the phase-2 panel)
-        // with their measured row scales, from the values this CTA has just written (was a separate launch per block column)
-        __threadfence_block();
-        __syncthreads();
-        oz_slice_d_block(dinv, dinvT, T, J, p, 0, rowsig, ddig, dsc, work);
-        __syncthreads();
-        oz_slice_d_block(dinv, dinvT, T, J, p, 1, rowsig, ddig, dsc, work);
-    }
 }
 
 int launch_diag_block(double* mat, int Np, int J, int P, double* dinv, double* dinvT, int T, int* info,
-                      const unsigned char* active, int mode, const double* rowsig, uint8_t* ddig, double* dsc, cudaStream_t st) {
+                      const unsigned char* active, int mode, cudaStream_t st) {
     static int variant = -1;          // GPK_DIAG_VARIANT = 0 | 1 | 2 (A/B runs and tests); default 0
     if (variant < 0) {
         const char* v = getenv("GPK_DIAG_VARIANT");
@@ -87,9 +76,9 @@ int launch_diag_block(double* mat, int Np, int J, int P, double* dinv, double* d
         if (e != cudaSuccess) { set_error("k_diag_block smem attr: %s", cudaGetErrorString(e)); return 1; }
         variant = want;
     }
-    if (variant == 0) k_diag_block<0><<<P, 256, DIAG_SMEM_BYTES, st>>>(mat, Np, J, dinv, dinvT, T, info, active, mode, rowsig, ddig, dsc);
-    else if (variant == 1) k_diag_block<1><<<P, 256, DIAG_SMEM_BYTES, st>>>(mat, Np, J, dinv, dinvT, T, info, active, mode, rowsig, ddig, dsc);
-    else k_diag_block<2><<<P, 256, DIAG_SMEM_BYTES, st>>>(mat, Np, J, dinv, dinvT, T, info, active, mode, rowsig, ddig, dsc);
+    if (variant == 0) k_diag_block<0><<<P, 256, DIAG_SMEM_BYTES, st>>>(mat, Np, J, dinv, dinvT, T, info, active, mode);
+    else if (variant == 1) k_diag_block<1><<<P, 256, DIAG_SMEM_BYTES, st>>>(mat, Np, J, dinv, dinvT, T, info, active, mode);
+    else k_diag_block<2><<<P, 256, DIAG_SMEM_BYTES, st>>>(mat, Np, J, dinv, dinvT, T, info, active, mode);
     return check_launch("k_diag_block");
 }
 

@@ -953,6 +953,22 @@ int launch_oz_syrk(double* mat, int Np, int T, int J, int P, const uint8_t* slic
     return check_launch("k_oz_syrk");
 }
 
+__global__ void __launch_bounds__(256)
+k_oz_slice_d(const double* __restrict__ dinv, const double* __restrict__ dinvT, int T, int J,
+             const double* __restrict__ rowsig, uint8_t* __restrict__ dig, double* __restrict__ dsc,
+             const unsigned char* __restrict__ active) {
+    __shared__ double inv[NB];
+    const int p = blockIdx.y, which = blockIdx.x;
+    if (active && !active[p]) return;
+    oz_slice_d_block(dinv, dinvT, T, J, p, which, rowsig, dig, dsc, inv);
+}
+
+int launch_oz_slice_d(const double* dinv, const double* dinvT, int T, int J, int P, const double* rowsig, uint8_t* ddig,
+                      double* dsc, const unsigned char* active, cudaStream_t st) {
+    k_oz_slice_d<<<dim3(2, P), 256, 0, st>>>(dinv, dinvT, T, J, rowsig, ddig, dsc, active);
+    return check_launch("k_oz_slice_d");
+}
+
 int launch_oz_trsm(double* mat, int Np, int T, int J, int P, const uint8_t* sdig, const uint8_t* ddig, const double* dsc,
                    const double* rowsig, const double* rowinv, uint8_t* slices, int* counter, const unsigned char* active,
                    cudaStream_t st) {
