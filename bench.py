@@ -543,6 +543,9 @@ def run_ours(args):
         json_fd = os.dup(1)
         os.dup2(2, 1)
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev, timeout=datetime.timedelta(minutes=20))
+    if world > 1:
+        # torchrun pins OMP_NUM_THREADS=1 per rank: give the host-side copies (pinned staging -> result arrays) their share
+        torch.set_num_threads(max(1, (os.cpu_count() or 1) // world))
     _lib.load()
     engine.set_precision(args.precision)
     N, d, S = WORKLOAD["n_points"], WORKLOAD["dims"], WORKLOAD["n_sigma"]

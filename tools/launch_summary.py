@@ -5,11 +5,19 @@ import csv, re, sys
 from collections import defaultdict
 
 
+ROLES = {"OzSyrkTiles": "syrk", "OzTrsmTiles": "trsm", "OzInvpTiles": "invp", "OzInvuTiles": "invu", "OzPredTiles": "predict",
+         "OzGemmTiles": "gemm"}
+
+
 def kernel_class(name):
-    m = re.search(r"k_oz<\(int\)(\d), \(int\)(\d), gpk::(\w+)>", name)
+    """ncu prints the digit GEMM either with its functor ('void k_oz<0, 8, 64, OzSyrkTiles>(T4, int, int *)') or, in older
+    lists, as a bare 'gpk::k_oz<...>' whose role is inferred from its neighbours on the stream (below)."""
+    m = re.search(r"k_oz<.*?(Oz\w+Tiles)", name)
     if m:
-        return f"k_oz<{m.group(3)}>"
-    m = re.search(r"gpk::(\w+)", name)
+        return f"k_oz[{ROLES.get(m.group(1), m.group(1))}]"
+    if "k_oz<" in name:
+        return "k_oz"
+    m = re.match(r"(?:void\s+)?(?:gpk::)?(k_\w+)", name)
     return m.group(1) if m else "other:" + name.split("(")[0][-40:]
 
 
