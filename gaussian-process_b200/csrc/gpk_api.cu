@@ -220,8 +220,7 @@ static int inverse_phase(double* mat, int Np, int T, int P, const double* dinvT,
 }
 
 // ---- concurrent particle groups ------------------------------------------------------------------
-static int g_groups = 4;
-static bool g_groups_explicit = false;     // gpk_set_groups was called: the small-swarm cap of 2 groups no longer applies
+static int g_groups = 2;
 static int g_min_group = 16;       // particles per group below which a swarm is not split further (gpk_set_groups)
 static cudaStream_t g_group_streams[MAX_GROUPS] = {};
 static cudaEvent_t g_join[MAX_GROUPS] = {};
@@ -445,13 +444,12 @@ int gpk_loss_batched(const double* X, const double* y, const double* e, const do
     const double tol = check_tol != 0.0 ? (check_tol > 0.0 ? check_tol : -check_tol) : 1e300;
     const size_t per1 = blocked_layout(1, N, d, emu).total;
     if (workspace == nullptr || workspace_bytes < per1) { set_error("gpk_loss_batched: workspace too small (%zu < %zu)", workspace_bytes, per1); return 3; }
-    // particle groups: measured on one B200 at N = 4096 (profiles/r02_bench_v1.json, strong_scaling_slices_1gpu): 4 groups
-    // of 64 for the full 256-particle swarm, 2 groups for the slices of a sharded swarm (128 / 64 / 32 particles: 2 groups
-    // beat 1 by 1-8 % and 4 by 1-3 %): one group's latency-bound diagonal-block kernel overlaps the other's digit GEMMs,
-    // while each persistent GEMM launch still has enough tiles for the 148 SMs
+    // particle groups: measured on one B200 at N = 4096 (profiles/r02_bench_v4.json / v5, strong_scaling_slices_1gpu):
+    // two groups are within noise of the best setting at every swarm size (256 particles: 1 / 2 / 4 groups = 1311 / 1307 /
+    // 1286 evals/s; 32 particles: 1113-1127 / 1167-1199 / 1186-1194): one group's latency-bound diagonal-block kernel
+    // overlaps the other's digit GEMMs, while each persistent GEMM launch keeps enough tiles for the 148 SMs
     int G = g_timing ? 1 : g_groups;
     if (G > P / g_min_group) G = P / g_min_group;
-    if (!g_groups_explicit && G > 2 && P < 256) G = 2;
     if (G < 1) G = 1;
     if (G > 1 && ensure_group_streams(G)) return 1;
     auto fits = [&](int pw) { const int pg = (pw + G - 1) / G; return (size_t)G * blocked_layout(pg, N, d, emu).total <= workspace_bytes; };
@@ -678,13 +676,12 @@ int gpk_oz_gemm_tn(const void* A, const void* B, int M, int N, int K, const doub
 
 int gpk_set_groups(int groups, int min_particles_per_group) {
     if (groups == 0 && min_particles_per_group == 0) {        // back to the built-in rule
-        g_groups = 4; g_min_group = 16; g_groups_explicit = false;
+        g_groups = 2; g_min_group = 16;
         return 0;
     }
     if (groups < 1 || groups > MAX_GROUPS || min_particles_per_group < 1) { set_error("gpk_set_groups: groups 1..%d, at least 1 particle per group", MAX_GROUPS); return 2; }
     g_groups = groups;
     g_min_group = min_particles_per_group;
-    g_groups_explicit = true;
     return 0;
 }
 

@@ -161,10 +161,9 @@ GPK_API int gpk_sum_gaussians(const double* y, int n, const double* gaus, int ng
                       void* stream);
 
 /* Scheduling knob, process-wide, results do not depend on it: gpk_loss_batched splits a swarm on the blocked path into at
- * most `groups` particle groups on concurrent streams (default 4, 1..8), each of at least `min_particles_per_group`
+ * most `groups` particle groups on concurrent streams (default 2, 1..8), each of at least `min_particles_per_group`
  * particles (default 16: smaller groups leave the persistent digit-GEMM launches of late block columns with fewer tiles
- * than SMs); swarms of fewer than 256 particles use at most 2 groups unless this function was called).  (0, 0) restores the
- * built-in rule. */
+ * than SMs).  (0, 0) restores the defaults. */
 GPK_API int gpk_set_groups(int groups, int min_particles_per_group);
 
 /* Emulated-FP64 primitives (used by the blocked path in the GPK_PREC_EMU* modes, exposed for tests and measurement).
