@@ -266,9 +266,11 @@ def measure_fp64_peak(torch, dev):
 
 
 # DRAM bytes per launch of the digit-GEMM roles, from the ncu launch list of this command (dram__bytes_read.sum +
-# dram__bytes_write.sum, mean over the launches of one role; 64-particle groups): profiles/r01_launch_summary_v12.csv
-NCU_TRAFFIC_PROFILE = "profiles/r01_launch_summary_v12.csv (ncu launch list of the bench command, 64-particle group launches)"
-NCU_TRAFFIC_PER_LAUNCH = {"k_oz_invu": 1409.57e6 + 219.37e6, "k_oz_syrk": 1445.11e6 + 107.60e6}
+# dram__bytes_write.sum, mean over the launches of one role; 128-particle groups): profiles/r02_launch_summary_dram.csv
+NCU_TRAFFIC_PROFILE = ("profiles/r02_launch_summary_dram.csv (ncu launch list of the bench command, round-2 code, default two "
+                       "groups of 128 particles: mean over the captured launches of the role)")
+NCU_TRAFFIC_GROUP = 128
+NCU_TRAFFIC_PER_LAUNCH = {"k_oz_invu": 2819.19e6 + 462.36e6, "k_oz_syrk": 2876.18e6 + 225.17e6}
 
 
 def dram_traffic(kernel, N, P, launches):
@@ -285,11 +287,16 @@ def dram_traffic(kernel, N, P, launches):
         per_matrix += T * 128 * 128 * 8                         # FP64 copy of the diagonal Schur blocks only
     else:
         per_matrix += sum(range(T)) * 128 * 128 * (8 + 7)       # FP64 output tile + its digits for the next contraction
-    return {"traffic": NCU_TRAFFIC_PER_LAUNCH[kernel],
-            "traffic_unit": "DRAM bytes per launch (64-particle group)",
+    # avg_launch_ms comes from the instrumented step, which runs the whole slice as ONE group (events after every launch need
+    # one stream); DRAM bytes scale linearly with the particles of a launch (each particle has its own operands), so the ncu
+    # figure of the 128-particle launches is scaled to that launch size: both fields describe the same launch
+    scale = P / NCU_TRAFFIC_GROUP
+    return {"traffic": NCU_TRAFFIC_PER_LAUNCH[kernel] * scale,
+            "traffic_unit": f"DRAM bytes per launch of {P} particles (the instrumented step's launches) = {scale:g} x the "
+                            f"{NCU_TRAFFIC_GROUP}-particle launches ncu measured",
             "traffic_measured_in_run": False,
             "traffic_from_profile": NCU_TRAFFIC_PROFILE,
-            "algorithmic_bytes_per_launch": per_matrix * 64 / (T - 1)}
+            "algorithmic_bytes_per_launch": per_matrix * P / (T - 1)}
 
 
 def aux_measurements(torch, engine):
