@@ -27,6 +27,7 @@ SIGNATURES = {
     "gpk_fit": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "gpk_predict_workspace_bytes": (_sz, [_i, _i]),
     "gpk_predict": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _ll, _vp, _vp, _i, _vp, _sz, _vp]),
+    "gpk_predict_static": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _ll, _vp, _vp, _vp]),
     "gpk_predict_state_bytes": (_sz, [_i]),
     "gpk_predict_prepare": (_i, [_vp, _vp, _i, _vp, _sz, _vp]),
     "gpk_predict_emu_workspace_bytes": (_sz, [_i, _i]),

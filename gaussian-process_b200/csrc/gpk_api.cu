@@ -593,6 +593,68 @@ int gpk_predict(const double* W, const double* alpha, const double* xs, const do
     return 0;
 }
 
+// ---- prediction without any allocation (no counterpart in the reference) ----
+// Scratch of the native prediction chain for one chunk of GPK_STATIC_CHUNK grid points against at most GPK_STATIC_MAX_N
+// known points, in a file-scope device array: K_*^T [chunk][Np] doubles, then the per-block partial sums [T][chunk].
+// Every GPU that loads the library holds these 4.03 MiB until the process exits.
+constexpr size_t STATIC_KST_BYTES = (size_t)GPK_STATIC_CHUNK * GPK_STATIC_MAX_N * 8;
+constexpr size_t STATIC_PARTIAL_BYTES = (size_t)(GPK_STATIC_MAX_N / NB) * GPK_STATIC_CHUNK * 8;
+static __device__ __align__(256) unsigned char g_static_scratch[STATIC_KST_BYTES + STATIC_PARTIAL_BYTES];
+
+// In host code `g_static_scratch` is a host-side stand-in, not a device address: the address a kernel may use comes from
+// cudaGetSymbolAddress, asked once per device with that device current.
+constexpr int STATIC_MAX_DEVICES = 64;
+static std::mutex g_static_mu;
+static unsigned char* g_static_ptr[STATIC_MAX_DEVICES] = {};
+
+static unsigned char* static_scratch_for_current_device() {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= STATIC_MAX_DEVICES) {
+        set_error("gpk_predict_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (g_static_ptr[dev] == nullptr) {
+        unsigned char* ptr = nullptr;
+        e = cudaGetSymbolAddress((void**)&ptr, g_static_scratch);
+        if (e != cudaSuccess || ptr == nullptr) {
+            set_error("gpk_predict_static: cudaGetSymbolAddress on device %d: %s", dev, cudaGetErrorString(e));
+            return nullptr;
+        }
+        g_static_ptr[dev] = ptr;
+    }
+    return g_static_ptr[dev];
+}
+
+int gpk_predict_static(const double* W, const double* alpha, const double* xs, const double* sq, const double* ls, int N,
+                       int d, const double* Xfit, long long M, double* mu_out, double* sd_out, void* stream) {
+    if (bad_dims("gpk_predict_static", N, d, 0)) return 2;
+    if (N > GPK_STATIC_MAX_N) {
+        set_error("gpk_predict_static: N=%d exceeds GPK_STATIC_MAX_N=%d (the static scratch holds %d x %d doubles); "
+                  "use gpk_predict with a caller-provided workspace", N, GPK_STATIC_MAX_N, GPK_STATIC_CHUNK, GPK_STATIC_MAX_N);
+        return 2;
+    }
+    if (M <= 0) return 0;
+    unsigned char* scratch = static_scratch_for_current_device();
+    if (scratch == nullptr) return 1;
+    cudaStream_t st = (cudaStream_t)stream;
+    set_stream(st);
+    const int Np = round_up(N, NB), T = Np / NB;
+    double* KsT = (double*)scratch;
+    double* partial = (double*)(scratch + STATIC_KST_BYTES);
+    // nothing has to start at zero: k_cross_cov writes all Bp x Np entries of K_*^T (zero rows for the padding points),
+    // k_predict_gemm all T x Bp partial sums, before the next kernel of the chain reads them
+    for (long long m0 = 0; m0 < M; m0 += GPK_STATIC_CHUNK) {
+        const int B = (int)((M - m0 < GPK_STATIC_CHUNK) ? (M - m0) : GPK_STATIC_CHUNK);
+        const int Bp = round_up(B, NB);
+        if (launch_cross_cov(xs, sq, ls, alpha, N, Np, d, Xfit, M, m0, B, Bp, KsT, mu_out, st)) return 1;
+        if (launch_predict_gemm(W, Np, T, KsT, Bp, partial, st)) return 1;
+        if (launch_predict_finalize(partial, T, Bp, B, sd_out + m0, st)) return 1;
+    }
+    return 0;
+}
+
 size_t gpk_predict_state_bytes(int N) { return oz_pred_state_bytes(round_up(N, NB)); }
 
 int gpk_predict_prepare(const double* W, const double* e, int N, void* state, size_t state_bytes, void* stream) {

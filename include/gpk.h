@@ -129,6 +129,21 @@ GPK_API int gpk_predict(const double* W, const double* alpha, const double* xs, 
                 int N, int d, const double* Xfit, long long M, double* mu_out, double* sd_out, int chunk,
                 void* workspace, size_t workspace_bytes, void* stream);
 
+/* (c) gpk_predict for callers that cannot allocate.  No counterpart in the reference: added
+ *     for code under CUDA-graph capture, tight serving loops and harnesses that forbid cudaMalloc.  Same
+ *     arguments, kernels and results as gpk_predict with chunk = GPK_STATIC_CHUNK, but the scratch (K_*^T of one chunk and the
+ *     partial sums, 4.03 MiB) is a file-scope `static __device__` array inside the library: the call allocates nothing (no
+ *     cudaMalloc / cudaFree, no allocating library routine) and takes no workspace.  Every GPU that loads the library holds
+ *     the array until the process exits.  Limit: N <= GPK_STATIC_MAX_N known points (status 2 beyond it, with an
+ *     explanation in gpk_last_error_string(); use gpk_predict there); M is unlimited (chunks run one after the other).
+ *     Every call on a device shares the one array, which keeps the previous call's contents (nothing in it has to start at
+ *     zero: each element is written before it is read within a call).  Calls that overlap on the GPU -- two streams, two host
+ *     threads, two graphs replayed concurrently -- RACE on it: serialise them on one stream. */
+#define GPK_STATIC_MAX_N 2048
+#define GPK_STATIC_CHUNK 256
+GPK_API int gpk_predict_static(const double* W, const double* alpha, const double* xs, const double* sq, const double* ls,
+                               int N, int d, const double* Xfit, long long M, double* mu_out, double* sd_out, void* stream);
+
 /* (c) the same prediction with |W k_*|^2 on the int8 tcgen05 digit GEMM (emulated FP64, see GPK_PREC_*):
  *     gpk_predict_prepare slices the fitted W once into a caller-owned state buffer (needs e > 0), gpk_predict_emu then
  *     builds the digits of each K_* chunk on the fly (no FP64 K_* in HBM) and reduces the squares in the epilogue.
