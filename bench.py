@@ -41,7 +41,7 @@ INT8_PEAK_SOURCE = ("int8 tcgen05.mma issue-rate probe on this pool's B200 (tool
                     "sustained figure is reported beside it as peak_from_measured_peaks")
 METRIC = "pso_loss_evals_per_sec_n4096"
 UNIT = "loss_evals/s"
-PRODUCTS = {"emu": 34, "emu28": 28, "emu21": 21, "emu15": 15}
+PRODUCTS = {"emu": 34, "emu28": 28, "emu21": 21, "emu15": 15, "emu28_34": 31, "emu34_28": 31}
 
 
 def measured_peaks():
@@ -809,7 +809,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-aux", action="store_true", help="skip the C4 / C5 / prediction / surface / scaling-slice measurements")
     ap.add_argument("--no-native", action="store_true", help="skip the short runs in the other arithmetic modes")
-    ap.add_argument("--precision", default="emu", choices=["fp64", "emu", "emu28", "emu21", "emu15"],
+    ap.add_argument("--precision", default="emu", choices=["fp64", "emu", "emu28", "emu21", "emu15", "emu28_34", "emu34_28"],
                     help="fp64: native DMMA contractions; emu: FP64 emulated on the int8 tcgen05 tensor cores "
                          "(34 digit products); emu28 / emu21 / emu15: fewer digit products (checked a posteriori)")
     args = ap.parse_args()

@@ -80,12 +80,20 @@ static int groups_of(int precision) {
         case GPK_PREC_EMU28: return 7;
         case GPK_PREC_EMU21: return 6;
         case GPK_PREC_EMU15: return 5;
+        case GPK_PREC_EMU28_34: return 7;       // Cholesky phase (the inverse phase and the prediction GEMM use inverse_groups_of)
+        case GPK_PREC_EMU34_28: return 8;
         default: return 0;
     }
 }
+// digit groups of the inverse phase (and of the prediction GEMM): the mixed modes differ from groups_of here
+static int inverse_groups_of(int precision) {
+    if (precision == GPK_PREC_EMU28_34) return 8;
+    if (precision == GPK_PREC_EMU34_28) return 7;
+    return groups_of(precision);
+}
 static bool bad_precision(const char* who, int precision, int N) {
-    if (precision < GPK_PREC_FP64 || precision > GPK_PREC_EMU15) {
-        set_error("%s: precision %d (0 native FP64, 1..4 emulated FP64 with 34 / 28 / 21 / 15 digit products)", who, precision);
+    if (precision < GPK_PREC_FP64 || precision > GPK_PREC_EMU34_28) {
+        set_error("%s: precision %d (0 native FP64, 1..4 emulated FP64 with 34 / 28 / 21 / 15 digit products, 5 / 6 mixed 28+34 / 34+28)", who, precision);
         return true;
     }
     if (precision != GPK_PREC_FP64 && round_up(N, NB) >= 16384) {
@@ -371,7 +379,7 @@ size_t gpk_loss_workspace_bytes(int P, int N, int d, int precision) {
 static int blocked_pass(const double* X, const double* y, const double* e, const double* lsp, const unsigned char* act,
                         const double* sigma_vals, int Pc, int N, int d, int S, int* counts, int* info, double* resid_out,
                         double* sig_out, char* ws, const BlockedLayout& L, int emu, bool probe, double tol,
-                        int zero_inactive, cudaStream_t gs) {
+                        int zero_inactive, cudaStream_t gs, int inv_groups = 0) {
     OzBuffers oz;
     if (emu) {
         oz = oz_buffers(ws, L);
@@ -395,7 +403,11 @@ static int blocked_pass(const double* X, const double* y, const double* e, const
     if (launch_cov_lower(xs, sq, e, Pc, N, L.Np, d, mat, pkv, act, gs)) return 1;
     if (probe && launch_probe_sum(pkv, L.Np, L.T, Pc, pu, act, gs)) return 1;
     if (factor_phase(mat, L.Np, L.T, Pc, dinv, dinvT, info, act, DIAG_WRITE_INVERSE, oz, gs)) return 1;
-    if (inverse_phase(mat, L.Np, L.T, Pc, dinvT, mt, act, oz, gs)) return 1;
+    const int fac_groups = oz_get_groups();
+    if (emu && inv_groups) oz_set_groups(inv_groups);           // mixed modes: another digit-product count for the inverse
+    const int rc_inv = inverse_phase(mat, L.Np, L.T, Pc, dinvT, mt, act, oz, gs);
+    if (emu && inv_groups) oz_set_groups(fac_groups);
+    if (rc_inv) return 1;
     if (launch_wy(mat, L.Np, N, Pc, y, z, pu, pt, act, gs)) return 1;
     if (launch_colnorm_alpha(mat, L.Np, Pc, z, cn, alpha, pt, pw, act, gs)) return 1;
     return launch_counts(alpha, cn, e, sigma_vals, Pc, N, L.Np, S, counts, resid_out, sig_out, pw, tol,
@@ -474,7 +486,8 @@ int gpk_loss_batched(const double* X, const double* y, const double* e, const do
             int* cnt = counts_out + (size_t)q0 * S;
             double* rs = resid_out ? resid_out + (size_t)q0 * N : nullptr;
             double* sg = sig_out ? sig_out + (size_t)q0 * N : nullptr;
-            if (blocked_pass(X, y, e, lsp, act, sigma_vals, Pc, N, d, S, cnt, info + q0, rs, sg, ws, L, emu, probe, tol, zero_inactive, gs)) return 1;
+            if (blocked_pass(X, y, e, lsp, act, sigma_vals, Pc, N, d, S, cnt, info + q0, rs, sg, ws, L, emu, probe, tol, zero_inactive, gs,
+                             emu ? inverse_groups_of(precision) : 0)) return 1;
             if (probe_out && cudaMemcpyAsync(probe_out + q0, ws + L.probe, (size_t)Pc * 8, cudaMemcpyDeviceToDevice, gs) != cudaSuccess) { set_error("copy of the probe values failed"); return 1; }
             if (fallback_out) {
                 cudaError_t ce = probe ? cudaMemcpyAsync(fallback_out + q0, ws + L.fail, (size_t)Pc, cudaMemcpyDeviceToDevice, gs)
@@ -556,6 +569,7 @@ int gpk_fit(const double* X, const double* y, const double* e, const double* ls,
     if (launch_cov_lower(xs_out, sq_out, e, 1, N, Np, d, W_out, probe ? pkv : nullptr, nullptr, st)) return 1;
     if (probe && launch_probe_sum(pkv, Np, T, 1, pu, nullptr, st)) return 1;
     if (factor_phase(W_out, Np, T, 1, dinv, dinvT, info, nullptr, DIAG_WRITE_INVERSE, oz, st)) return 1;
+    if (emu) oz_set_groups(inverse_groups_of(precision));
     if (inverse_phase(W_out, Np, T, 1, dinvT, mt, nullptr, oz, st)) return 1;
     if (launch_wy(W_out, Np, N, 1, y, z, probe ? pu : nullptr, pt, nullptr, st)) return 1;
     if (launch_colnorm_alpha(W_out, Np, 1, z, cn, alpha_out, probe ? pt : nullptr, pw, nullptr, st)) return 1;
@@ -676,7 +690,7 @@ int gpk_predict_emu(const void* state, const double* alpha, const double* xs, co
         if (precision == GPK_PREC_FP64) set_error("gpk_predict_emu: an emulated precision (GPK_PREC_EMU*) is required; gpk_predict is the native path");
         return 2;
     }
-    oz_set_groups(groups_of(precision));
+    oz_set_groups(inverse_groups_of(precision));
     if (M <= 0) return 0;
     if (workspace_bytes < gpk_predict_emu_workspace_bytes(N, chunk)) { set_error("gpk_predict_emu: workspace too small"); return 3; }
     cudaStream_t st = (cudaStream_t)stream;

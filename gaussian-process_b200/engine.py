@@ -61,7 +61,7 @@ def to_dev(a, dtype=None):
 #   "emu21"  6 digits, 21 products;  "emu15"  5 digits, 15 products -- for use under the a-posteriori check below
 #   "auto"   "emu" when every e_i is finite and > 0 and N >= 1024 (below that the native kernels are faster:
 #            profiles/r01_mode_crossover.log), else "fp64"                        (default; env GPK_PRECISION)
-_MODES = {"fp64": 0, "emu": 1, "emu28": 2, "emu21": 3, "emu15": 4}
+_MODES = {"fp64": 0, "emu": 1, "emu28": 2, "emu21": 3, "emu15": 4, "emu28_34": 5, "emu34_28": 6}
 MODE_NAMES = {v: k for k, v in _MODES.items()}
 EMU_MIN_N = 1024
 EMU_MAX_N = 16256             # contraction length below 2^14: the int32 sums of 8 digit products of 2^14 each cannot overflow

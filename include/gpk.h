@@ -48,6 +48,10 @@ extern "C" {
 #define GPK_PREC_EMU28 2
 #define GPK_PREC_EMU21 3
 #define GPK_PREC_EMU15 4
+/* mixed: 28 products in the Cholesky phase + 34 in the inverse phase (5), and the other way round (6); measured in
+ * DESIGN.md 3.2 */
+#define GPK_PREC_EMU28_34 5
+#define GPK_PREC_EMU34_28 6
 
 /* `flags` argument of gpk_loss_batched (bit mask).
  *   GPK_FLAG_REFERENCE_FORM  which algebraic form of the self-prediction the loss uses.  Clear: the reduced form,

@@ -151,7 +151,7 @@ def test_adversarial_milder_cases_meet_the_reference(eng, name, cond):
     assert fbck == int(np.sum(pck > 1e-10))
 
 
-@pytest.mark.parametrize("mode", ["emu28", "emu21", "emu15"])
+@pytest.mark.parametrize("mode", ["emu28", "emu21", "emu15", "emu28_34", "emu34_28"])
 def test_reduced_digit_modes_are_checked(eng, mode):
     """Fewer digit products (28 / 21 / 15) under the a-posteriori check: whatever the mode, the result that comes back is
     either within the bar (probe <= 1e-10) or the native FP64 one."""
