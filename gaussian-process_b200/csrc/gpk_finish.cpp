@@ -39,16 +39,22 @@ double pairwise_sum(const double* a, long long n) {
 extern "C" int gpk_finish_wasserstein(const int* counts, long long P, int S, const double* measured_of, int n_points,
                                       const double* expected, const double* d_sigma, double* scratch, double* out) {
     if (P < 0 || S < 2 || n_points < 1 || !counts || !measured_of || !expected || !d_sigma || !scratch || !out) return 2;
-    double* y = scratch;              // S values
-    double* t = scratch + S;          // S - 1 terms
+    double* t = scratch;              // S - 1 terms (scratch holds 2 S doubles for older callers; S - 1 are used)
     for (long long p = 0; p < P; ++p) {
         const int* c = counts + p * (long long)S;
-        for (int s = 0; s < S; ++s) {
-            const int k = c[s];
-            if (k < 0 || k > n_points) return 3;
-            y[s] = std::fabs(measured_of[k] - expected[s]);
+        // one pass: y_s = |measured - expected| and t_s = d_s * (y_{s+1} + y_s) / 2.0 (NumPy's operation order; the division by
+        // 2.0 is exact either way); a count outside 0..n_points is remembered and reported after the loop
+        unsigned bad = (unsigned)c[0] > (unsigned)n_points;
+        double y_prev = std::fabs(measured_of[bad ? 0 : c[0]] - expected[0]);
+        for (int s = 1; s < S; ++s) {
+            const unsigned k = (unsigned)c[s];
+            const unsigned oob = k > (unsigned)n_points;
+            bad |= oob;
+            const double y_cur = std::fabs(measured_of[oob ? 0u : k] - expected[s]);
+            t[s - 1] = d_sigma[s - 1] * (y_cur + y_prev) / 2.0;
+            y_prev = y_cur;
         }
-        for (int s = 0; s + 1 < S; ++s) t[s] = d_sigma[s] * (y[s + 1] + y[s]) / 2.0;
+        if (bad) return 3;
         out[p] = pairwise_sum(t, S - 1);
     }
     return 0;

@@ -74,6 +74,57 @@ struct SmallSmem {
 // FORM 0: reduced form (above).  FORM 1: the reference's own formulae (GP_func.py:36-40, find_len_scales.py:161-163):
 // mu = K_s^T alpha, v = L^-1 K_s, var = 1 - sum_rows v^2, pull = (mu - y) / max(sd s, 1e-12) -- the cancellations of the
 // reference are reproduced (K_s is rebuilt over the factor in shared memory, L^-1 is applied as the explicit inverse).
+// Lower triangle of kernel_func(x, x) (+ diag(e^2) when dv != nullptr) into the shared staging array, Lm[r][c], c <= r < N
+// (GP_func.py:49-65, :21), shared evenly by the 256 threads of the CTA: rows i and N - 1 - i are folded into one row of
+// N + 1 elements, a thread takes every 256th element of the folded array, four independent chains at a time.  (Each thread
+// evaluating the 64 elements of the 8 x 8 tile it owns instead runs 64 exp() latency chains back to back in the threads of the
+// diagonal tiles while most of the CTA idles: 64 k cycles of a 227 k cycle kernel at N = 100, profiles/r02_small_profile.log.)
+// Same expressions per element as before: bit-identical values.
+__device__ __forceinline__ void small_cov_to_smem(const double (*xs)[NB], const double* __restrict__ sq,
+                                                  const double* __restrict__ dv, int N, int d, double* __restrict__ Lm) {
+    const int W = N + 1, total = ((N + 1) >> 1) * W;
+    for (int e0 = threadIdx.x; e0 < total; e0 += 4 * 256) {
+        int r[4], c[4];
+        bool ok[4];
+        double dot[4], val[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int e = e0 + 256 * u;
+            ok[u] = e < total;
+            const int i = ok[u] ? e / W : 0;
+            const int j = ok[u] ? e - i * W : 0;
+            if (j <= i) { r[u] = i; c[u] = j; }
+            else { r[u] = N - 1 - i; c[u] = j - i - 1; ok[u] = ok[u] && (r[u] != i); }      // odd N: the middle row once
+            dot[u] = __dmul_rn(xs[0][r[u]], xs[0][c[u]]);
+        }
+        for (int dd = 1; dd < d; ++dd) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) dot[u] = fma(xs[dd][r[u]], xs[dd][c[u]], dot[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            double sd = __dsub_rn(__dadd_rn(sq[r[u]], sq[c[u]]), __dmul_rn(2.0, dot[u]));
+            sd = fmax(sd, 0.0);
+            val[u] = exp(__dmul_rn(-0.5, sd));
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (ok[u]) {
+                if (dv != nullptr && r[u] == c[u]) val[u] = __dadd_rn(val[u], dv[r[u]]);
+                Lm[r[u] * CI_LD + c[u]] = val[u];
+            }
+        }
+    }
+}
+
+#ifdef GPK_SMALL_PROFILE
+// instrumented build only (tools/small_profile.py): clock64 at the phase boundaries of CTA 0
+__device__ long long g_small_prof[16];
+#define SMALL_PROF(i) do { __syncthreads(); if (blockIdx.x == 0 && threadIdx.x == 0) g_small_prof[i] = clock64(); } while (0)
+#else
+#define SMALL_PROF(i)
+#endif
+
 template <int FORM>
 __global__ void __launch_bounds__(256, 1)
 k_small_loss(const double* __restrict__ X, const double* __restrict__ y, const double* __restrict__ e,
@@ -99,6 +150,7 @@ k_small_loss(const double* __restrict__ X, const double* __restrict__ y, const d
         for (int k = tid; k < S; k += 256) counts[(size_t)p * S + k] = 0;
         return;
     }
+    SMALL_PROF(0);
     if (tid < N) {
         double acc = 0.0;
         for (int dd = 0; dd < d; ++dd) {
@@ -115,7 +167,11 @@ k_small_loss(const double* __restrict__ X, const double* __restrict__ y, const d
     for (int k = tid; k <= S; k += 256) hist[k] = 0;
     __syncthreads();
 
-    // K + diag(e^2): each thread builds its 8x8 register tile of the lower triangle (zero elsewhere)
+    SMALL_PROF(1);
+    // K + diag(e^2): built by all threads into the staging array, then each thread loads its 8x8 register tile of the lower
+    // triangle (zero elsewhere)
+    small_cov_to_smem(xs, sq, dv, N, d, Lm);
+    __syncthreads();
     double E[8][8];
     {
         const int R0 = (tid >> 4) * 8, C0 = (tid & 15) * 8;
@@ -124,22 +180,17 @@ k_small_loss(const double* __restrict__ X, const double* __restrict__ y, const d
 #pragma unroll
             for (int cc = 0; cc < 8; ++cc) {
                 const int r = R0 + rr, c = C0 + cc;
-                double val = 0.0;
-                if (c <= r && r < N) {
-                    double dot = __dmul_rn(xs[0][r], xs[0][c]);
-                    for (int dd = 1; dd < d; ++dd) dot = fma(xs[dd][r], xs[dd][c], dot);
-                    double s = __dsub_rn(__dadd_rn(sq[r], sq[c]), __dmul_rn(2.0, dot));
-                    s = fmax(s, 0.0);
-                    val = exp(__dmul_rn(-0.5, s));
-                    if (r == c) val = __dadd_rn(val, dv[r]);
-                }
-                E[rr][cc] = val;
+                E[rr][cc] = (c <= r && r < N) ? Lm[r * CI_LD + c] : 0.0;
             }
     }
+    __syncthreads();                     // the staging array is rewritten by chol_inv_dump
+    SMALL_PROF(2);
     const int bad = chol_inv_regs(E, N, col, xr);
     if (bad && tid == 0) info[p] = bad;
+    SMALL_PROF(3);
     chol_inv_dump(E, xr, Lm);
     __syncthreads();
+    SMALL_PROF(4);
 
     // z = W y  (W[k][c] = Lm[c][k+1])
     if (tid < N) {
@@ -149,6 +200,7 @@ k_small_loss(const double* __restrict__ X, const double* __restrict__ y, const d
         zv[k] = acc;
     }
     __syncthreads();
+    SMALL_PROF(5);
     double cn = 0.0, al = 0.0;
     if (tid < N) {
         const int i = tid;
@@ -177,22 +229,7 @@ k_small_loss(const double* __restrict__ X, const double* __restrict__ y, const d
         double* alv = col;                          // scratch of the factorisation, free now
         double* muv = col + NB;
         if (tid < N) alv[tid] = al;
-        {
-            const int R0 = (tid >> 4) * 8, C0 = (tid & 15) * 8;
-#pragma unroll
-            for (int rr = 0; rr < 8; ++rr)
-#pragma unroll
-                for (int cc = 0; cc < 8; ++cc) {
-                    const int r = R0 + rr, c = C0 + cc;
-                    if (c <= r && r < N) {
-                        double dot = __dmul_rn(xs[0][r], xs[0][c]);
-                        for (int dd = 1; dd < d; ++dd) dot = fma(xs[dd][r], xs[dd][c], dot);
-                        double sdist = __dsub_rn(__dadd_rn(sq[r], sq[c]), __dmul_rn(2.0, dot));
-                        sdist = fmax(sdist, 0.0);
-                        Lm[r * CI_LD + c] = exp(__dmul_rn(-0.5, sdist));
-                    }
-                }
-        }
+        small_cov_to_smem(xs, sq, nullptr, N, d, Lm);
         __syncthreads();
         if (tid >= NB && tid - NB < N) {            // mu_i = sum_c K_s[c][i] alpha_c                       GP_func.py:36
             const int i = tid - NB;
@@ -221,7 +258,9 @@ k_small_loss(const double* __restrict__ X, const double* __restrict__ y, const d
         }
     }
     __syncthreads();
+    SMALL_PROF(6);
     prefix_and_store(hist, S, counts + (size_t)p * S);
+    SMALL_PROF(7);
 }
 
 int launch_small_loss(const double* X, const double* y, const double* e, const double* ls,
@@ -502,3 +541,10 @@ int launch_predict_finalize(const double* partial, int T, int Bp, int B, double*
 }
 
 }  // namespace gpk
+
+#ifdef GPK_SMALL_PROFILE
+extern "C" __attribute__((visibility("default"))) int gpk_debug_small_prof(long long* out16) {
+    if (cudaDeviceSynchronize() != cudaSuccess) return 1;
+    return cudaMemcpyFromSymbol(out16, gpk::g_small_prof, sizeof(long long) * 16) == cudaSuccess ? 0 : 1;
+}
+#endif

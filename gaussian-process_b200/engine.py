@@ -277,6 +277,7 @@ class LossContext:
         self._pin_pos = None
         self._dev_pos = None
         self._pin_counts = None
+        self._packed = None
         self._mode_key = None
         self._graphs = {}
         self.fallbacks = 0
@@ -398,6 +399,9 @@ class LossContext:
         positions = np.atleast_2d(_f64(positions))
         p = positions.shape[0]
         dev = device()
+        plain = not want_detail and not want_probe and self._sig_unsort is None
+        if plain and not (GRAPH_MIN_N < self.n <= GRAPH_MAX_N and _graphs_enabled()):
+            return self._counts_packed(positions, active, p, dev)
         if self._pin_pos is None or self._pin_pos.shape[0] != p or self._dev_pos.device != dev:
             self._pin_pos = torch.empty((p, self.d), dtype=torch.float64).pin_memory()
             self._pin_act = torch.empty(p, dtype=torch.uint8).pin_memory()
@@ -422,6 +426,49 @@ class LossContext:
         self.evaluated += int(self._np_act.sum())
         self.fallbacks += int(self._np_fb.sum())
         return self._np_counts, self._np_info, (out[2:] if want_detail else None)
+
+    def _counts_packed(self, positions, active, p, dev):
+        """The PSO loop's evaluation (counts and status only, direct launches): the inputs of a call travel as ONE block
+        [positions | active] and its outputs as ONE block [counts | info | fallback flags], both preallocated with the
+        context: one copy up, one launch, one copy down, one synchronise per swarm evaluation (was two copies up, three
+        allocations and three copies down: 25 us of a 300 us iteration at the reference's PSO size,
+        profiles/r02_pso_host_profile.log)."""
+        pk = self._packed
+        if pk is None or pk["p"] != p or pk["dev"] != dev:
+            n_in = p * self.d * 8 + p
+            o_info = p * self.s * 4
+            o_fb = o_info + p * 4
+            n_out = o_fb + p
+            pin_in = torch.empty(n_in, dtype=torch.uint8).pin_memory()
+            pin_out = torch.empty(n_out, dtype=torch.uint8).pin_memory()
+            dev_in = torch.empty(n_in, dtype=torch.uint8, device=dev)
+            dev_out = torch.empty(n_out, dtype=torch.uint8, device=dev)
+            pk = self._packed = {
+                "p": p, "dev": dev, "pin_in": pin_in, "pin_out": pin_out, "dev_in": dev_in, "dev_out": dev_out,
+                "np_pos": pin_in[:p * self.d * 8].view(torch.float64).view(p, self.d).numpy(),
+                "np_act": pin_in[p * self.d * 8:].numpy(),
+                "np_counts": pin_out[:o_info].view(torch.int32).view(p, self.s).numpy(),
+                "np_info": pin_out[o_info:o_fb].view(torch.int32).numpy(),
+                "np_fb": pin_out[o_fb:].numpy(),
+                "d_pos": dev_in.data_ptr(), "d_act": dev_in.data_ptr() + p * self.d * 8,
+                "d_counts": dev_out.data_ptr(), "d_info": dev_out.data_ptr() + o_info, "d_fb": dev_out.data_ptr() + o_fb,
+                "fb_view": dev_out[o_fb:]}
+        stream = torch.cuda.current_stream(dev.index)
+        pk["np_pos"][...] = positions              # (the previous evaluation ended with a synchronize: staging is free)
+        pk["np_act"][...] = 1 if active is None else np.asarray(active, dtype=np.uint8)
+        pk["dev_in"].copy_(pk["pin_in"], non_blocking=True)
+        ws = self._ws(p)
+        st = self.lib.gpk_loss_batched(
+            self.x.data_ptr(), self.y.data_ptr(), self.e.data_ptr(), pk["d_pos"], pk["d_act"], self.sig.data_ptr(), p, self.n,
+            self.d, self.s, self.mode, self._form(), _check_tol if self.mode != 0 else 0.0, pk["d_counts"], pk["d_info"],
+            None, None, None, pk["d_fb"], ws.data_ptr(), ws.numel(), stream.cuda_stream)
+        _lib.check(st, "gpk_loss_batched")
+        pk["pin_out"].copy_(pk["dev_out"], non_blocking=True)
+        stream.synchronize()
+        self.last_fallback, self.last_probe = pk["fb_view"], None
+        self.evaluated += int(pk["np_act"].sum())
+        self.fallbacks += int(pk["np_fb"].sum())
+        return pk["np_counts"], pk["np_info"], None
 
 
 # ------------------------------------------------------------------------------------ (b)+(c)

@@ -81,6 +81,7 @@ class SwarmLoss:
         self._work = None
         self._table = np.arange(self.n + 1, dtype=np.int32).astype(np.float64) / self.n      # counts / n, every value
         self._scratch = np.empty(2 * self.sigma_vals.shape[0])
+        self._fin = None
 
     def _integral(self, counts):
         """np.trapz(|counts / n - expected|, sigma_vals, axis=1) by libgpk's host routine (gpk_finish_wasserstein: NumPy's
@@ -89,13 +90,17 @@ class SwarmLoss:
         key = counts.shape[1]
         if _FAST_FINISH.get(key) is False or counts.dtype != np.int32 or not counts.flags.c_contiguous:
             return None
-        import ctypes as C
-        lib = engine._lib.load()
-        out = np.empty(counts.shape[0])
-        vp = C.c_void_p
-        st = lib.gpk_finish_wasserstein(vp(counts.ctypes.data), counts.shape[0], counts.shape[1], vp(self._table.ctypes.data),
-                                        self.n, vp(self.expected.ctypes.data), vp(self._d_sigma.ctypes.data),
-                                        vp(self._scratch.ctypes.data), vp(out.ctypes.data))
+        fin = self._fin
+        if fin is None or fin[0] != counts.shape[0]:
+            import ctypes as C
+            out = np.empty(counts.shape[0])
+            vp = C.c_void_p
+            fin = self._fin = (counts.shape[0], engine._lib.load().gpk_finish_wasserstein, out, vp(self._table.ctypes.data),
+                               vp(self.expected.ctypes.data), vp(self._d_sigma.ctypes.data), vp(self._scratch.ctypes.data),
+                               vp(out.ctypes.data))
+        _p, fn, out, p_table, p_exp, p_dsig, p_scr, p_out = fin
+        st = fn(counts.ctypes.data, counts.shape[0], counts.shape[1], p_table, self.n, p_exp, p_dsig, p_scr, p_out)
+        out = out.copy()
         if st != 0:
             _FAST_FINISH[key] = False
             return None
