@@ -149,12 +149,125 @@ __device__ __forceinline__ int chol_inv_regs(double (&E)[8][8], int n, double* w
     return bad;
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Thread -> tile maps.  MAP 0 (chol_inv_regs, chol_inv_blocked): tile row = tid / 16, tile column = tid % 16.  MAP 1
+// (chol_inv_lookahead): the 16 tiles of a tile column belong to ONE warp -- tile column = 2 * warp + lane / 16, tile row =
+// lane % 16 -- so that everything only the owners of a column do (scaling, pivot root, publishing) is executed by one warp
+// instead of by two lanes of each of the eight.
+template <int MAP>
+__device__ __forceinline__ void ci_tile_of(int tid, int& tr, int& tc) {
+    if (MAP == 0) { tr = tid >> 4; tc = tid & 15; }
+    else { tr = tid & 15; tc = ((tid >> 5) << 1) + ((tid >> 4) & 1); }
+}
+
+// Look-ahead form of chol_inv_regs: same contract, same operations on every element in the same order (bit-identical
+// results), different schedule.  ncu source counters of chol_inv_regs (profiles/r02_ncu_diag_source.md): of 242 warp
+// instructions per warp and column only 64 are the update FMAs; 80 are the publish block and 30 the pivot's root and
+// reciprocal, executed by all eight warps with two active lanes each, on the critical path before the block barrier.  Here
+//   * the owners of a column are one warp (MAP 1): the other seven skip that code;
+//   * the owners of column j + 1 apply step j to that column only, take the root of its pivot and publish it (into the other
+//     generation of the published vectors) BEFORE their remaining 56 FMAs of step j: when the other warps arrive at the next
+//     barrier the column is there.
+// The published vectors are stored as [r % 8][r / 8] so that the 16 tile rows of a warp read and write consecutive doubles.
+template <bool FAST = false>
+__device__ __forceinline__ int chol_inv_lookahead(double (&E)[8][8], int n, double* work, double* xd) {
+    double* dgs = work + 6 * NB;             // initial diagonal
+    double* piv = work + 7 * NB;             // pivot of step j at piv[j & 1]
+    const int tid = threadIdx.x;
+    int tr, tc;
+    ci_tile_of<1>(tid, tr, tc);
+    const int R0 = tr * 8, C0 = tc * 8;
+    int bad = 0;
+    if (tr == tc) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) dgs[R0 + k] = E[k][k];
+    }
+    __syncthreads();
+    double pv[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) pv[k] = dgs[C0 + k];
+    // column jn (in-tile index jjn) of this thread's tile, already updated by every step < jn: scale it and publish it
+    auto publish = [&](int jn, int jjn_rt, double pivot) {
+        double s, inv;
+        pivot_root<FAST>(pivot, s, inv);
+        double* v = work + (jn & 1) * 3 * NB;
+        double* vcm = v + NB;
+        double* vup = v + 2 * NB;
+        if (tr == 0) piv[jn & 1] = pivot;
+#pragma unroll
+        for (int rr = 0; rr < 8; ++rr) {
+            const int r = R0 + rr;
+            double t = 0.0;
+#pragma unroll
+            for (int cc = 0; cc < 8; ++cc) {              // jjn_rt is a compile-time constant at every call site
+                if (cc == jjn_rt) {
+                    if (r == jn) { E[rr][cc] = s; t = inv; xd[r] = inv; }
+                    else { t = E[rr][cc] * inv; E[rr][cc] = t; }
+                }
+            }
+            const int ti = rr * 16 + tr;
+            v[ti] = t;
+            vcm[ti] = (r > jn) ? t : 0.0;
+            vup[ti] = (r <= jn) ? t : 0.0;
+        }
+    };
+    if (tc == 0) publish(0, 0, pv[0]);
+    for (int jb = 0; jb * 8 < n; ++jb) {
+#pragma unroll
+        for (int jj = 0; jj < 8; ++jj) {
+            const int j = jb * 8 + jj;
+            if (j < n) {                               // uniform over the CTA
+                const double* v = work + (j & 1) * 3 * NB;
+                const double* vcm = v + NB;
+                const double* vup = v + 2 * NB;
+                __syncthreads();                       // column j is published
+                if (!(piv[j & 1] > 0.0) && bad == 0) bad = j + 1;
+                if (C0 + 7 > j) {                      // columns <= j are final
+                    double vc[8];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) vc[k] = vcm[k * 16 + tc];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) pv[k] = fma(-vc[k], vc[k], pv[k]);
+                    const bool live = !(tc > tr && R0 > j);      // tiles above the diagonal whose rows are all > j have not started
+                    const double* row_lo = (tc > tr) ? vup : v;  // row multiplier of the elements with c <= r
+                    const double* row_up = (tc < tr) ? v : vup;  // ... and of those with c > r
+                    double lo[8], up[8];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) { lo[k] = row_lo[k * 16 + tr]; up[k] = row_up[k * 16 + tr]; }
+                    const int jn = j + 1;
+                    const int jjn = (jj + 1) & 7;                // compile-time after unrolling
+                    const bool own_next = ((jn >> 3) == tc) && jn < n;
+                    if (own_next) {                              // one warp (16 lanes): look ahead
+#pragma unroll
+                        for (int rr = 0; rr < 8; ++rr)
+                            E[rr][jjn] = fma(-((jjn <= rr) ? lo[rr] : up[rr]), vc[jjn], E[rr][jjn]);
+                        publish(jn, jjn, pv[jjn]);
+                    }
+                    if (live) {
+#pragma unroll
+                        for (int rr = 0; rr < 8; ++rr)
+#pragma unroll
+                            for (int cc = 0; cc < 8; ++cc)
+                                if (cc != jjn || !own_next)
+                                    E[rr][cc] = fma(-((cc <= rr) ? lo[rr] : up[rr]), vc[cc], E[rr][cc]);
+                    }
+                }
+            }
+        }
+    }
+    __syncthreads();                                   // the callers reuse the scratch and read xd
+    return bad;
+}
+
 // Dump the register tiles into the shared staging array in the layout the consumers read:
 //   L[r][c] (c <= r) at Lm[r][c];   X[i][c] (c < i) at Lm[c][i + 1];   X[i][i] at Lm[i][i + 1].
+template <int MAP = 0>
 __device__ __forceinline__ void chol_inv_dump(const double (&E)[8][8], const double* __restrict__ xd,
                                               double* __restrict__ Lm) {
     const int tid = threadIdx.x;
-    const int R0 = (tid >> 4) * 8, C0 = (tid & 15) * 8;
+    int tr, tc;
+    ci_tile_of<MAP>(tid, tr, tc);
+    const int R0 = tr * 8, C0 = tc * 8;
 #pragma unroll
     for (int rr = 0; rr < 8; ++rr) {
         const int r = R0 + rr;

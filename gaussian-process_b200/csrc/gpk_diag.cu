@@ -7,16 +7,19 @@
 
 namespace gpk {
 
+constexpr int DIAG_DEFAULT_VARIANT = 3;
 constexpr int DIAG_WORK = (CBK_WORK > CI_WORK) ? CBK_WORK : CI_WORK;
 constexpr size_t DIAG_SMEM_BYTES = (size_t)NB * CI_LD * sizeof(double) + (size_t)(DIAG_WORK + NB) * sizeof(double);
 
-// VARIANT 0: one column per step, correctly rounded pivot roots (round 1); 1: panels of 8 columns, exact roots; 2: one
-// column per step with the short reciprocal-square-root chain.  Measured on C2 (N = 1024, 64 particles,
-// profiles/r02_ab_diag.md): 54.9 / 77.7 / 53.2 us per launch, all three bit-identical on the test problems.  A column step
-// costs ~0.43 us whatever the variant: the 64 update FMAs per thread (256 cycles of the SM's FP64 pipe per step when every
-// tile is active) plus the publish -> barrier -> load round trip, not the root chain (3 % from shortening it) and not the
-// barrier alone (the panel form trades it for shuffles and shared-memory stores of the same cost).  Variant 0 stays the
-// default: its roots are the correctly rounded ones of the reference's LAPACK path.
+// VARIANT 0: one column per step, owners of a column spread over the eight warps (round 1); 1: panels of 8 columns in one
+// warp; 2: as 0 with the short reciprocal-square-root chain; 3 (default): look-ahead schedule with warp-owned columns
+// (chol_inv_lookahead), correctly rounded pivot roots as the reference's LAPACK path; 4: as 3 with the short root chain.
+// All five give the same bits on the test problems (0, 1 and 3 by construction: same operations in the same order per
+// element).  Measured on C2 (N = 1024, 64 particles, profiles/r02_ab_diag_la_v*.json), real launches: 107 / 152 / 103 /
+// 83 / 77 us.  What the ncu source counters showed for variant 0 (profiles/r02_ncu_diag_source.md): 242 warp instructions
+// per warp and column, of which 64 are the update FMAs, 80 the publish block and 30 the pivot's root and reciprocal --
+// executed by every warp with two active lanes, before the barrier.  In variant 3 one warp owns a column; it is then the
+// critical path by itself (root ~400 cycles, its own 56 FMAs, the publish: ~900 cycles per column).
 template <int VARIANT>
 __global__ void __launch_bounds__(256, 1)
 k_diag_block(double* __restrict__ mat, int Np, int J, double* __restrict__ dinv, double* __restrict__ dinvT,
@@ -33,8 +36,11 @@ k_diag_block(double* __restrict__ mat, int Np, int J, double* __restrict__ dinv,
     // each thread loads its 8x8 register tile of the lower triangle (the X part starts at zero)
     double* xd = xr;
     double E[8][8];
+    constexpr int MAP = (VARIANT >= 3) ? 1 : 0;
     {
-        const int R0 = (tid >> 4) * 8, C0 = (tid & 15) * 8;
+        int tr, tc;
+        ci_tile_of<MAP>(tid, tr, tc);
+        const int R0 = tr * 8, C0 = tc * 8;
 #pragma unroll
         for (int rr = 0; rr < 8; ++rr)
 #pragma unroll
@@ -46,9 +52,11 @@ k_diag_block(double* __restrict__ mat, int Np, int J, double* __restrict__ dinv,
     int bad;
     if (VARIANT == 1) bad = chol_inv_blocked(E, work, xd);
     else if (VARIANT == 2) bad = chol_inv_regs<true>(E, NB, work, xd);
+    else if (VARIANT == 3) bad = chol_inv_lookahead<false>(E, NB, work, xd);
+    else if (VARIANT == 4) bad = chol_inv_lookahead<true>(E, NB, work, xd);
     else bad = chol_inv_regs<false>(E, NB, work, xd);
     if (bad && tid == 0) atomicCAS(&info[p], 0, J * NB + bad);
-    chol_inv_dump(E, xd, Lm);
+    chol_inv_dump<MAP>(E, xd, Lm);
     __syncthreads();
 
     double* dI = dinv + ((size_t)p * T + J) * NB * NB;
@@ -66,19 +74,20 @@ k_diag_block(double* __restrict__ mat, int Np, int J, double* __restrict__ dinv,
 
 int launch_diag_block(double* mat, int Np, int J, int P, double* dinv, double* dinvT, int T, int* info,
                       const unsigned char* active, int mode, cudaStream_t st) {
-    static int variant = -1;          // GPK_DIAG_VARIANT = 0 | 1 | 2 (A/B runs and tests); default 0
+    static int variant = -1;          // GPK_DIAG_VARIANT = 0 .. 4 (A/B runs and tests)
     if (variant < 0) {
         const char* v = getenv("GPK_DIAG_VARIANT");
-        const int want = (v && atoi(v) >= 0 && atoi(v) <= 2) ? atoi(v) : 0;
-        cudaError_t e = want == 0 ? cudaFuncSetAttribute(k_diag_block<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DIAG_SMEM_BYTES)
-                      : want == 1 ? cudaFuncSetAttribute(k_diag_block<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DIAG_SMEM_BYTES)
-                                  : cudaFuncSetAttribute(k_diag_block<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DIAG_SMEM_BYTES);
+        const int want = (v && atoi(v) >= 0 && atoi(v) <= 4) ? atoi(v) : DIAG_DEFAULT_VARIANT;
+        cudaError_t e = cudaSuccess;
+#define GPK_DIAG_ATTR(V) case V: e = cudaFuncSetAttribute(k_diag_block<V>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DIAG_SMEM_BYTES); break
+        switch (want) { GPK_DIAG_ATTR(0); GPK_DIAG_ATTR(1); GPK_DIAG_ATTR(2); GPK_DIAG_ATTR(3); default: GPK_DIAG_ATTR(4); }
+#undef GPK_DIAG_ATTR
         if (e != cudaSuccess) { set_error("k_diag_block smem attr: %s", cudaGetErrorString(e)); return 1; }
         variant = want;
     }
-    if (variant == 0) k_diag_block<0><<<P, 256, DIAG_SMEM_BYTES, st>>>(mat, Np, J, dinv, dinvT, T, info, active, mode);
-    else if (variant == 1) k_diag_block<1><<<P, 256, DIAG_SMEM_BYTES, st>>>(mat, Np, J, dinv, dinvT, T, info, active, mode);
-    else k_diag_block<2><<<P, 256, DIAG_SMEM_BYTES, st>>>(mat, Np, J, dinv, dinvT, T, info, active, mode);
+#define GPK_DIAG_GO(V) case V: k_diag_block<V><<<P, 256, DIAG_SMEM_BYTES, st>>>(mat, Np, J, dinv, dinvT, T, info, active, mode); break
+    switch (variant) { GPK_DIAG_GO(0); GPK_DIAG_GO(1); GPK_DIAG_GO(2); GPK_DIAG_GO(3); default: GPK_DIAG_GO(4); }
+#undef GPK_DIAG_GO
     return check_launch("k_diag_block");
 }
 

@@ -12,6 +12,8 @@
 // contributes to all scales from its first passing index on: histogram of first indices + prefix sum.
 #include "gpk_cholinv.cuh"
 
+#include <cstdlib>
+
 namespace gpk {
 
 // first index k in [0, S) with  a <= max(fl(sd * s_k), 1e-12);  S if none
@@ -55,6 +57,7 @@ __device__ __forceinline__ void resid_sigma(double d, double alpha, double cn, d
 // ---------------------------------------------------------------------------------------------
 // Small-N fused loss: covariance, Cholesky, inverse, alpha, counts -- one CTA per particle, all in
 // shared memory (the reference's real PSO size: N <= 100 after the KMeans cap, find_len_scales.py:24-47).
+constexpr int SMALL_DEFAULT_VARIANT = 1;
 struct SmallSmem {
     static constexpr size_t lm = 0;
     static constexpr size_t col = lm + (size_t)NB * CI_LD * 8;
@@ -125,7 +128,9 @@ __device__ long long g_small_prof[16];
 #define SMALL_PROF(i)
 #endif
 
-template <int FORM>
+// LA: the factorisation's schedule -- 0 chol_inv_regs (one column per step, owners spread over the warps), 1 chol_inv_lookahead
+// (warp-owned columns, next column published ahead of the bulk update; bit-identical results)
+template <int FORM, int LA>
 __global__ void __launch_bounds__(256, 1)
 k_small_loss(const double* __restrict__ X, const double* __restrict__ y, const double* __restrict__ e,
              const double* __restrict__ ls, const unsigned char* __restrict__ active,
@@ -174,7 +179,9 @@ k_small_loss(const double* __restrict__ X, const double* __restrict__ y, const d
     __syncthreads();
     double E[8][8];
     {
-        const int R0 = (tid >> 4) * 8, C0 = (tid & 15) * 8;
+        int tr, tc;
+        ci_tile_of<LA>(tid, tr, tc);
+        const int R0 = tr * 8, C0 = tc * 8;
 #pragma unroll
         for (int rr = 0; rr < 8; ++rr)
 #pragma unroll
@@ -185,10 +192,10 @@ k_small_loss(const double* __restrict__ X, const double* __restrict__ y, const d
     }
     __syncthreads();                     // the staging array is rewritten by chol_inv_dump
     SMALL_PROF(2);
-    const int bad = chol_inv_regs(E, N, col, xr);
+    const int bad = LA ? chol_inv_lookahead<false>(E, N, col, xr) : chol_inv_regs<false>(E, N, col, xr);
     if (bad && tid == 0) info[p] = bad;
     SMALL_PROF(3);
-    chol_inv_dump(E, xr, Lm);
+    chol_inv_dump<LA>(E, xr, Lm);
     __syncthreads();
     SMALL_PROF(4);
 
@@ -266,21 +273,21 @@ k_small_loss(const double* __restrict__ X, const double* __restrict__ y, const d
 int launch_small_loss(const double* X, const double* y, const double* e, const double* ls,
                       const unsigned char* active, const double* sigma_vals, int P, int N, int d, int S,
                       int* counts, int* info, double* resid_out, double* sig_out, int form, cudaStream_t st) {
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t er = cudaFuncSetAttribute(k_small_loss<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                              (int)SmallSmem::total);
-        if (er == cudaSuccess)
-            er = cudaFuncSetAttribute(k_small_loss<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SmallSmem::total);
+    static int la = -1;               // GPK_SMALL_VARIANT = 0 | 1 (A/B runs): schedule of the factorisation
+    if (la < 0) {
+        const char* v = getenv("GPK_SMALL_VARIANT");
+        const int want = (v && (atoi(v) == 0 || atoi(v) == 1)) ? atoi(v) : SMALL_DEFAULT_VARIANT;
+        cudaError_t er = cudaFuncSetAttribute(k_small_loss<0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SmallSmem::total);
+        if (er == cudaSuccess) er = cudaFuncSetAttribute(k_small_loss<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SmallSmem::total);
+        if (er == cudaSuccess) er = cudaFuncSetAttribute(k_small_loss<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SmallSmem::total);
+        if (er == cudaSuccess) er = cudaFuncSetAttribute(k_small_loss<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SmallSmem::total);
         if (er != cudaSuccess) { set_error("k_small_loss smem attr: %s", cudaGetErrorString(er)); return 1; }
-        configured = true;
+        la = want;
     }
-    if (form)
-        k_small_loss<1><<<P, 256, SmallSmem::total, st>>>(X, y, e, ls, active, sigma_vals, N, d, S, counts, info,
-                                                          resid_out, sig_out);
-    else
-        k_small_loss<0><<<P, 256, SmallSmem::total, st>>>(X, y, e, ls, active, sigma_vals, N, d, S, counts, info,
-                                                          resid_out, sig_out);
+#define GPK_SMALL_GO(F, L) k_small_loss<F, L><<<P, 256, SmallSmem::total, st>>>(X, y, e, ls, active, sigma_vals, N, d, S, counts, info, resid_out, sig_out)
+    if (form) { if (la) GPK_SMALL_GO(1, 1); else GPK_SMALL_GO(1, 0); }
+    else { if (la) GPK_SMALL_GO(0, 1); else GPK_SMALL_GO(0, 0); }
+#undef GPK_SMALL_GO
     return check_launch(form ? "k_small_loss_ref_form" : "k_small_loss");
 }
 
