@@ -707,6 +707,31 @@ int gpk_predict_emu(const void* state, const double* alpha, const double* xs, co
     return 0;
 }
 
+size_t gpk_pso_layout(int P, int d, int S, int n_points, int max_iter, int max_evals, long long rng_len,
+                      unsigned long long* offsets_out) {
+    if (P < 1 || d < 1 || d > MAX_D || S < 2 || S > MAX_S || n_points < 1 || max_iter < 0 || max_evals < 1 || rng_len < 0) return 0;
+    const PsoLayout L = pso_layout(P, d, S, n_points, max_iter, max_evals, rng_len);
+    if (offsets_out) {
+        const size_t o[GPK_PSO_N_OFFSETS] = {L.scalars, L.lower, L.upper, L.vmax, L.pos, L.vel, L.pbest_pos, L.pbest_sc, L.gbest_pos,
+                                             L.scores, L.expected, L.d_sigma, L.measured_of, L.log_best, L.log_stall,
+                                             L.log_restart, L.trace_pos, L.trace_sc, L.rng};
+        for (int i = 0; i < GPK_PSO_N_OFFSETS; ++i) offsets_out[i] = o[i];
+    }
+    return L.total;
+}
+
+int gpk_pso_step(void* state, size_t state_bytes, int P, int d, int S, int n_points, int max_iter, int max_evals,
+                 long long rng_len, const int* counts, const int* info, const unsigned char* fallback, double* positions_out,
+                 unsigned char* active_out, void* stream) {
+    const size_t need = gpk_pso_layout(P, d, S, n_points, max_iter, max_evals, rng_len, nullptr);
+    if (need == 0) { set_error("gpk_pso_step: unsupported sizes P=%d d=%d S=%d", P, d, S); return 2; }
+    if (state == nullptr || state_bytes < need) { set_error("gpk_pso_step: state buffer too small (%zu < %zu)", state_bytes, need); return 3; }
+    if (!counts || !info || !positions_out || !active_out) { set_error("gpk_pso_step: null argument"); return 2; }
+    set_stream((cudaStream_t)stream);
+    return launch_pso_step((unsigned char*)state, pso_layout(P, d, S, n_points, max_iter, max_evals, rng_len), P, S, counts, info,
+                           fallback, positions_out, active_out, (cudaStream_t)stream);
+}
+
 int gpk_prob_surface(const double* table, long long R, int ncols, int npoints, double* y_out, double* p_out,
                      int* valid_out, void* stream) {
     if (npoints < 1) { set_error("gpk_prob_surface: npoints=%d", npoints); return 2; }

@@ -152,6 +152,15 @@ int launch_probe_value(const double* pw, int N, int Np, int P, double* probe, un
 int launch_clear_info(int* info, const unsigned char* mask, int P, cudaStream_t st);
 int launch_predict_finalize(const double* partial, int T, int Bp, int B, double* sigma_out, cudaStream_t st);
 
+// gpk_pso.cu -- device-resident swarm loop: byte offsets of the state buffer (include/gpk.h gpk_pso_layout)
+struct PsoLayout {
+    size_t scalars, lower, upper, vmax, pos, vel, pbest_pos, pbest_sc, gbest_pos, scores, expected, d_sigma, measured_of,
+           log_best, log_stall, log_restart, trace_pos, trace_sc, rng, total;
+};
+PsoLayout pso_layout(int P, int d, int S, int n_points, int max_iter, int max_evals, long long rng_len);
+int launch_pso_step(unsigned char* state, const PsoLayout& L, int P, int S, const int* counts, const int* info,
+                    const unsigned char* fallback, double* pos_out, unsigned char* active_out, cudaStream_t st);
+
 // gpk_surface.cu
 int launch_prob_surface(const double* table, long long R, int ncols, int npoints,
                         double* y_out, double* p_out, int* valid_out, cudaStream_t st);

@@ -158,6 +158,109 @@ def swarm_bounds(x_known):
     return lower, upper
 
 
+PSO_HDR_WORDS = 32            # include/gpk.h gpk_pso_layout: int32 header of the state buffer
+_HDR = {"P": 0, "d": 1, "S": 2, "n_points": 3, "max_iter": 4, "patience": 5, "max_evals": 6, "iter": 7, "pending": 8,
+        "stall": 9, "restarts": 10, "n_evals": 11, "error": 12, "rng_cursor": 13, "fallbacks": 14, "rng_len": 15, "logged": 16}
+_OFFS = ("scalars", "lower", "upper", "vmax", "pos", "vel", "pbest_pos", "pbest_sc", "gbest_pos", "scores", "expected",
+         "d_sigma", "measured_of", "log_best", "log_stall", "log_restart", "trace_pos", "trace_sc", "rng")
+
+
+def device_loop_enabled():
+    import os
+    return os.environ.get("GPK_PSO_DEVICE", "1") != "0"
+
+
+def _device_swarm_loop(x_known, y_known, e_known, positions, lower, upper, v_max, sigma_vals, expected, num_particles,
+                       max_iter, patience, inertia_decay):
+    """The swarm loop of find_len_scales.py:76-141 without a host round trip per iteration: max_evals pairs of
+    (gpk_loss_batched, gpk_pso_step) are enqueued on the current stream and the state is read back once.  The random
+    numbers the reference would draw from np.random during the loop are generated up front with the same generator and
+    consumed on the device in the same order; afterwards the global np.random state is left exactly where the host loop
+    would have left it.  Returns a dict with the final state, the per-iteration log and the trace of every evaluation."""
+    import ctypes as C
+    import torch
+    lib = engine._lib.load()
+    P, d = positions.shape
+    n = x_known.shape[1]
+    S = sigma_vals.shape[0]
+    max_restarts = (max_iter // patience + 1) if patience >= 1 else max_iter
+    max_evals = 1 + max_iter + max_restarts
+    rng_len = (2 * max_iter + max_restarts) * P * d
+    offs = (C.c_ulonglong * len(_OFFS))()
+    total = lib.gpk_pso_layout(P, d, S, n, max_iter, max_evals, rng_len, offs)
+    if total == 0:
+        raise ValueError(f"swarm of {P} particles in {d} dimensions with {S} sigma scales is outside the kernels' limits")
+    off = dict(zip(_OFFS, (int(v) for v in offs)))
+    ctx = engine.LossContext(x_known, y_known, e_known, sigma_vals)
+    if ctx._sig_unsort is not None:
+        return None                                  # unsorted sigma grid: the host loop handles the permutation
+    # ---- initial state (everything up to the logs), one upload
+    rng_state = np.random.get_state()
+    stream_vals = np.random.random_sample(rng_len)
+    host = np.zeros(total, dtype=np.uint8)
+    hdr = host[:PSO_HDR_WORDS * 4].view(np.int32)
+    for k, v in (("P", P), ("d", d), ("S", S), ("n_points", n), ("max_iter", max_iter), ("patience", patience),
+                 ("max_evals", max_evals), ("rng_len", rng_len)):
+        hdr[_HDR[k]] = v
+
+    def f64(name, count):
+        return host[off[name]:off[name] + 8 * count].view(np.float64)
+
+    f64("scalars", 8)[1] = inertia_decay
+    f64("lower", d)[:] = lower
+    f64("upper", d)[:] = upper
+    f64("vmax", d)[:] = v_max
+    f64("pos", P * d)[:] = positions.reshape(-1)
+    f64("expected", S)[:] = expected
+    f64("d_sigma", S)[:S - 1] = np.diff(sigma_vals)
+    f64("measured_of", n + 1)[:] = np.arange(n + 1, dtype=np.int32).astype(np.float64) / n      # counts / n as NumPy divides
+    f64("rng", rng_len)[:] = stream_vals
+    dev = engine.device()
+    state = torch.from_numpy(host).to(dev)
+    d_pos = torch.from_numpy(np.ascontiguousarray(positions)).to(dev)
+    oob0 = out_of_bounds_mask(positions, lower, upper)
+    d_act = torch.from_numpy((~oob0).astype(np.uint8)).to(dev)
+    counts = torch.zeros((P, S), dtype=torch.int32, device=dev)
+    info = torch.zeros(P, dtype=torch.int32, device=dev)
+    fb = torch.zeros(P, dtype=torch.uint8, device=dev)
+    ws = ctx._ws(P)
+    st = torch.cuda.current_stream(dev.index).cuda_stream
+    tol = engine.get_check_tol() if ctx.mode != 0 else 0.0
+    loss_args = (ctx.x.data_ptr(), ctx.y.data_ptr(), ctx.e.data_ptr(), d_pos.data_ptr(), d_act.data_ptr(), ctx.sig.data_ptr(),
+                 P, n, d, S, ctx.mode, ctx._form(), tol, counts.data_ptr(), info.data_ptr(), None, None, None, fb.data_ptr(),
+                 ws.data_ptr(), ws.numel(), st)
+    step_args = (state.data_ptr(), total, P, d, S, n, max_iter, max_evals, rng_len, counts.data_ptr(), info.data_ptr(),
+                 fb.data_ptr(), d_pos.data_ptr(), d_act.data_ptr(), st)
+    loss, step = lib.gpk_loss_batched, lib.gpk_pso_step
+    for _ in range(max_evals):
+        rc = loss(*loss_args)
+        if rc == 0:
+            rc = step(*step_args)
+        if rc != 0:
+            engine._lib.check(rc, "device swarm loop")
+    out = state.cpu().numpy()
+    hdr = out[:PSO_HDR_WORDS * 4].view(np.int32)
+
+    def g64(name, count):
+        return out[off[name]:off[name] + 8 * count].view(np.float64)
+
+    n_evals = int(hdr[_HDR["n_evals"]])
+    consumed = int(hdr[_HDR["rng_cursor"]])
+    np.random.set_state(rng_state)                   # leave the global stream where the host loop would have left it
+    if consumed:
+        np.random.random_sample(consumed)
+    return {
+        "error": int(hdr[_HDR["error"]]), "restarts": int(hdr[_HDR["restarts"]]), "n_evals": n_evals,
+        "fallbacks": int(hdr[_HDR["fallbacks"]]), "iters_logged": min(int(hdr[_HDR["logged"]]), max_iter),
+        "gbest_pos": g64("gbest_pos", d).copy(), "gbest_score": float(g64("scalars", 8)[0]),
+        "log_best": g64("log_best", max_iter).copy(),
+        "log_stall": out[off["log_stall"]:off["log_stall"] + 4 * max_iter].view(np.int32).copy(),
+        "log_restart": out[off["log_restart"]:off["log_restart"] + 4 * max_iter].view(np.int32).copy(),
+        "trace_pos": g64("trace_pos", max_evals * P * d).reshape(max_evals, P, d)[:n_evals].copy(),
+        "trace_sc": g64("trace_sc", max_evals * P).reshape(max_evals, P)[:n_evals].copy(),
+    }
+
+
 def len_scale_opt(x_known, y_known, e_known, PSO_progress, *, num_particles=40, max_iter=500, patience=100,
                   max_points=100, inertia_decay=0.002, lhs_random_state=None, swarm_fn=None, trace=None,
                   distributed=None, timings=None):
@@ -206,12 +309,36 @@ def len_scale_opt(x_known, y_known, e_known, PSO_progress, *, num_particles=40, 
         positions, rng_state = sharding.broadcast_object((positions, np.random.get_state()))
         positions = np.array(positions, dtype=np.float64)
         np.random.set_state(rng_state)
-    evaluate = swarm_fn if swarm_fn is not None else SwarmLoss(
-        x_known, y_known, e_known, sigma_vals, expected_percents, lower_bounds, upper_bounds)
     if distributed is None:
         distributed = in_group and sharding.worth_sharding(num_particles, x_known.shape[1])
-    if distributed and in_group:
-        evaluate = sharding.ShardedSwarm(evaluate)
+    sharded = bool(distributed and in_group)
+    dev_run = None
+    if swarm_fn is None and not sharded and device_loop_enabled():
+        # the whole loop on the device (one kernel pair per swarm evaluation, no host round trip): same trajectory, bit
+        # for bit, as the host loop below, which stays for sharded swarms, `swarm_fn` and GPK_PSO_DEVICE=0
+        dev_run = _device_swarm_loop(x_known, y_known, e_known, positions, lower_bounds, upper_bounds, v_max, sigma_vals,
+                                     expected_percents, num_particles, max_iter, patience, inertia_decay)
+    if dev_run is not None:
+        if trace is not None:
+            for k in range(dev_run["n_evals"]):
+                trace.append((dev_run["trace_pos"][k].copy(), dev_run["trace_sc"][k].copy()))
+        for i in range(dev_run["iters_logged"]):
+            if PSO_progress and i % 20 == 0:
+                print(f"Iter {i}: Best Score = {dev_run['log_best'][i]:.6f}, No Improve = {int(dev_run['log_stall'][i])}")
+            if dev_run["log_restart"][i] and PSO_progress:
+                print(f"Stagnation at iter {i}, soft-restarting swarm...")
+        if dev_run["error"] == 1:
+            raise np.linalg.LinAlgError("Matrix is not positive definite")   # GP_func.py:22 behaviour
+        if dev_run["error"]:
+            raise RuntimeError("device swarm loop: random stream exhausted (more restarts than max_iter // patience + 1)")
+        gbest_pos, gbest_score, restart_count = dev_run["gbest_pos"], np.float64(dev_run["gbest_score"]), dev_run["restarts"]
+        max_iter = 0                                 # the loop below has nothing left to do
+        evaluate = None
+    else:
+        evaluate = swarm_fn if swarm_fn is not None else SwarmLoss(
+            x_known, y_known, e_known, sigma_vals, expected_percents, lower_bounds, upper_bounds)
+        if sharded:
+            evaluate = sharding.ShardedSwarm(evaluate)
 
     def scored(p):
         s = np.asarray(evaluate(p), dtype=np.float64)
@@ -219,11 +346,12 @@ def len_scale_opt(x_known, y_known, e_known, PSO_progress, *, num_particles=40, 
             trace.append((p.copy(), s.copy()))
         return s
 
-    pbest_scores = scored(positions)
-    pbest_pos = positions.copy()
-    g = np.argmin(pbest_scores)
-    gbest_pos = pbest_pos[g].copy()
-    gbest_score = pbest_scores[g]
+    if dev_run is None:
+        pbest_scores = scored(positions)
+        pbest_pos = positions.copy()
+        g = np.argmin(pbest_scores)
+        gbest_pos = pbest_pos[g].copy()
+        gbest_score = pbest_scores[g]
     stall = 0
 
     for i in range(max_iter):

@@ -159,6 +159,31 @@ GPK_API int gpk_predict_emu(const void* state, const double* alpha, const double
                     int N, int d, int precision, const double* Xfit, long long M, double* mu_out, double* sd_out,
                     int chunk, void* workspace, size_t workspace_bytes, void* stream);
 
+/* (b) the swarm loop of len_scale_opt kept on the device, find_len_scales.py:76-141.  After every gpk_loss_batched of the
+ *     swarm, gpk_pso_step (one small kernel, asynchronous) finishes the scores from the counts (find_len_scales.py:163-177,182:
+ *     NumPy's operation order and pairwise summation, bit for bit what the host finish gives), absorbs them (personal and
+ *     global bests, stagnation counter, :79-83,106-125), and prepares the next evaluation (:88-100 velocity / position update of
+ *     the next iteration, or the soft restart of :123-141): it writes the next positions [P][d] and the in-bounds mask [P] that
+ *     the next gpk_loss_batched reads.  No host round trip per iteration: the caller enqueues max_evals pairs of calls and
+ *     reads the state back once.  Random numbers are taken from a stream the caller generated with NumPy's legacy generator
+ *     (np.random.random_sample), in the reference's order (two rand(P, d) per iteration, P d uniforms per restart), so the
+ *     trajectory is the host loop's.
+ *     State buffer (caller-allocated, gpk_pso_layout bytes): int32 header[32] = {P, d, S, n_points, max_iter, patience,
+ *     max_evals, iteration, pending (0 initial evaluation, 1 iteration, 2 restart re-evaluation, 3 done), stall, restarts,
+ *     evaluations recorded, error (1: covariance not positive definite, 2: random stream exhausted), random cursor, particles
+ *     that fell back to FP64, random stream length, iterations logged}, then the arrays at the byte offsets gpk_pso_layout reports, in this order:
+ *     scalars (gbest score, inertia decay), lower, upper, v_max [d], positions, velocities, personal best positions [P][d],
+ *     personal best scores [P], global best position [d], last scores [P], expected [S], diff(sigma_vals) [S] (S - 1 used),
+ *     measured_of [n_points + 1] (k / n_points as NumPy divides), per-iteration log: best score (f64), stall (i32), restarted
+ *     (i32) [max_iter], trace of every evaluation: positions [max_evals][P][d], scores [max_evals][P], random stream.
+ *     The caller fills everything up to the logs before the first call (positions = the initial swarm, pending = 0). */
+#define GPK_PSO_N_OFFSETS 19
+GPK_API size_t gpk_pso_layout(int P, int d, int S, int n_points, int max_iter, int max_evals, long long rng_len,
+                              unsigned long long* offsets_out);
+GPK_API int gpk_pso_step(void* state, size_t state_bytes, int P, int d, int S, int n_points, int max_iter, int max_evals,
+                         long long rng_len, const int* counts, const int* info, const unsigned char* fallback,
+                         double* positions_out, unsigned char* active_out, void* stream);
+
 /* (d) generate_prob_surf row loop, calc_prob_surf.py:67-81 + sum_gaussians :15-30.
  *     table: [R][ncols] payload columns of the merged frame (interleaved mean, std; non-finite = gap).
  *     valid[r] = 1 if the row emits output; y_out/p_out [R][npoints] are written for valid rows only. */
