@@ -332,7 +332,6 @@ def len_scale_opt(x_known, y_known, e_known, PSO_progress, *, num_particles=40, 
         if dev_run["error"]:
             raise RuntimeError("device swarm loop: random stream exhausted (more restarts than max_iter // patience + 1)")
         gbest_pos, gbest_score, restart_count = dev_run["gbest_pos"], np.float64(dev_run["gbest_score"]), dev_run["restarts"]
-        max_iter = 0                                 # the loop below has nothing left to do
         evaluate = None
     else:
         evaluate = swarm_fn if swarm_fn is not None else SwarmLoss(
@@ -354,7 +353,7 @@ def len_scale_opt(x_known, y_known, e_known, PSO_progress, *, num_particles=40, 
         gbest_score = pbest_scores[g]
     stall = 0
 
-    for i in range(max_iter):
+    for i in range(max_iter if dev_run is None else 0):          # host loop (the device loop above has done all of it)
         w = max(0.4, 0.9 - i * inertia_decay)
         c1 = c2 = 1.4
         r1 = np.random.rand(num_particles, ndim)

@@ -176,7 +176,8 @@ GPK_API int gpk_predict_emu(const void* state, const double* alpha, const double
  *     personal best scores [P], global best position [d], last scores [P], expected [S], diff(sigma_vals) [S] (S - 1 used),
  *     measured_of [n_points + 1] (k / n_points as NumPy divides), per-iteration log: best score (f64), stall (i32), restarted
  *     (i32) [max_iter], trace of every evaluation: positions [max_evals][P][d], scores [max_evals][P], random stream.
- *     The caller fills everything up to the logs before the first call (positions = the initial swarm, pending = 0). */
+ *     The caller fills everything up to the logs before the first call (positions = the initial swarm, pending = 0); the
+ *     header's P, d, S, n_points, max_iter, max_evals and random stream length must equal the arguments of every call. */
 #define GPK_PSO_N_OFFSETS 19
 GPK_API size_t gpk_pso_layout(int P, int d, int S, int n_points, int max_iter, int max_evals, long long rng_len,
                               unsigned long long* offsets_out);
