@@ -32,6 +32,7 @@ SIGNATURES = {
     "gpk_predict_prepare": (_i, [_vp, _vp, _i, _vp, _sz, _vp]),
     "gpk_predict_emu_workspace_bytes": (_sz, [_i, _i]),
     "gpk_predict_emu": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _ll, _vp, _vp, _i, _vp, _sz, _vp]),
+    "gpk_kmeans_step": (_i, [_vp, _i, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp]),
     "gpk_pso_layout": (_sz, [_i, _i, _i, _i, _i, _i, _ll, _vp]),
     "gpk_pso_step": (_i, [_vp, _sz, _i, _i, _i, _i, _i, _i, _ll, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gpk_prob_surface": (_i, [_vp, _ll, _i, _i, _vp, _vp, _vp, _vp]),

@@ -7,7 +7,7 @@ OUT=../libgpk.so
 FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -Xcompiler -fvisibility=hidden"
 mkdir -p build
 objs=()
-for f in gpk_api gpk_cov gpk_diag gpk_gemm gpk_loss gpk_oz gpk_pso gpk_surface; do
+for f in gpk_api gpk_cov gpk_diag gpk_gemm gpk_kmeans gpk_loss gpk_oz gpk_pso gpk_surface; do
   if [ ! -f build/$f.o ] || [ $f.cu -nt build/$f.o ] || [ gpk_common.cuh -nt build/$f.o ] || [ gpk_cholinv.cuh -nt build/$f.o ] || [ gpk_ozdig.cuh -nt build/$f.o ] || [ ../../include/gpk.h -nt build/$f.o ]; then
     $NVCC $FLAGS "$@" -c $f.cu -o build/$f.o &
   fi

@@ -707,6 +707,13 @@ int gpk_predict_emu(const void* state, const double* alpha, const double* xs, co
     return 0;
 }
 
+int gpk_kmeans_step(const double* X, int N, int d, const double* centers, const double* csq, int k, int* labels_inout,
+                    int* changed_out, double* sums_out, double* counts_out, void* stream) {
+    if (!X || !centers || !csq || !labels_inout || !changed_out || (sums_out && !counts_out)) { set_error("gpk_kmeans_step: null argument"); return 2; }
+    set_stream((cudaStream_t)stream);
+    return launch_kmeans_step(X, N, d, centers, csq, k, labels_inout, changed_out, sums_out, counts_out, (cudaStream_t)stream);
+}
+
 size_t gpk_pso_layout(int P, int d, int S, int n_points, int max_iter, int max_evals, long long rng_len,
                       unsigned long long* offsets_out) {
     if (P < 1 || d < 1 || d > MAX_D || S < 2 || S > MAX_S || n_points < 1 || max_iter < 0 || max_evals < 1 || rng_len < 0) return 0;

@@ -161,6 +161,10 @@ PsoLayout pso_layout(int P, int d, int S, int n_points, int max_iter, int max_ev
 int launch_pso_step(unsigned char* state, const PsoLayout& L, int P, int S, const int* counts, const int* info,
                     const unsigned char* fallback, double* pos_out, unsigned char* active_out, cudaStream_t st);
 
+// gpk_kmeans.cu -- E-step and cluster sums of one Lloyd iteration (include/gpk.h gpk_kmeans_step)
+int launch_kmeans_step(const double* X, int N, int d, const double* centers, const double* csq, int k, int* labels,
+                       int* changed, double* sums, double* counts, cudaStream_t st);
+
 // gpk_surface.cu
 int launch_prob_surface(const double* table, long long R, int ncols, int npoints,
                         double* y_out, double* p_out, int* valid_out, cudaStream_t st);

@@ -133,18 +133,29 @@ def evaluate_loss_batch(positions, x_known, y_known, e_known, sigma_vals, expect
     return SwarmLoss(x_known, y_known, e_known, sigma_vals, expected_percents, lower_bounds, upper_bounds)(positions)
 
 
-def kmeans_subsample(x_known, y_known, e_known, max_points):
-    """Host-side KMeans cap of find_len_scales.py:25-47 (sklearn, random_state=0)."""
-    from sklearn.cluster import KMeans
+def kmeans_subsample(x_known, y_known, e_known, max_points, backend=None):
+    """KMeans cap of find_len_scales.py:25-47: KMeans(n_clusters=max_points, n_init='auto', random_state=0) on the points,
+    then the member closest to each centroid.  backend "device" (default; env GPK_KMEANS): the Lloyd iterations run in
+    libgpk (kmeans.fit_predict: sklearn's labels and centres); "sklearn": the library itself on the host."""
+    import os
+    backend = backend or os.environ.get("GPK_KMEANS", "device")
     pts = x_known.T
-    km = KMeans(n_clusters=max_points, n_init='auto', random_state=0)
-    labels = km.fit_predict(pts)
+    if backend == "device":
+        from . import kmeans
+        labels, centers, _n_iter = kmeans.fit_predict(pts, max_points, random_state=0)
+    elif backend == "sklearn":
+        from sklearn.cluster import KMeans
+        km = KMeans(n_clusters=max_points, n_init='auto', random_state=0)
+        labels = km.fit_predict(pts)
+        centers = km.cluster_centers_
+    else:
+        raise ValueError(f"GPK_KMEANS / backend must be 'device' or 'sklearn' (got {backend!r})")
     chosen = []
     for k in range(max_points):
         members = np.where(labels == k)[0]
         if len(members) == 0:
             continue
-        dist2 = np.sum((pts[members] - km.cluster_centers_[k]) ** 2, axis=1)
+        dist2 = np.sum((pts[members] - centers[k]) ** 2, axis=1)
         chosen.append(members[np.argmin(dist2)])
     chosen = np.array(chosen)
     return x_known[:, chosen], y_known[chosen], e_known[chosen]

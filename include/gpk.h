@@ -159,6 +159,16 @@ GPK_API int gpk_predict_emu(const void* state, const double* alpha, const double
                     int N, int d, int precision, const double* Xfit, long long M, double* mu_out, double* sd_out,
                     int chunk, void* workspace, size_t workspace_bytes, void* stream);
 
+/* (N4) one Lloyd iteration of the KMeans subsample, find_len_scales.py:25-47 (sklearn.cluster.KMeans(...).fit_predict with
+ *     sklearn's single-threaded arithmetic).  X is [N][d] (points first, as sklearn holds them), centers [k][d], csq [k] their
+ *     squared norms.  E-step: labels_inout[i] = first j minimising csq_j - 2 <x_i, c_j>; *changed_out is set to 1 when a label
+ *     differs from the one the buffer held (the caller clears it; labels start at -1).  When sums_out != NULL the M-step sums
+ *     follow: sums_out[j] = sum of the members of cluster j in ascending sample order, counts_out[j] = their number (float64).
+ *     Everything on the centres' side (norms, empty clusters, averaging, shift, tolerance, k-means++ seeding) is the host's:
+ *     gaussian-process_b200/kmeans.py.  Limits: k <= 1024, d <= GPK_MAX_D. */
+GPK_API int gpk_kmeans_step(const double* X, int N, int d, const double* centers, const double* csq, int k,
+                            int* labels_inout, int* changed_out, double* sums_out, double* counts_out, void* stream);
+
 /* (b) the swarm loop of len_scale_opt kept on the device, find_len_scales.py:76-141.  After every gpk_loss_batched of the
  *     swarm, gpk_pso_step (one small kernel, asynchronous) finishes the scores from the counts (find_len_scales.py:163-177,182:
  *     NumPy's operation order and pairwise summation, bit for bit what the host finish gives), absorbs them (personal and

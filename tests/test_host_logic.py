@@ -30,7 +30,7 @@ def test_bounds_and_subsample_match_oracle():
     lo, hi = pso.swarm_bounds(x)
     lo2, hi2 = orc.pso_bounds(x)
     assert np.array_equal(lo, lo2) and np.array_equal(hi, hi2)
-    a = pso.kmeans_subsample(x, y, e, 100)
+    a = pso.kmeans_subsample(x, y, e, 100, backend="sklearn")      # the selection logic; the device backend: tests/test_gpu_kmeans.py
     b = orc.kmeans_subsample(x, y, e, 100)
     for u, v in zip(a, b):
         assert np.array_equal(u, v)
