@@ -244,12 +244,19 @@ __device__ __forceinline__ int chol_inv_lookahead(double (&E)[8][8], int n, doub
                         publish(jn, jjn, pv[jjn]);
                     }
                     if (live) {
+                        // column jjn was updated ahead by its owners; every other column unconditionally (jjn is a
+                        // compile-time constant here: no per-element test)
 #pragma unroll
                         for (int rr = 0; rr < 8; ++rr)
 #pragma unroll
                             for (int cc = 0; cc < 8; ++cc)
-                                if (cc != jjn || !own_next)
+                                if (cc != jjn)
                                     E[rr][cc] = fma(-((cc <= rr) ? lo[rr] : up[rr]), vc[cc], E[rr][cc]);
+                        if (!own_next) {
+#pragma unroll
+                            for (int rr = 0; rr < 8; ++rr)
+                                E[rr][jjn] = fma(-((jjn <= rr) ? lo[rr] : up[rr]), vc[jjn], E[rr][jjn]);
+                        }
                     }
                 }
             }
