@@ -12,9 +12,9 @@ arithmetic (the reference pins OMP / BLAS to one thread, GP_func.py:3-7).  Divis
   (`_kmeans_single_lloyd`, `_relocate_empty_clusters_dense`, `_average_centers`, `_center_shift`, `_tolerance`): k (d + 1)
   numbers per iteration.
 
-The host part was checked bit for bit against sklearn (labels, centres, iteration count) on 36 data sets with the E-step in
-NumPy, including duplicated points, fewer distinct points than clusters and N = k; the GPU test does the same for the
-whole on the B200 box (tests/test_gpu_kmeans.py)."""
+The host part is checked bit for bit against sklearn (labels, centres, iteration count) with a NumPy stand-in for the two
+device steps, including duplicated points, fewer distinct points than clusters and N = k (tests/test_kmeans_host.py, CPU);
+the GPU test does the same for the whole on the B200 box (tests/test_gpu_kmeans.py)."""
 import warnings
 
 import numpy as np
@@ -41,11 +41,52 @@ def _center_shift(old, new):
     return np.sqrt(res)
 
 
-def fit_predict(X, n_clusters, random_state=0):
-    """-> (labels (N,) int32, cluster_centers (k, d) float64, n_iter)."""
+class _DeviceSteps:
+    """The two O(N k) steps of a Lloyd iteration on the device (gpk_kmeans_step): the points go up once, per iteration the
+    centres and their squared norms go up and the per-cluster sums, counts and the changed flag come down."""
+
+    def __init__(self, X, k):
+        self.lib = _lib.load()
+        self.n, self.d = X.shape
+        self.k = k
+        n, d = self.n, self.d
+        dev = engine.device()
+        self.stream = torch.cuda.current_stream(dev.index)
+        self.d_x = torch.from_numpy(X).to(dev)
+        self.d_labels = torch.full((n,), -1, dtype=torch.int32, device=dev)
+        self.pin_in = torch.empty(k * (d + 1), dtype=torch.float64).pin_memory()          # [centres | squared norms]
+        self.d_in = torch.empty(k * (d + 1), dtype=torch.float64, device=dev)
+        self.d_out = torch.zeros(k * (d + 1) + 1, dtype=torch.float64, device=dev)        # [sums | counts | changed flag (int32)]
+        self.pin_out = torch.empty(k * (d + 1) + 1, dtype=torch.float64).pin_memory()
+        self.np_in, self.np_out = self.pin_in.numpy(), self.pin_out.numpy()
+        self.flag_view = self.d_out[k * (d + 1):]
+
+    def step(self, centers, csq, with_sums):
+        """-> (changed, sums (k, d), counts (k,)); the labels stay on the device."""
+        k, d = self.k, self.d
+        self.np_in[:k * d] = centers.reshape(-1)
+        self.np_in[k * d:] = csq
+        self.d_in.copy_(self.pin_in, non_blocking=True)
+        self.flag_view.zero_()
+        base_in, base_out = self.d_in.data_ptr(), self.d_out.data_ptr()
+        rc = self.lib.gpk_kmeans_step(self.d_x.data_ptr(), self.n, d, base_in, base_in + k * d * 8, k, self.d_labels.data_ptr(),
+                                      base_out + k * (d + 1) * 8, base_out if with_sums else None,
+                                      base_out + k * d * 8 if with_sums else None, self.stream.cuda_stream)
+        _lib.check(rc, "gpk_kmeans_step")
+        self.pin_out.copy_(self.d_out, non_blocking=True)
+        self.stream.synchronize()
+        changed = bool(self.np_out[k * (d + 1):].view(np.int32)[0])
+        return changed, self.np_out[:k * d].reshape(k, d).copy(), self.np_out[k * d:k * (d + 1)].copy()
+
+    def labels(self):
+        return self.d_labels.cpu().numpy()
+
+
+def fit_predict(X, n_clusters, random_state=0, _backend=None):
+    """-> (labels (N,) int32, cluster_centers (k, d) float64, n_iter).  `_backend` (tests): a factory (X, k) -> object with
+    step(centers, csq, with_sums) and labels() standing in for the device steps."""
     from sklearn.cluster import kmeans_plusplus
     from sklearn.exceptions import ConvergenceWarning
-    lib = _lib.load()
     X = np.array(X, dtype=np.float64, order="C", copy=True)
     n, d = X.shape
     k = int(n_clusters)
@@ -60,42 +101,18 @@ def fit_predict(X, n_clusters, random_state=0):
     centers, _ = kmeans_plusplus(X, k, x_squared_norms=x_sq, random_state=random_state)
     centers = np.ascontiguousarray(centers, dtype=np.float64)
 
-    dev = engine.device()
-    stream = torch.cuda.current_stream(dev.index)
-    st = stream.cuda_stream
-    d_x = torch.from_numpy(X).to(dev)
-    d_labels = torch.full((n,), -1, dtype=torch.int32, device=dev)
-    pin_in = torch.empty(k * (d + 1), dtype=torch.float64).pin_memory()          # [centres | squared norms]
-    d_in = torch.empty(k * (d + 1), dtype=torch.float64, device=dev)
-    d_out = torch.zeros(k * (d + 1) + 1, dtype=torch.float64, device=dev)        # [sums | counts | changed flag (as int32)]
-    pin_out = torch.empty(k * (d + 1) + 1, dtype=torch.float64).pin_memory()
-    np_in, np_out = pin_in.numpy(), pin_out.numpy()
-    p_centers, p_csq = d_in.data_ptr(), d_in.data_ptr() + k * d * 8
-    p_sums, p_counts, p_flag = d_out.data_ptr(), d_out.data_ptr() + k * d * 8, d_out.data_ptr() + k * (d + 1) * 8
-    flag_view = d_out[k * (d + 1):]
+    backend = _backend(X, k) if _backend is not None else _DeviceSteps(X, k)
 
     def e_step(cur, with_sums):
-        np_in[:k * d] = cur.reshape(-1)
-        np_in[k * d:] = np.einsum("ij,ij->i", cur, cur)          # row_norms(centers_old, squared=True)
-        d_in.copy_(pin_in, non_blocking=True)
-        flag_view.zero_()
-        rc = lib.gpk_kmeans_step(d_x.data_ptr(), n, d, p_centers, p_csq, k, d_labels.data_ptr(), p_flag,
-                                 p_sums if with_sums else None, p_counts if with_sums else None, st)
-        _lib.check(rc, "gpk_kmeans_step")
-        pin_out.copy_(d_out, non_blocking=True)
-        stream.synchronize()
-        changed = bool(np_out[k * (d + 1):].view(np.int32)[0])
-        return changed
+        return backend.step(cur, np.einsum("ij,ij->i", cur, cur), with_sums)     # row_norms(centers_old, squared=True)
 
     strict = False
     n_iter = 0
     for it in range(MAX_ITER):
-        changed = e_step(centers, True)
-        new = np_out[:k * d].reshape(k, d).copy()
-        w = np_out[k * d:k * (d + 1)].copy()
+        changed, new, w = e_step(centers, True)
         empty = np.where(np.equal(w, 0))[0]
         if len(empty):                                           # _relocate_empty_clusters_dense
-            labels = d_labels.cpu().numpy()
+            labels = backend.labels()
             dist = ((X - centers[labels]) ** 2).sum(axis=1)
             far = np.argpartition(dist, -len(empty))[:-len(empty) - 1:-1]
             if np.max(dist) != 0:
@@ -125,7 +142,7 @@ def fit_predict(X, n_clusters, random_state=0):
             break
     if not strict:
         e_step(centers, False)                                   # "rerun E-step so that predicted labels match cluster centers"
-    labels = d_labels.cpu().numpy()
+    labels = backend.labels()
     if len(set(labels.tolist())) < k:
         warnings.warn("Number of distinct clusters ({}) found smaller than n_clusters ({}). Possibly due to duplicate points "
                       "in X.".format(len(set(labels.tolist())), k), ConvergenceWarning, stacklevel=2)
