@@ -29,6 +29,12 @@ CASES = [
     ("one dim", dict(n=50, d=1, seed=8), dict(num_particles=5, max_iter=40)),
     ("blocked path", dict(n=300, d=2, seed=9), dict(num_particles=10, max_iter=12, max_points=1000)),
     ("blocked path, emulated", dict(n=1024, d=2, seed=4), dict(num_particles=6, max_iter=5, max_points=2000)),
+    ("no iterations", dict(n=30, d=2, seed=1), dict(num_particles=5, max_iter=0)),
+    ("single particle", dict(n=30, d=2, seed=2), dict(num_particles=1, max_iter=25, patience=6)),
+    ("four dims", dict(n=80, d=4, seed=6), dict(num_particles=16, max_iter=40, patience=9)),
+    ("patience beyond the run", dict(n=45, d=2, seed=7), dict(num_particles=8, max_iter=30, patience=1000)),
+    ("restart every iteration", dict(n=45, d=2, seed=7), dict(num_particles=8, max_iter=20, patience=1)),
+    ("kmeans subsample first", dict(n=400, d=2, seed=8), dict(num_particles=10, max_iter=15)),
 ]
 
 
